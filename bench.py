@@ -1,0 +1,352 @@
+#!/usr/bin/env python3
+"""bench.py -- NF4 fused-MoE expert path on B200.
+
+    python bench.py --gpus 1 --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W     # the reference's CPU path (oracle port) on host cores
+    torchrun ... bench.py --gpus N ...                        # expert-parallel, one rank per GPU
+
+Workload at N=1 (BASELINE.json configs[1]): the 24 MoE layers of gpt-oss-20b (H=I=2880, 32 experts, top-4, NF4 bs64,
+double-quant absmax) in the decode regime, T=64 tokens; one "step" = one pass of all 24 layers over the batch.
+`value` = T / step-time with everything resident in HBM (CUDA-graph replay, CUDA events); `e2e` = the same through the
+public `B200NF4MoEMethod.apply_legacy` call with host buffers (H2D of x + logits and D2H of the output inside the timed
+region).  9.6 GB of weights are streamed per step, far more than the 126 MB L2, so no explicit L2 flush is needed.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+H = I = 2880
+TOP_K = 4
+SEED = 20250805
+METRIC = "NF4 MoE-layer tokens/s (24-layer gpt-oss-20b MoE stack, decode)"
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=20)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--tokens", type=int, default=64, help="tokens per rank (decode batch)")
+    p.add_argument("--layers", type=int, default=24)
+    p.add_argument("--experts", type=int, default=32)
+    p.add_argument("--absmax", default="nested", choices=["nested", "flat"])
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--cpu-tokens", type=int, default=16)
+    return p.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0: float, t1: float) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [l.split(", ") for ts, l in self.lines if t0 - 0.05 <= ts <= t1 + 0.15] or [l.split(", ") for _, l in self.lines]
+        sm = [float(r[1]) for r in rows if len(r) >= 9]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            if len(r) >= 9:
+                for n, v in zip(names, r[5:9]):
+                    if v.strip().lower() == "active":
+                        reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": float(rows[0][2]) if rows and len(rows[0]) >= 3 else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks() -> tuple[float, str]:
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------------- CPU arm
+def cpu_states(rng, E, rows, cols):
+    """Synthetic bnb quant states made directly (random codes, plausible double-quant absmax): same bytes and arithmetic
+    per weight as a quantised N(0, 0.02^2) matrix, without minutes of CPU quantisation."""
+    import numpy as np
+    from oracle import nf4_oracle as orc
+    nb = rows * cols // 64
+    n2 = -(-nb // 256)
+    code2 = orc.create_dynamic_map()
+    return [{"packed": rng.integers(0, 256, size=rows * cols // 2, dtype=np.uint8),
+             "absmax_u8": rng.integers(0, 256, size=nb, dtype=np.uint8),
+             "absmax2": (rng.random(n2, dtype=np.float32) * np.float32(0.01) + np.float32(0.005)), "code2": code2,
+             "offset": np.float32(0.05), "shape": (rows, cols), "blocksize": 64} for _ in range(E)]
+
+
+def cpu_layer_seconds(st13, st2, T, E, reps, warm):
+    """The reference path on CPU (oracle): bnb-semantics dequant of every expert, per-expert fp16 matmul (fp32 acc),
+    clamped SwiGLU, top-4 weighted sum -- one MoE layer, T tokens."""
+    import numpy as np
+    import torch
+    from oracle import nf4_oracle as orc
+    torch.set_num_threads(os.cpu_count() or 1)
+    rng = np.random.default_rng(SEED)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    times = []
+    for i in range(warm + reps):
+        t0 = time.perf_counter()
+        orc.moe_forward_from_states(x, lg, st13, st2, k=TOP_K, nested=True)
+        dt = time.perf_counter() - t0
+        if i >= warm:
+            times.append(dt)
+    return times
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path.  The reference's files cannot be imported on
+    a box without bitsandbytes, so this is the oracle port; each step is ONE layer of the 24-layer workload on
+    `--cpu-tokens` tokens (bounded sample), scaled to the stack metric."""
+    import numpy as np
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    E = args.experts
+    rng = np.random.default_rng(SEED)
+    st13, st2 = cpu_states(rng, E, 2 * I, H), cpu_states(rng, E, H, I)
+    steps, warm = max(1, min(args.steps, 6)), max(0, min(args.warmup, 1))
+    T = args.cpu_tokens
+    times = cpu_layer_seconds(st13, st2, T, E, steps, warm)
+    sec = sum(times) / len(times)
+    val = T / (sec * args.layers)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "tokens/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16 storage / f32 accumulate (CPU)", "data": "synthetic (random NF4 codes + double-quant absmax made in numpy)",
+            "config": {"workload": f"gpt-oss-20b NF4 MoE stack decode, CPU oracle port: 1 of {args.layers} layers x {T} tokens per step, "
+                                   f"tokens/s scaled by 1/{args.layers}", "hidden": H, "intermediate": I, "experts": E, "top_k": TOP_K,
+                       "layers": args.layers, "tokens": T},
+            "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port",
+                             "sample": f"one MoE layer, T={T}, all {E} experts dequantised (as V/.../bitsandbytes.py:588-603 does); "
+                                       f"mean of {steps} after {warm} warm-up; steps capped at 6 to bound CPU time"},
+            "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------- GPU arm
+def make_stack(pkg, dev, layers, E, code2):
+    import torch
+    g = torch.Generator(device=dev).manual_seed(SEED)
+    stack = []
+    for _ in range(layers):
+        w13 = pkg.NF4ExpertWeights.quantize((torch.randn(E, 2 * I, H, generator=g, device=dev) * 0.02).half(), code2)
+        w2 = pkg.NF4ExpertWeights.quantize((torch.randn(E, H, I, generator=g, device=dev) * 0.02).half(), code2)
+        stack.append((w13, w2))
+    torch.cuda.synchronize(dev)
+    return stack
+
+
+def state_to_cpu(w, e):
+    return {"packed": w.packed[e].cpu().numpy().reshape(-1), "absmax_u8": w.absmax_u8[e].cpu().numpy(),
+            "absmax2": w.absmax2[e].cpu().numpy(), "code2": w.code2.cpu().numpy(), "offset": w.offset[e].item(),
+            "shape": (w.rows, w.cols), "blocksize": 64}
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from oracle import nf4_oracle as orc     # cpu_baseline leg only (and the code2 table, which is data)
+    pkg = importlib.import_module("gpt-oss-vllm_b200")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: there is no CPU fallback on the product path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if world != args.gpus and rank == 0:
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}", file=sys.stderr)
+
+    E, T, L, K, W = args.experts, args.tokens, args.layers, args.steps, max(3, args.warmup)
+    nested = args.absmax == "nested"
+    code2 = torch.from_numpy(orc.create_dynamic_map())
+    if world > 1:
+        ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+        return ep.bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, METRIC)
+
+    stack = make_stack(pkg, dev, L, E, code2)
+    g = torch.Generator(device=dev).manual_seed(SEED + 1)
+    x = torch.randn(T, H, generator=g, device=dev).half()
+    logits = [torch.randn(T, E, generator=g, device=dev).half() for _ in range(L)]
+    outs = [torch.empty(T, H, dtype=torch.float16, device=dev) for _ in range(L)]
+    ws = pkg.ops.get_workspace(dev, T, E, H, I, TOP_K)
+
+    def stack_forward():
+        for l, (w13, w2) in enumerate(stack):
+            pkg.ops.moe_forward(x, w13, w2, TOP_K, router_logits=logits[l], out=outs[l], workspace=ws, nested=nested,
+                                regime=pkg.REGIME_GEMV)
+
+    stack_forward()
+    launches_per_layer = pkg.ops.last_launch_count()
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        stack_forward()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(graph, stream=side):
+            stack_forward()
+    torch.cuda.synchronize()
+
+    # ---- value: device-resident, CUDA-graph replay, CUDA events ----
+    for _ in range(W):
+        graph.replay()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.25)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    t_wall0 = time.time()
+    torch.cuda.synchronize()
+    ev[0].record()
+    for i in range(K):
+        graph.replay()
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    t_wall1 = time.time()
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(K)]
+    total_ms = ev[0].elapsed_time(ev[K])
+    ms_per_step = total_ms / K
+    value = T / (ms_per_step * 1e-3)
+
+    # ---- e2e: public API, host buffers, H2D + D2H inside the timed region ----
+    method = pkg.B200NF4MoEMethod(top_k=TOP_K, nested=nested, regime=pkg.REGIME_GEMV)
+    layers_mod = []
+    for w13, w2 in stack:
+        m = torch.nn.Module()
+        method.bind(m, w13, w2)
+        layers_mod.append(m)
+    hx = x.cpu().pin_memory()
+    hlg = torch.stack([l.cpu() for l in logits]).pin_memory()
+    hout = torch.empty(T, H, dtype=torch.float16).pin_memory()
+
+    def e2e_step():
+        dx = hx.to(dev, non_blocking=True)
+        dlg = hlg.to(dev, non_blocking=True)
+        o = None
+        for l, m in enumerate(layers_mod):
+            o = method.apply_legacy(m, dx, dlg[l], TOP_K)
+        hout.copy_(o, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for _ in range(W):
+        e2e_step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        e2e_step()
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / K
+    clocks = sampler.stop(t_wall0, time.time())
+
+    # ---- roofline of the dominant kernel (w13 GEMV), timed live with CUDA events on the launching stream ----
+    peak, peak_src = measured_peaks()
+    t13, t2, eact = [], [], []
+    for rep in range(3):
+        for l, (w13, w2) in enumerate(stack):
+            ids, wts = pkg.ops.route_topk(logits[l], TOP_K)
+            b = pkg.ops.bucket(ids, E, want_tiles=False)
+            a0, a1, a2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            a0.record()
+            hbuf = pkg.ops.expert_w13(x, w13, b, T, TOP_K, nested=nested)
+            a1.record()
+            pkg.ops.expert_w2(hbuf, w2, b, T, TOP_K, nested=nested)
+            a2.record()
+            torch.cuda.synchronize()
+            if rep > 0:
+                t13.append(a0.elapsed_time(a1))
+                t2.append(a1.elapsed_time(a2))
+                eact.append(int(b["meta"][0].item()))
+    ea = sum(eact) / len(eact)
+    b13 = ea * stack[0][0].nbytes(nested) + T * H * 2 + T * TOP_K * I * 2
+    b2 = ea * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2
+    d13, d2 = statistics.mean(t13) * 1e-3, statistics.mean(t2) * 1e-3
+    layer_bytes = b13 + b2
+    roof = {"bound": "hbm", "kernel": "gemv_kernel<NT=2,W13> (w13 NF4 GEMV + SwiGLU)", "achieved": b13 / d13 / 1e9, "peak": peak,
+            "unit": "GB/s", "frac": b13 / d13 / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": b13, "avg_launch_us": d13 * 1e6, "frac_of_nominal_8TBs": b13 / d13 / 8e12,
+            "w2_kernel": {"achieved": b2 / d2 / 1e9, "frac": b2 / d2 / 1e9 / peak, "avg_launch_us": d2 * 1e6,
+                          "algorithmic_bytes_per_launch": b2},
+            "whole_step": {"achieved": layer_bytes * L / (ms_per_step * 1e-3) / 1e9,
+                           "frac": layer_bytes * L / (ms_per_step * 1e-3) / 1e9 / peak, "experts_active_mean": ea}}
+
+    line = {"metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": 1, "steps": K, "warmup": W,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "nf4 weights -> f16 mma operands, f32 accumulate, f16 activations", "data": "synthetic (seeded N(0,0.02^2) weights quantised on device, N(0,1) tokens and logits)",
+            "config": {"workload": f"gpt-oss-20b {L}-layer NF4 MoE stack decode, T={T} (BASELINE.json configs[1])", "hidden": H,
+                       "intermediate": I, "experts": E, "top_k": TOP_K, "layers": L, "tokens": T, "absmax": args.absmax,
+                       "regime": "gemv", "l2": "9.6 GB of weights streamed per step >> 126 MB L2 (no flush needed)",
+                       "cuda_graph": True, "per_layer_us": ms_per_step * 1e3 / L},
+            "clocks": clocks,
+            "e2e": {"value": T / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2 + hlg.numel() * 2,
+                    "d2h_bytes_per_step": hout.numel() * 2, "ms_per_step": e2e_ms,
+                    "api": "B200NF4MoEMethod.apply_legacy(layer, x, router_logits, top_k) x 24, pinned host buffers"},
+            "gpu_launches": launches_per_layer * L * K, "launches_per_layer": launches_per_layer,
+            "roofline": roof, "step_ms_min_max": [min(step_ms), max(step_ms)]}
+
+    if not args.no_cpu_baseline:
+        st13 = [state_to_cpu(stack[0][0], e) for e in range(E)]
+        st2 = [state_to_cpu(stack[0][1], e) for e in range(E)]
+        Tc = args.cpu_tokens
+        times = cpu_layer_seconds(st13, st2, Tc, E, reps=2, warm=0)
+        sec = min(times)
+        line["cpu_baseline"] = {"value": Tc / (sec * L), "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port",
+                                "sample": f"oracle port of the reference path, ONE of the {L} layers, T={Tc} tokens, all {E} experts "
+                                          f"dequantised then fp16 matmul per expert; best of 2; scaled to the stack by 1/{L}",
+                                "layer_seconds": sec}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

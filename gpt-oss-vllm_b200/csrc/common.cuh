@@ -1,0 +1,196 @@
+// Shared device helpers for libnf4moe (sm_100a only).  No CPU fallback exists anywhere in this library.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/nf4moe.h"
+
+#ifndef __CUDA_ARCH_FEAT_SM100_ALL
+#if defined(__CUDA_ARCH__)
+#error "libnf4moe is written for sm_100a (compile with -gencode arch=compute_100a,code=sm_100a)"
+#endif
+#endif
+
+namespace nf4moe {
+
+constexpr int kBlock = 64;    // NF4 quantisation block (P/unsloth_bnb_loader.py:71,112)
+constexpr int kNested = 256;  // double-quant block
+
+// P/streaming_unsloth_bnb.py:101-106 (values only; exactly representable in fp32)
+__device__ __constant__ float kNF4[16] = {-1.0f,
+                                          -0.6961928009986877f,
+                                          -0.5250730514526367f,
+                                          -0.39491748809814453f,
+                                          -0.28444138169288635f,
+                                          -0.18477343022823334f,
+                                          -0.09105003625154495f,
+                                          0.0f,
+                                          0.07958029955625534f,
+                                          0.16093020141124725f,
+                                          0.24611230194568634f,
+                                          0.33791524171829224f,
+                                          0.44070982933044434f,
+                                          0.5626170039176941f,
+                                          0.7229568362236023f,
+                                          1.0f};
+
+// Device-side view of nf4moe_qweight with the per-expert strides resolved.
+struct QW {
+  const uint8_t* packed;
+  const float* absmax_f32;
+  const uint8_t* absmax_u8;
+  const float* absmax2;
+  const float* code2;
+  const float* offset;
+  long long code2_stride;
+  int rows, cols;
+  int nkb;              // cols / 64
+  long long nb;         // blocks per expert = rows * nkb
+  long long n2;         // nested blocks per expert = ceil(nb / 256)
+  long long packed_stride;  // bytes per expert
+};
+
+inline QW make_qw(const nf4moe_qweight& w) {
+  QW q;
+  q.packed = w.packed;
+  q.absmax_f32 = w.absmax_f32;
+  q.absmax_u8 = w.absmax_u8;
+  q.absmax2 = w.absmax2;
+  q.code2 = w.code2;
+  q.offset = w.offset;
+  q.code2_stride = w.code2_stride;
+  q.rows = w.rows;
+  q.cols = w.cols;
+  q.nkb = w.cols / kBlock;
+  q.nb = (long long)w.rows * q.nkb;
+  q.n2 = (q.nb + kNested - 1) / kNested;
+  q.packed_stride = (long long)w.rows * w.cols / 2;
+  return q;
+}
+
+// absmax of block b of expert e, bnb double-quant semantics: two separately rounded fp32 ops
+// (V/model_executor/model_loader/bitsandbytes_loader.py:599-601).
+__device__ __forceinline__ float absmax_of(const QW& q, int e, long long b) {
+  if (q.absmax_f32) return __ldg(q.absmax_f32 + (long long)e * q.nb + b);
+  const uint8_t c = __ldg(q.absmax_u8 + (long long)e * q.nb + b);
+  const float s = __ldg(q.absmax2 + (long long)e * q.n2 + (b >> 8));
+  const float v = __ldg(q.code2 + (long long)e * q.code2_stride + c);
+  return __fadd_rn(__fmul_rn(v, s), __ldg(q.offset + e));
+}
+
+// ---- PTX wrappers -------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
+// TMA 1-D bulk copy global -> shared, completion counted on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// D(16x8,f32) += A(16x16,f16,row) * B(16x8,f16,col)   (SASS: HMMA.16816.F32)
+__device__ __forceinline__ void mma_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                          uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+
+__device__ __forceinline__ uint32_t pack_half2(float lo, float hi) {
+  __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// gpt-oss activation, V/model_executor/layers/activation.py:389-397; inputs already rounded to fp16 storage.
+__device__ __forceinline__ float swiglu_oai(float g, float u) {
+  g = fminf(g, 7.0f);
+  u = fminf(fmaxf(u, -7.0f), 7.0f);
+  const float glu = g * (1.0f / (1.0f + __expf(-1.702f * g)));
+  return (u + 1.0f) * glu;
+}
+// the reference wrapper's own variant, P/unsloth_to_vllm_converter.py:312-315
+__device__ __forceinline__ float silu_mul(float g, float u) { return g / (1.0f + __expf(-g)) * u; }
+
+}  // namespace nf4moe

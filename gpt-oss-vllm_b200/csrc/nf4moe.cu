@@ -1,0 +1,390 @@
+// libnf4moe.so -- C ABI over the sm_100a kernels (single translation unit).  See include/nf4moe.h for the contract.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "dequant.cuh"
+#include "gemm_tc.cuh"
+#include "gemv.cuh"
+#include "route.cuh"
+
+using namespace nf4moe;
+
+namespace {
+
+thread_local char g_err[512] = "";
+thread_local int g_launches = 0;
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+  return (int)e;
+}
+
+#define CHECK_LAUNCH(what)                                  \
+  do {                                                      \
+    ++g_launches;                                           \
+    cudaError_t e__ = cudaGetLastError();                   \
+    if (e__ != cudaSuccess) return cuda_fail(e__, what);    \
+  } while (0)
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+struct DevInfo {
+  int sms = 0;
+  int cc_major = 0;
+};
+
+int device_info(DevInfo* out) {
+  static thread_local int cached_dev = -1;
+  static thread_local DevInfo cached;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  if (dev != cached_dev) {
+    e = cudaDeviceGetAttribute(&cached.sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+    e = cudaDeviceGetAttribute(&cached.cc_major, cudaDevAttrComputeCapabilityMajor, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+    cached_dev = dev;
+  }
+  if (cached.cc_major != 10) return fail(NF4MOE_EARCH, "libnf4moe needs an sm_100 device (got sm_%d0)", cached.cc_major);
+  *out = cached;
+  return 0;
+}
+
+int check_qw(const nf4moe_qweight* w, const char* name) {
+  if (!w || !w->packed) return fail(NF4MOE_EINVAL, "%s: null weight", name);
+  if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "%s: cols must be a multiple of 64", name);
+  if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset))
+    return fail(NF4MOE_EINVAL, "%s: give absmax_f32 or the nested {absmax_u8, absmax2, code2, offset}", name);
+  if (!aligned16(w->packed) || (w->absmax_f32 && !aligned16(w->absmax_f32)) || (w->absmax_u8 && !aligned16(w->absmax_u8)))
+    return fail(NF4MOE_EALIGN, "%s: packed/absmax pointers must be 16-byte aligned", name);
+  return 0;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct Workspace {
+  int32_t *ids, *offsets, *sorted, *active, *meta, *tiles;
+  float* weights;
+  __half *h, *raw, *xs, *y;
+  size_t total;
+};
+
+Workspace carve(void* base, int T, int E, int H, int I, int k) {
+  Workspace w;
+  char* p = reinterpret_cast<char*>(base);
+  size_t off = 0;
+  const size_t n = (size_t)T * k;
+  const size_t n_pad = align_up(n, 128) + 128;
+  auto take = [&](size_t bytes) {
+    char* r = p ? p + off : nullptr;
+    off += align_up(bytes, 256);
+    return r;
+  };
+  w.ids = (int32_t*)take(n * 4);
+  w.weights = (float*)take(n * 4);
+  w.offsets = (int32_t*)take((size_t)(E + 1) * 4);
+  w.sorted = (int32_t*)take(n_pad * 4);
+  w.active = (int32_t*)take((size_t)E * 4);
+  w.meta = (int32_t*)take(64);
+  w.tiles = (int32_t*)take((n / 128 + E + 2) * 8);
+  w.h = (__half*)take(n_pad * I * 2);
+  w.raw = (__half*)take(n_pad * 2 * I * 2);
+  w.xs = (__half*)take(n_pad * H * 2);
+  w.y = (__half*)take(n * H * 2);
+  w.total = off;
+  return w;
+}
+
+template <int NT, bool W13, bool NESTED>
+int launch_gemv_inst(const GemvArgs& args, int sms, cudaStream_t stream) {
+  static thread_local bool attr_set = false;
+  auto kern = gemv_kernel<NT, W13, NESTED>;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemvSmemBytes);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemv)");
+    attr_set = true;
+  }
+  kern<<<sms, kGemvThreads, kGemvSmemBytes, stream>>>(args);
+  CHECK_LAUNCH("gemv_kernel");
+  return 0;
+}
+
+template <bool W13>
+int launch_gemv(const GemvArgs& args, int T, bool nested, int sms, cudaStream_t stream) {
+  // every expert sees at most T rows (top-k experts of a token are distinct): T <= 8 needs one token tile
+  if (T <= 8) return nested ? launch_gemv_inst<1, W13, true>(args, sms, stream) : launch_gemv_inst<1, W13, false>(args, sms, stream);
+  return nested ? launch_gemv_inst<2, W13, true>(args, sms, stream) : launch_gemv_inst<2, W13, false>(args, sms, stream);
+}
+
+int check_gemv_shape(const nf4moe_qweight* w, const char* name) {
+  if (int rc = check_qw(w, name)) return rc;
+  if (w->cols > kGemvMaxK) return fail(NF4MOE_EINVAL, "%s: decode kernel supports cols <= %d", name, kGemvMaxK);
+  if (w->rows % kGemvRows) return fail(NF4MOE_EINVAL, "%s: rows must be a multiple of 16", name);
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nf4moe_version(void) { return NF4MOE_VERSION; }
+const char* nf4moe_last_error(void) { return g_err; }
+int nf4moe_last_launch_count(void) { return g_launches; }
+
+size_t nf4moe_workspace_bytes(int T, int E, int H, int I, int k) {
+  if (T < 0 || E <= 0 || H <= 0 || I <= 0 || k <= 0) return 0;
+  return carve(nullptr, T, E, H, I, k).total;
+}
+
+int nf4moe_dequant(const nf4moe_qweight* w, int e0, int ne, void* out_f16, void* stream) {
+  if (int rc = check_qw(w, "dequant")) return rc;
+  if (!out_f16 || e0 < 0 || ne < 0) return fail(NF4MOE_EINVAL, "dequant: bad arguments");
+  if (!aligned16(out_f16)) return fail(NF4MOE_EALIGN, "dequant: out must be 16-byte aligned");
+  if (ne == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  const QW q = make_qw(*w);
+  const long long per = q.packed_stride / 16, total = per * ne;
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 16);
+  dequant_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(q, e0, per, total, (__half*)out_f16);
+  CHECK_LAUNCH("dequant_kernel");
+  return 0;
+}
+
+int nf4moe_dequant_absmax(const nf4moe_qweight* w, int E, float* out, void* stream) {
+  if (!w || !out || E <= 0) return fail(NF4MOE_EINVAL, "dequant_absmax: bad arguments");
+  if (!(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "dequant_absmax: nested state required");
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  nf4moe_qweight tmp = *w;
+  tmp.absmax_f32 = nullptr;
+  const QW q = make_qw(tmp);
+  const long long total = q.nb * E;
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 16);
+  dequant_absmax_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(q, total, out);
+  CHECK_LAUNCH("dequant_absmax_kernel");
+  return 0;
+}
+
+int nf4moe_quantize(const void* w_f16, int E, int rows, int cols, uint8_t* packed, uint8_t* absmax_u8, float* absmax2,
+                    const float* code2, float* offset, float* absmax_f32_out, void* scratch, void* stream) {
+  if (!w_f16 || !packed || !absmax_u8 || !absmax2 || !code2 || !offset || !scratch || E <= 0 || rows <= 0 || cols <= 0 ||
+      cols % kBlock)
+    return fail(NF4MOE_EINVAL, "quantize: bad arguments");
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long nb = (long long)rows * (cols / kBlock), n2 = (nb + kNested - 1) / kNested, total = nb * E;
+  double* sums = reinterpret_cast<double*>(scratch);
+  float* am = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + align_up((size_t)E * 8, 256));
+  cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)E * 8, st);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync");
+  const int grid = (int)std::min<long long>((total + 7) / 8, (long long)di.sms * 32);
+  quantize_blocks_kernel<<<grid, 256, 0, st>>>((const __half*)w_f16, nb, total, packed, am, sums);
+  CHECK_LAUNCH("quantize_blocks_kernel");
+  quantize_nested_kernel<<<(unsigned)(n2 * E), 256, 0, st>>>(am, nb, n2, sums, code2, absmax_u8, absmax2, offset,
+                                                            absmax_f32_out);
+  CHECK_LAUNCH("quantize_nested_kernel");
+  return 0;
+}
+
+int nf4moe_route_topk(const void* logits, int dtype, int T, int E, int k, int32_t* ids, float* weights, void* stream) {
+  if (!logits || !ids || !weights || T < 0 || k <= 0 || k > 32 || k > E || dtype < 0 || dtype > 2)
+    return fail(NF4MOE_EINVAL, "route_topk: bad arguments");
+  if (E <= 0 || E > 256) return fail(NF4MOE_EINVAL, "route_topk: E must be in 1..256 (got %d)", E);
+  if (T == 0) return 0;
+  const int grid = (T + 7) / 8;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int per_lane = (E + 31) / 32;
+  switch (per_lane <= 2 ? per_lane : per_lane <= 4 ? 4 : 8) {
+    case 1: route_topk_kernel<1><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
+    case 2: route_topk_kernel<2><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
+    case 4: route_topk_kernel<4><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
+    case 8: route_topk_kernel<8><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
+    default: return fail(NF4MOE_EINVAL, "route_topk: unsupported E %d", E);
+  }
+  CHECK_LAUNCH("route_topk_kernel");
+  return 0;
+}
+
+int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* sorted_pairs,
+                  int32_t* active_experts, int32_t* meta, int32_t* tile_list, void* stream) {
+  if (!ids || !expert_offsets || !sorted_pairs || !active_experts || !meta || T < 0 || k <= 0 || E <= 0 || E > 255)
+    return fail(NF4MOE_EINVAL, "bucket: bad arguments (E must be <= 255)");
+  const long long n = (long long)T * k;
+  const size_t smem = (size_t)((n + 31) & ~31ll);
+  if (smem > 200 * 1024) return fail(NF4MOE_EINVAL, "bucket: T*k = %lld exceeds the single-CTA limit of 204800 pairs", n);
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(bucket)");
+    attr_set = true;
+  }
+  bucket_kernel<<<1, kBucketThreads, smem, (cudaStream_t)stream>>>(ids, (int)n, E, expert_offsets, sorted_pairs,
+                                                                  active_experts, meta, tile_list);
+  CHECK_LAUNCH("bucket_kernel");
+  return 0;
+}
+
+int nf4moe_permute_rows(const void* x, const int32_t* sorted_pairs, const int32_t* meta, int T, int k, int H,
+                        void* x_sorted, void* stream) {
+  if (!x || !sorted_pairs || !meta || !x_sorted || T < 0 || k <= 0 || H <= 0 || H % 8)
+    return fail(NF4MOE_EINVAL, "permute_rows: bad arguments");
+  if (!aligned16(x) || !aligned16(x_sorted)) return fail(NF4MOE_EALIGN, "permute_rows: 16-byte alignment required");
+  if (T == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  const long long rows = (long long)T * k;
+  const int grid = (int)std::min<long long>((rows + 7) / 8, (long long)di.sms * 8);
+  permute_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)x, sorted_pairs, meta, (int)rows, k, H,
+                                                             (__half*)x_sorted);
+  CHECK_LAUNCH("permute_rows_kernel");
+  return 0;
+}
+
+int nf4moe_combine(const void* y, const float* weights, const int32_t* ids, int E, int T, int k, int H, void* out,
+                   void* stream) {
+  if (!y || !weights || !out || T < 0 || k <= 0 || H <= 0 || H % 8) return fail(NF4MOE_EINVAL, "combine: bad arguments");
+  if (!aligned16(y) || !aligned16(out)) return fail(NF4MOE_EALIGN, "combine: 16-byte alignment required");
+  if (T == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  const long long total = (long long)T * (H / 8);
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 8);
+  combine_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y, weights, ids, E, T, k, H, (__half*)out);
+  CHECK_LAUNCH("combine_kernel");
+  return 0;
+}
+
+int nf4moe_gemv_w13_swiglu(const void* x, const nf4moe_qweight* w13, const int32_t* expert_offsets,
+                           const int32_t* sorted_pairs, const int32_t* active_experts, const int32_t* meta, int T, int k,
+                           int E, int act, void* h_sorted, void* stream) {
+  if (int rc = check_gemv_shape(w13, "gemv_w13")) return rc;
+  if (!x || !expert_offsets || !sorted_pairs || !active_experts || !meta || !h_sorted || T < 0 || k <= 0 || E <= 0 ||
+      (w13->rows & 1) || (act != NF4MOE_ACT_SWIGLU_OAI && act != NF4MOE_ACT_CHUNK_SILU))
+    return fail(NF4MOE_EINVAL, "gemv_w13: bad arguments");
+  if (!aligned16(x)) return fail(NF4MOE_EALIGN, "gemv_w13: x must be 16-byte aligned");
+  if (T == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  GemvArgs a;
+  a.w = make_qw(*w13);
+  a.x = (const __half*)x;
+  a.out = h_sorted;
+  a.expert_offsets = expert_offsets;
+  a.sorted_pairs = sorted_pairs;
+  a.active_experts = active_experts;
+  a.meta = meta;
+  a.k = k;
+  a.act = act;
+  return launch_gemv<true>(a, T, w13->absmax_f32 == nullptr, di.sms, (cudaStream_t)stream);
+}
+
+int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
+                   const int32_t* sorted_pairs, const int32_t* active_experts, const int32_t* meta, int T, int k, int E,
+                   void* y, void* stream) {
+  if (int rc = check_gemv_shape(w2, "gemv_w2")) return rc;
+  if (!h_sorted || !expert_offsets || !sorted_pairs || !active_experts || !meta || !y || T < 0 || k <= 0 || E <= 0)
+    return fail(NF4MOE_EINVAL, "gemv_w2: bad arguments");
+  if (!aligned16(h_sorted)) return fail(NF4MOE_EALIGN, "gemv_w2: h must be 16-byte aligned");
+  if (T == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  GemvArgs a;
+  a.w = make_qw(*w2);
+  a.x = (const __half*)h_sorted;
+  a.out = y;
+  a.expert_offsets = expert_offsets;
+  a.sorted_pairs = sorted_pairs;
+  a.active_experts = active_experts;
+  a.meta = meta;
+  a.k = k;
+  a.act = 0;
+  return launch_gemv<false>(a, T, w2->absmax_f32 == nullptr, di.sms, (cudaStream_t)stream);
+}
+
+int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
+                           const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted,
+                           void* stream) {
+  return gemm_w13_entry(x_sorted, w13, expert_offsets, meta, tile_list, T, k, E, act, h_sorted, stream, g_err, sizeof(g_err),
+                        &g_launches);
+}
+
+int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
+                   const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
+                   void* y, void* stream) {
+  return gemm_w2_entry(h_sorted, w2, expert_offsets, sorted_pairs, meta, tile_list, T, k, E, y, stream, g_err, sizeof(g_err),
+                       &g_launches);
+}
+
+int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtype, const int32_t* topk_ids,
+                       const float* topk_weights, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* out, int T,
+                       int E, int H, int I, int k, int act, int regime, void* workspace, size_t workspace_bytes,
+                       int32_t* topk_ids_out, float* topk_weights_out, void* stream) {
+  g_launches = 0;
+  if (!x || !out || !w13 || !w2 || T < 0 || E <= 0 || H <= 0 || I <= 0 || k <= 0)
+    return fail(NF4MOE_EINVAL, "moe_forward: bad arguments");
+  if (!router_logits && !(topk_ids && topk_weights))
+    return fail(NF4MOE_EINVAL, "moe_forward: give router_logits or (topk_ids, topk_weights)");
+  if (w13->rows != 2 * I || w13->cols != H || w2->rows != H || w2->cols != I)
+    return fail(NF4MOE_EINVAL, "moe_forward: weight shapes must be w13 [2I,H] = [%d,%d], w2 [H,I] = [%d,%d]", 2 * I, H, H, I);
+  if (T == 0) return 0;
+  const Workspace ws = carve(workspace, T, E, H, I, k);
+  if (!workspace || workspace_bytes < ws.total)
+    return fail(NF4MOE_EWORKSPACE, "moe_forward: workspace needs %zu bytes, got %zu", ws.total, workspace_bytes);
+  if (!aligned16(workspace)) return fail(NF4MOE_EALIGN, "moe_forward: workspace must be 16-byte aligned");
+  cudaStream_t st = (cudaStream_t)stream;
+  int launches = 0;
+  const int32_t* ids = topk_ids;
+  const float* wts = topk_weights;
+  if (router_logits) {
+    int32_t* ids_w = topk_ids_out ? topk_ids_out : ws.ids;
+    float* wts_w = topk_weights_out ? topk_weights_out : ws.weights;
+    if (int rc = nf4moe_route_topk(router_logits, logits_dtype, T, E, k, ids_w, wts_w, stream)) return rc;
+    launches += g_launches; g_launches = 0;
+    ids = ids_w;
+    wts = wts_w;
+  }
+  if (regime == NF4MOE_REGIME_AUTO) regime = gemm_available() && T > kGemmAutoThreshold ? NF4MOE_REGIME_GEMM : NF4MOE_REGIME_GEMV;
+  const bool gemm = regime == NF4MOE_REGIME_GEMM;
+  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, stream)) return rc;
+  launches += g_launches; g_launches = 0;
+  __half* h_dst = act == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
+  if (gemm) {
+    if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
+    launches += g_launches; g_launches = 0;
+    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act, h_dst, stream)) return rc;
+  } else {
+    if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act, h_dst, stream)) return rc;
+  }
+  launches += g_launches; g_launches = 0;
+  if (act == NF4MOE_ACT_CHUNK_SILU) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    chunk_silu_kernel<<<di.sms * 4, 256, 0, st>>>(ws.raw, ws.meta, I, ws.h);
+    CHECK_LAUNCH("chunk_silu_kernel");
+    launches += g_launches; g_launches = 0;
+  }
+  if (gemm) {
+    if (int rc = nf4moe_gemm_w2(ws.h, w2, ws.offsets, ws.sorted, ws.meta, ws.tiles, T, k, E, ws.y, stream)) return rc;
+  } else {
+    if (int rc = nf4moe_gemv_w2(ws.h, w2, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, ws.y, stream)) return rc;
+  }
+  launches += g_launches; g_launches = 0;
+  if (int rc = nf4moe_combine(ws.y, wts, ids, E, T, k, H, out, stream)) return rc;
+  g_launches += launches;
+  return 0;
+}
+
+}  // extern "C"

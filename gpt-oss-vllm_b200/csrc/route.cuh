@@ -1,0 +1,196 @@
+// Router top-k, expert bucketing (stable counting sort), row permute and the weighted un-permute epilogue.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace nf4moe {
+
+// ---------------------------------------------------------------------------------------------------------------
+// (1) router: one warp per token, E/32 logits per lane, k rounds of warp arg-max with shuffles
+// (ties -> lowest expert index, like torch.topk on the reference's P/unsloth_to_vllm_converter.py:291), then a
+// softmax over the k selected logits in fp32 (:292) == softmax -> top-k -> renormalise.
+// ---------------------------------------------------------------------------------------------------------------
+template <int kPerLane>
+__global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict__ logits, int dtype, int T, int E, int k,
+                                                         int32_t* __restrict__ ids, float* __restrict__ weights) {
+  const int lane = threadIdx.x & 31;
+  const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (t >= T) return;
+  float v[kPerLane];
+#pragma unroll
+  for (int i = 0; i < kPerLane; ++i) {
+    const int eid = i * 32 + lane;
+    const long long idx = (long long)t * E + eid;
+    float x;
+    if (eid >= E) x = -INFINITY;
+    else if (dtype == 0) x = __half2float(reinterpret_cast<const __half*>(logits)[idx]);
+    else if (dtype == 1) x = reinterpret_cast<const float*>(logits)[idx];
+    else x = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(logits)[idx]);
+    // NaN never wins a comparison below; map it to -inf so the order stays total.
+    v[i] = (x == x) ? x : -INFINITY;
+  }
+  float sel_v = 0.f;  // lane j keeps the j-th selected logit / id
+  int sel_i = 0;
+  float vmax = 0.f;
+  for (int j = 0; j < k; ++j) {
+    float best = v[0];
+    int bi = lane;
+#pragma unroll
+    for (int i = 1; i < kPerLane; ++i)
+      if (v[i] > best) { best = v[i]; bi = i * 32 + lane; }  // strict >: lower index wins inside a lane
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if (j == 0) vmax = best;
+    if (lane == j) { sel_v = best; sel_i = bi; }
+    if ((bi & 31) == lane) {
+#pragma unroll
+      for (int i = 0; i < kPerLane; ++i)
+        if (i == (bi >> 5)) v[i] = -INFINITY;  // taken
+    }
+  }
+  const float ex = lane < k ? expf(sel_v - vmax) : 0.f;
+  float sum = ex;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane < k) {
+    ids[(long long)t * k + lane] = sel_i;
+    weights[(long long)t * k + lane] = ex / sum;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// (2) bucketing: ONE CTA of 1024 threads; ids staged in shared memory as bytes (E <= 256; 0xFF = dropped).
+// Warp w owns experts w, w+32, ...: a counting pass and a placement pass over all pairs with ballots, so the
+// order inside an expert is ascending pair index (deterministic).  Replaces the per-(token,k) `.item()` dispatch of
+// P/unsloth_to_vllm_converter.py:298-305.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kBucketThreads = 1024;
+constexpr int kTileRows = 128;  // M tile of the grouped GEMM
+
+__global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* __restrict__ ids, int n_pairs, int E,
+                                                                int32_t* __restrict__ expert_offsets,
+                                                                int32_t* __restrict__ sorted_pairs,
+                                                                int32_t* __restrict__ active_experts,
+                                                                int32_t* __restrict__ meta,
+                                                                int32_t* __restrict__ tile_list) {
+  extern __shared__ uint8_t s_ids[];  // n_pairs rounded up to 32
+  __shared__ int s_count[256];
+  __shared__ int s_off[257];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int n_pad = (n_pairs + 31) & ~31;
+  for (int i = tid; i < n_pad; i += kBucketThreads) {
+    int e = i < n_pairs ? ids[i] : -1;
+    s_ids[i] = (e >= 0 && e < E) ? (uint8_t)e : (uint8_t)0xFF;
+  }
+  if (tid < 256) s_count[tid] = 0;
+  __syncthreads();
+  for (int e = warp; e < E; e += 32) {
+    int c = 0;
+    for (int i = lane; i < n_pad; i += 32) c += __popc(__ballot_sync(0xffffffffu, s_ids[i] == e));
+    if (lane == 0) s_count[e] = c;
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive scan over <= 256 experts, 8 per lane
+    int loc[8], run = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { loc[j] = run; run += s_count[lane * 8 + j]; }
+    int inc = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    const int base = inc - run;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s_off[lane * 8 + j] = base + loc[j];
+    if (lane == 31) s_off[256] = inc;
+  }
+  __syncthreads();
+  for (int e = tid; e <= E; e += kBucketThreads) expert_offsets[e] = s_off[e];
+  if (tid == 0) {  // E <= 256 entries: serial compaction is a few hundred cycles
+    int na = 0, nt = 0, mx = 0;
+    for (int e = 0; e < E; ++e) {
+      const int c = s_count[e];
+      if (c > 0) {
+        active_experts[na++] = e;
+        mx = max(mx, c);
+        if (tile_list)
+          for (int r = 0; r < c; r += kTileRows) { tile_list[2 * nt] = e; tile_list[2 * nt + 1] = s_off[e] + r; ++nt; }
+        else
+          nt += (c + kTileRows - 1) / kTileRows;
+      }
+    }
+    for (int i = na; i < E; ++i) active_experts[i] = -1;
+    meta[0] = na; meta[1] = s_off[E]; meta[2] = nt; meta[3] = mx;
+  }
+  for (int e = warp; e < E; e += 32) {
+    int run = s_off[e];
+    for (int i = lane; i < n_pad; i += 32) {
+      const bool hit = s_ids[i] == e;
+      const unsigned m = __ballot_sync(0xffffffffu, hit);
+      if (hit) sorted_pairs[run + __popc(m & ((1u << lane) - 1u))] = i;
+      run += __popc(m);
+    }
+  }
+}
+
+// x_sorted[s,:] = x[sorted_pairs[s]/k,:]; one warp per row, 16-byte accesses.  Rows past meta[1] are zeroed so the
+// grouped GEMM's last tile reads defined data.
+__global__ void __launch_bounds__(256) permute_rows_kernel(const __half* __restrict__ x,
+                                                           const int32_t* __restrict__ sorted_pairs,
+                                                           const int32_t* __restrict__ meta, int n_rows, int k, int H,
+                                                           __half* __restrict__ xs) {
+  const int lane = threadIdx.x & 31;
+  const int n_kept = meta[1];
+  const int vec = H / 8;
+  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < n_rows; s += (gridDim.x * blockDim.x) >> 5) {
+    uint4* dst = reinterpret_cast<uint4*>(xs + (long long)s * H);
+    if (s < n_kept) {
+      const uint4* src = reinterpret_cast<const uint4*>(x + (long long)(sorted_pairs[s] / k) * H);
+      for (int i = lane; i < vec; i += 32) dst[i] = __ldg(src + i);
+    } else {
+      for (int i = lane; i < vec; i += 32) dst[i] = make_uint4(0, 0, 0, 0);
+    }
+  }
+}
+
+// (5) out[t,:] = fp16( sum_slot w[t,slot] * y[t*k+slot,:] ), fp32, slot ascending
+// (P/unsloth_to_vllm_converter.py:321-323).  One thread = 8 columns.
+__global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ y, const float* __restrict__ w,
+                                                      const int32_t* __restrict__ ids, int E, int T, int k, int H,
+                                                      __half* __restrict__ out) {
+  const int vec = H / 8;
+  const long long total = (long long)T * vec;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(i / vec), c = (int)(i - (long long)t * vec);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < k; ++s) {
+      if (ids) {
+        const int e = ids[(long long)t * k + s];
+        if (e < 0 || e >= E) continue;
+      }
+      const float ws = w[(long long)t * k + s];
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(y + ((long long)t * k + s) * H) + c);
+      const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = __half22float2(h[j]);
+        acc[2 * j] = __fadd_rn(acc[2 * j], __fmul_rn(ws, f.x));
+        acc[2 * j + 1] = __fadd_rn(acc[2 * j + 1], __fmul_rn(ws, f.y));
+      }
+    }
+    uint4 o;
+    uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ow[j] = pack_half2(acc[2 * j], acc[2 * j + 1]);
+    reinterpret_cast<uint4*>(out + (long long)t * H)[c] = o;
+  }
+}
+
+}  // namespace nf4moe

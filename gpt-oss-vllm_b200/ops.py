@@ -1,0 +1,174 @@
+"""Tensor-level wrappers over the C ABI (one Python function per entry point of include/nf4moe.h).
+
+All tensors must live on one CUDA device; calls are asynchronous on torch's current stream of that device and do not
+synchronise.  Nothing here falls back to PyTorch math.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .quant import NF4ExpertWeights, _require_cuda, _stream_ptr
+
+_ws_cache: dict[tuple, torch.Tensor] = {}
+
+
+def workspace_bytes(T: int, E: int, H: int, I: int, k: int) -> int:
+    return int(_lib.load_library().nf4moe_workspace_bytes(T, E, H, I, k))
+
+
+def get_workspace(device, T: int, E: int, H: int, I: int, k: int) -> torch.Tensor:
+    """A cached scratch buffer (one per device and shape; grown, never shrunk)."""
+    key = (str(device), E, H, I, k)
+    need = workspace_bytes(T, E, H, I, k)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def route_topk(logits: torch.Tensor, k: int) -> tuple[torch.Tensor, torch.Tensor]:
+    """(ids int32 [T,k], weights fp32 [T,k]); P/unsloth_to_vllm_converter.py:291-292."""
+    _require_cuda(logits, "router_logits")
+    T, E = logits.shape
+    dt = _lib.LOGITS_DTYPE[str(logits.dtype).replace("torch.", "")]
+    ids = torch.empty(T, k, dtype=torch.int32, device=logits.device)
+    w = torch.empty(T, k, dtype=torch.float32, device=logits.device)
+    with torch.cuda.device(logits.device):
+        _lib.check(_lib.load_library().nf4moe_route_topk(logits.data_ptr(), dt, T, E, k, ids.data_ptr(), w.data_ptr(),
+                                                         _stream_ptr(logits.device)))
+    return ids, w
+
+
+def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True) -> dict[str, torch.Tensor]:
+    """Stable counting sort of the (token,slot) pairs by expert -> offsets / sorted_pairs / active / meta / tiles."""
+    _require_cuda(ids, "topk_ids")
+    T, k = ids.shape
+    dev = ids.device
+    n = T * k
+    out = {
+        "expert_offsets": torch.empty(E + 1, dtype=torch.int32, device=dev),
+        "sorted_pairs": torch.full(((n + 127) // 128 * 128 + 128,), -1, dtype=torch.int32, device=dev),
+        "active_experts": torch.empty(E, dtype=torch.int32, device=dev),
+        "meta": torch.zeros(16, dtype=torch.int32, device=dev),
+        "tile_list": torch.full((2 * (n // 128 + E + 2),), -1, dtype=torch.int32, device=dev) if want_tiles else None,
+    }
+    with torch.cuda.device(dev):
+        _lib.check(_lib.load_library().nf4moe_bucket(
+            ids.data_ptr(), T, k, E, out["expert_offsets"].data_ptr(), out["sorted_pairs"].data_ptr(),
+            out["active_experts"].data_ptr(), out["meta"].data_ptr(),
+            out["tile_list"].data_ptr() if want_tiles else None, _stream_ptr(dev)))
+    return out
+
+
+def permute_rows(x: torch.Tensor, b: dict, k: int) -> torch.Tensor:
+    T, H = x.shape
+    xs = torch.empty((T * k + 127) // 128 * 128 + 128, H, dtype=torch.float16, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load_library().nf4moe_permute_rows(x.data_ptr(), b["sorted_pairs"].data_ptr(), b["meta"].data_ptr(),
+                                                           T, k, H, xs.data_ptr(), _stream_ptr(x.device)))
+    return xs
+
+
+def combine(y: torch.Tensor, weights: torch.Tensor, ids: torch.Tensor | None, E: int) -> torch.Tensor:
+    T, k = weights.shape
+    H = y.shape[-1]
+    out = torch.empty(T, H, dtype=torch.float16, device=y.device)
+    with torch.cuda.device(y.device):
+        _lib.check(_lib.load_library().nf4moe_combine(y.data_ptr(), weights.data_ptr(),
+                                                      None if ids is None else ids.data_ptr(), E, T, k, H,
+                                                      out.data_ptr(), _stream_ptr(y.device)))
+    return out
+
+
+def expert_w13(x: torch.Tensor, w13: NF4ExpertWeights, b: dict, T: int, k: int, act: int = _lib.ACT_SWIGLU_OAI,
+               nested: bool | None = None, regime: int = _lib.REGIME_GEMV) -> torch.Tensor:
+    """h_sorted fp16 [rows_padded, I] (act fused) or [rows_padded, 2I] raw for ACT_CHUNK_SILU."""
+    lib = _lib.load_library()
+    E = w13.num_experts
+    width = w13.rows // 2 if act == _lib.ACT_SWIGLU_OAI else w13.rows
+    h = torch.zeros((T * k + 127) // 128 * 128 + 128, width, dtype=torch.float16, device=x.device)
+    q = w13.c_struct(nested)
+    with torch.cuda.device(x.device):
+        if regime == _lib.REGIME_GEMM:
+            _lib.check(lib.nf4moe_gemm_w13_swiglu(x.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
+                                                  b["meta"].data_ptr(), b["tile_list"].data_ptr(), T, k, E, act,
+                                                  h.data_ptr(), _stream_ptr(x.device)))
+        else:
+            _lib.check(lib.nf4moe_gemv_w13_swiglu(x.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
+                                                  b["sorted_pairs"].data_ptr(), b["active_experts"].data_ptr(),
+                                                  b["meta"].data_ptr(), T, k, E, act, h.data_ptr(),
+                                                  _stream_ptr(x.device)))
+    return h
+
+
+def expert_w2(h: torch.Tensor, w2: NF4ExpertWeights, b: dict, T: int, k: int, nested: bool | None = None,
+              regime: int = _lib.REGIME_GEMV) -> torch.Tensor:
+    """y fp16 [T*k, H] in (token, slot) order."""
+    lib = _lib.load_library()
+    E = w2.num_experts
+    y = torch.zeros(T * k, w2.rows, dtype=torch.float16, device=h.device)
+    q = w2.c_struct(nested)
+    with torch.cuda.device(h.device):
+        if regime == _lib.REGIME_GEMM:
+            _lib.check(lib.nf4moe_gemm_w2(h.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
+                                          b["sorted_pairs"].data_ptr(), b["meta"].data_ptr(), b["tile_list"].data_ptr(),
+                                          T, k, E, y.data_ptr(), _stream_ptr(h.device)))
+        else:
+            _lib.check(lib.nf4moe_gemv_w2(h.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
+                                          b["sorted_pairs"].data_ptr(), b["active_experts"].data_ptr(),
+                                          b["meta"].data_ptr(), T, k, E, y.data_ptr(), _stream_ptr(h.device)))
+    return y
+
+
+def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, top_k: int,
+                router_logits: torch.Tensor | None = None, topk_ids: torch.Tensor | None = None,
+                topk_weights: torch.Tensor | None = None, act: int = _lib.ACT_SWIGLU_OAI,
+                regime: int = _lib.REGIME_AUTO, nested: bool | None = None, out: torch.Tensor | None = None,
+                workspace: torch.Tensor | None = None, return_routing: bool = False):
+    """The whole layer (nf4moe_moe_forward): x fp16 [T,H] -> fp16 [T,H]."""
+    _require_cuda(x, "hidden_states")
+    if x.dtype != torch.float16:
+        raise TypeError("hidden_states must be fp16 (the reference serves with --dtype float16)")
+    lib = _lib.load_library()
+    T, H = x.shape
+    E, I = w13.num_experts, w13.rows // 2
+    dev = x.device
+    if out is None:
+        out = torch.empty(T, H, dtype=torch.float16, device=dev)
+    if workspace is None:
+        workspace = get_workspace(dev, T, E, H, I, top_k)
+    ldt = 0
+    if router_logits is not None:
+        _require_cuda(router_logits, "router_logits")
+        ldt = _lib.LOGITS_DTYPE[str(router_logits.dtype).replace("torch.", "")]
+    else:
+        if topk_ids is None or topk_weights is None:
+            raise ValueError("give router_logits or (topk_ids, topk_weights)")
+        if topk_ids.dtype != torch.int32:
+            topk_ids = topk_ids.to(torch.int32)
+        if topk_weights.dtype != torch.float32:
+            topk_weights = topk_weights.to(torch.float32)
+        topk_ids, topk_weights = topk_ids.contiguous(), topk_weights.contiguous()
+    ids_out = w_out = None
+    if return_routing and router_logits is not None:
+        ids_out = torch.empty(T, top_k, dtype=torch.int32, device=dev)
+        w_out = torch.empty(T, top_k, dtype=torch.float32, device=dev)
+    q13, q2 = w13.c_struct(nested), w2.c_struct(nested)
+    with torch.cuda.device(dev):
+        _lib.check(lib.nf4moe_moe_forward(
+            x.data_ptr(), None if router_logits is None else router_logits.data_ptr(), ldt,
+            None if topk_ids is None else topk_ids.data_ptr(), None if topk_weights is None else topk_weights.data_ptr(),
+            C.byref(q13), C.byref(q2), out.data_ptr(), T, E, H, I, top_k, act, regime, workspace.data_ptr(),
+            workspace.numel(), None if ids_out is None else ids_out.data_ptr(),
+            None if w_out is None else w_out.data_ptr(), _stream_ptr(dev)))
+    if return_routing:
+        return out, (ids_out if ids_out is not None else topk_ids), (w_out if w_out is not None else topk_weights)
+    return out
+
+
+def last_launch_count() -> int:
+    return int(_lib.load_library().nf4moe_last_launch_count())

@@ -1,0 +1,166 @@
+/*
+ * nf4moe.h -- C ABI of libnf4moe.so: the bitsandbytes-NF4 fused-MoE expert path on B200 (sm_100a).
+ *
+ * This is the drop-in boundary.  Each entry point names the reference interface it replaces
+ * (P/ = toddllm/gpt-oss-vllm patches/, V/ = vLLM 0.22 site-packages/vllm/):
+ *
+ *   nf4moe_dequant            bitsandbytes.functional.dequantize_4bit as called from
+ *                             V/model_executor/layers/quantization/bitsandbytes.py:588-603 and restated on CPU by
+ *                             P/streaming_unsloth_bnb.py:109-230 (dequant_unsloth_expert_cpu)
+ *   nf4moe_dequant_absmax     the double-quant de-nesting of V/model_executor/model_loader/bitsandbytes_loader.py:585-617
+ *                             and P/unsloth_direct_loader.py:21-48 (dequantize_absmax)
+ *   nf4moe_quantize           bnb quantize_4bit(blocksize=64, compress_statistics=True, quant_type='nf4') as invoked by
+ *                             P/bnb_moe_4bit.py:86-91 and P/streaming_unsloth_loader.py:48-71
+ *   nf4moe_route_topk         P/unsloth_to_vllm_converter.py:291-292 == V/.../fused_moe/router/fused_topk_router.py:69-102
+ *   nf4moe_bucket             the per-(token,k) expert dispatch loop of P/unsloth_to_vllm_converter.py:298-305
+ *                             (== moe_align_block_size inside V/.../fused_moe/fused_moe.py fused_experts)
+ *   nf4moe_gemv_w13_swiglu    w13_experts[e](x) + split + activation, P/unsloth_to_vllm_converter.py:309-315,
+ *                             activation per V/model_executor/layers/activation.py:389-397
+ *   nf4moe_gemv_w2            w2_experts[e](intermediate), P/unsloth_to_vllm_converter.py:318
+ *   nf4moe_gemm_w13_swiglu /
+ *   nf4moe_gemm_w2            same two products at prefill sizes (vLLM: Triton fused_experts, V/.../fused_moe.py:1587-1617)
+ *   nf4moe_combine            token_output += weight * expert_output, P/unsloth_to_vllm_converter.py:321-323
+ *   nf4moe_moe_forward        UnslothMoEWrapper.forward (P/unsloth_to_vllm_converter.py:282-325) ==
+ *                             BitsAndBytesMoEMethod.apply (V/.../quantization/bitsandbytes.py:478-506)
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller; the library allocates nothing and keeps no device state;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), does no host<->device sync and is
+ *     CUDA-graph capturable;
+ *   - return value: 0 on success, a negative NF4MOE_E* code on a usage error, or a positive cudaError_t passed through;
+ *     nf4moe_last_error() returns a thread-local description of the last failure;
+ *   - activations are fp16 (the reference serves with --dtype float16, P/gpt_oss_server.py:41), accumulation is fp32;
+ *   - packed weights: uint8, element 2j in the HIGH nibble, element 2j+1 in the LOW nibble (bitsandbytes order),
+ *     row-major [rows, cols] per expert, experts concatenated: exactly vLLM's `w13_weight[E, rows*cols/2, 1]`.
+ */
+#ifndef NF4MOE_H_
+#define NF4MOE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NF4MOE_VERSION 100 /* 0.1.0 */
+
+#define NF4MOE_OK 0
+#define NF4MOE_EINVAL (-1)      /* bad shape / null pointer / unsupported size */
+#define NF4MOE_EALIGN (-2)      /* pointer not 16-byte aligned */
+#define NF4MOE_EWORKSPACE (-3)  /* workspace too small */
+#define NF4MOE_EARCH (-4)       /* not an sm_100 device */
+
+/* activation selector for the w13 epilogue */
+#define NF4MOE_ACT_SWIGLU_OAI 0 /* interleaved, clamped, alpha=1.702, limit=7 (gpt-oss; the product default) */
+#define NF4MOE_ACT_CHUNK_SILU 1 /* gate=[:I], up=[I:], silu(gate)*up -- the reference wrapper's own variant */
+
+/* regime selector for nf4moe_moe_forward */
+#define NF4MOE_REGIME_AUTO 0
+#define NF4MOE_REGIME_GEMV 1  /* decode: HBM-bound NF4 streaming kernel */
+#define NF4MOE_REGIME_GEMM 2  /* prefill: tcgen05 grouped GEMM */
+
+/* One fused NF4 expert matrix set: E experts, each [rows, cols] row-major, cols % 64 == 0.
+ * Quantisation blocks (64) run along the flat row-major index, so block b of expert e covers
+ * row b / (cols/64), columns (b % (cols/64))*64 .. +63.
+ * Exactly one absmax form is given:
+ *   flat   : absmax_f32 != NULL, fp32 [E, rows*cols/64]       (what vLLM keeps after _dequantize_dq)
+ *   nested : absmax_f32 == NULL; absmax_u8 [E, nb], absmax2 fp32 [E, ceil(nb/256)], code2 fp32 [256] (+ e*code2_stride),
+ *            offset fp32 [E]:  absmax[b] = code2[absmax_u8[b]] * absmax2[b/256] + offset   (two roundings, no FMA)
+ *            -- the on-disk Unsloth/bnb key set {.absmax, .nested_absmax, .nested_quant_map} of P/unsloth_bnb_loader.py:202-222. */
+typedef struct nf4moe_qweight {
+  const uint8_t* packed;
+  const float* absmax_f32;
+  const uint8_t* absmax_u8;
+  const float* absmax2;
+  const float* code2;
+  const float* offset;
+  int64_t code2_stride; /* 0: one table shared by all experts; 256: one per expert */
+  int32_t rows;
+  int32_t cols;
+} nf4moe_qweight;
+
+int nf4moe_version(void);
+const char* nf4moe_last_error(void);
+
+/* Scratch the fused forward needs for T tokens (bytes).  Layout is private to the library. */
+size_t nf4moe_workspace_bytes(int T, int E, int H, int I, int k);
+
+/* ---- NF4 (de)quantisation ------------------------------------------------------------------------------------ */
+
+/* out_f16[e, i] = fp16_rn( fp32(NF4[q_i]) * absmax[i/64] ) for experts [e0, e0+ne): bit-exact bnb semantics. */
+int nf4moe_dequant(const nf4moe_qweight* w, int e0, int ne, void* out_f16, void* stream);
+
+/* absmax_f32[e, b] = code2[absmax_u8[e,b]] * absmax2[e, b/256] + offset[e] for all E experts (nested form only). */
+int nf4moe_dequant_absmax(const nf4moe_qweight* w, int E, float* absmax_f32_out, void* stream);
+
+/* fp16 [E, rows, cols] -> packed NF4 + double-quantised absmax (also writes the de-nested fp32 absmax if non-NULL).
+ * `code2` (256 sorted fp32) is an INPUT.  Two passes on `stream`; `scratch` needs E*(rows*cols/64)*4 + E*8 + 512 bytes. */
+int nf4moe_quantize(const void* w_f16, int E, int rows, int cols, uint8_t* packed, uint8_t* absmax_u8, float* absmax2,
+                    const float* code2, float* offset, float* absmax_f32_out, void* scratch, void* stream);
+
+/* ---- routing --------------------------------------------------------------------------------------------------- */
+
+/* logits [T,E] (dtype: 0 = fp16, 1 = fp32, 2 = bf16) -> ids int32 [T,k] (descending logit, ties -> lowest index),
+ * weights fp32 [T,k] = softmax over the k selected logits (== softmax -> top-k -> renormalise). 1 <= E <= 256. */
+int nf4moe_route_topk(const void* logits, int logits_dtype, int T, int E, int k, int32_t* ids, float* weights,
+                      void* stream);
+
+/* Stable counting sort of the T*k (token,slot) pairs by expert.  ids outside [0,E) are dropped (expert-parallel
+ * callers mask non-local experts with -1).  Outputs (all int32):
+ *   expert_offsets[E+1]  exclusive prefix of per-expert pair counts
+ *   sorted_pairs[T*k]    pair index t*k+slot, grouped by expert, ascending within an expert
+ *   active_experts[E]    experts with >=1 pair, ascending;  meta[0] = how many, meta[1] = total kept pairs,
+ *                        meta[2] = number of (expert, 128-row tile) entries, meta[3] = largest per-expert count
+ *   tile_list[2*(ceil(T*k/128)+E)]  (expert, first sorted row) per 128-row tile of the grouped GEMM */
+int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* sorted_pairs,
+                  int32_t* active_experts, int32_t* meta, int32_t* tile_list, void* stream);
+
+/* x_sorted[s, :] = x[sorted_pairs[s] / k, :]  (fp16, H % 8 == 0); rows s >= meta[1] are zero-filled. */
+int nf4moe_permute_rows(const void* x, const int32_t* sorted_pairs, const int32_t* meta, int T, int k, int H,
+                        void* x_sorted, void* stream);
+
+/* out[t, :] = fp16( sum_slot weights[t,slot] * y[t*k+slot, :] ) in fp32, slot ascending; pairs whose id was dropped
+ * contribute zero (ids may be NULL when none are).  y is fp16 [T*k, H]. */
+int nf4moe_combine(const void* y, const float* weights, const int32_t* ids, int E, int T, int k, int H, void* out,
+                   void* stream);
+
+/* ---- expert products --------------------------------------------------------------------------------------------- */
+
+/* Decode regime.  h_sorted[s, j] = act( x[sorted_pairs[s]/k, :] . W13[e]^T )  for every sorted row s of every active e.
+ * w13->rows = 2*I, w13->cols = H (H % 64 == 0, H <= 2880, rows % 16 == 0). h_sorted is fp16 [T*k, I]. */
+int nf4moe_gemv_w13_swiglu(const void* x, const nf4moe_qweight* w13, const int32_t* expert_offsets,
+                           const int32_t* sorted_pairs, const int32_t* active_experts, const int32_t* meta, int T, int k,
+                           int E, int act, void* h_sorted, void* stream);
+
+/* y[sorted_pairs[s], n] = h_sorted[s, :] . W2[e]^T ; w2->rows = H, w2->cols = I.  y is fp16 [T*k, H]. */
+int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
+                   const int32_t* sorted_pairs, const int32_t* active_experts, const int32_t* meta, int T, int k, int E,
+                   void* y, void* stream);
+
+/* Prefill regime: the same two products as tcgen05 grouped GEMMs over 128-row tiles of x_sorted (from
+ * nf4moe_permute_rows), NF4 tiles dequantised into shared memory, accumulators in TMEM. */
+int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
+                           const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted,
+                           void* stream);
+int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
+                   const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
+                   void* y, void* stream);
+
+/* ---- the whole layer ---------------------------------------------------------------------------------------------- */
+
+/* out[T,H] = MoE(x[T,H]).  Routing is computed from `router_logits` when non-NULL (the north-star / legacy
+ * `apply(x, router_logits, top_k)` and vLLM `apply_monolithic` shape), else taken from topk_ids/topk_weights (vLLM 0.22
+ * `apply`).  `topk_ids_out`/`topk_weights_out` (optional) receive the routing actually used. */
+int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtype, const int32_t* topk_ids,
+                       const float* topk_weights, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* out, int T,
+                       int E, int H, int I, int k, int act, int regime, void* workspace, size_t workspace_bytes,
+                       int32_t* topk_ids_out, float* topk_weights_out, void* stream);
+
+/* Number of kernels the last nf4moe_moe_forward on this thread launched (bench.py's gpu_launches). */
+int nf4moe_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NF4MOE_H_ */

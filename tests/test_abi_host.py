@@ -1,0 +1,113 @@
+"""CPU: the C-ABI library loads and exports every symbol include/nf4moe.h declares; host-side logic; the product
+path never touches the oracle and fails loudly without a GPU (no compute calls are made here)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_header_symbols(pkg):
+    lib = pkg.load_library()
+    header = open(os.path.join(ROOT, "include", "nf4moe.h")).read()
+    body = header[header.index("typedef struct"):]                       # past the comment block that lists the ops
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    declared = set(re.findall(r"\b(nf4moe_[a-z0-9_]+)\s*\(", body))
+    assert declared == set(pkg._lib.EXPORTED)
+    for name in declared:
+        assert getattr(lib, name) is not None
+    assert lib.nf4moe_version() == 100
+    assert int(re.search(r"#define NF4MOE_VERSION (\d+)", header).group(1)) == 100
+
+
+def test_qweight_struct_layout_matches_header(pkg):
+    q = pkg._lib.QWeight
+    assert [f[0] for f in q._fields_] == ["packed", "absmax_f32", "absmax_u8", "absmax2", "code2", "offset",
+                                          "code2_stride", "rows", "cols"]
+    assert C.sizeof(q) == 6 * 8 + 8 + 4 + 4
+
+
+def test_usage_errors_return_codes_without_gpu(pkg):
+    lib = pkg.load_library()
+    q = pkg._lib.QWeight()
+    assert lib.nf4moe_dequant(C.byref(q), 0, 1, None, None) == -1          # NF4MOE_EINVAL: null packed
+    assert b"null" in lib.nf4moe_last_error()
+    q.packed, q.rows, q.cols = 16, 4, 100                                   # cols not a multiple of 64
+    assert lib.nf4moe_dequant(C.byref(q), 0, 1, 16, None) == -1
+    q.cols = 64                                                             # no absmax form
+    assert lib.nf4moe_dequant(C.byref(q), 0, 1, 16, None) == -1
+    q.absmax_f32, q.packed = 16, 8                                          # misaligned packed
+    assert lib.nf4moe_dequant(C.byref(q), 0, 1, 16, None) == -2            # NF4MOE_EALIGN
+    assert lib.nf4moe_route_topk(None, 0, 4, 32, 4, None, None, None) == -1
+    assert lib.nf4moe_moe_forward(None, None, 0, None, None, None, None, None, 4, 32, 64, 64, 4, 0, 0, None, 0, None,
+                                  None, None) == -1
+
+
+def test_workspace_bytes(pkg):
+    ws = pkg.ops.workspace_bytes
+    assert ws(0, 32, 2880, 2880, 4) > 0 and ws(64, 32, 2880, 2880, 4) > ws(1, 32, 2880, 2880, 4)
+    assert ws(8192, 32, 2880, 2880, 4) > 8192 * 4 * 2880 * 2 * 3
+    assert ws(1, 0, 1, 1, 1) == 0
+
+
+def test_config_and_create_weights_mirror_reference(pkg):
+    cfg = pkg.B200NF4MoEConfig()
+    assert cfg.get_name() == "bnb_moe_4bit"                                 # P/bnb_moe_4bit.py:33
+    assert cfg.is_moe_weight("model.layers.3.mlp.experts.w13_weight")       # P/bnb_moe_4bit.py:43-48
+    assert cfg.is_moe_weight("model.layers.3.mlp.experts.down_proj")
+    assert not cfg.is_moe_weight("model.layers.3.self_attn.qkv_proj")
+    assert cfg.get_quant_method(None, "model.layers.0.self_attn.o_proj") is None
+    m = cfg.get_quant_method(None, "model.layers.0.mlp.experts")
+    layer = torch.nn.Module()
+    m.create_weights(layer, 32, 2880, 2880, torch.float16, weight_loader="wl")
+    # P/validate_conversion.py:45-46, P/debug_shapes.py:53-54
+    assert tuple(layer.w13_weight.shape) == (32, 8294400, 1) and tuple(layer.w2_weight.shape) == (32, 4147200, 1)
+    assert layer.w13_weight.experts_shape == (32, 5760, 2880) and layer.w2_weight.experts_shape == (32, 2880, 2880)
+    assert layer.w13_weight.pack_factor == 2 and layer.w13_weight.use_bitsandbytes_4bit and layer.w13_weight.weight_loader == "wl"
+    n = sum(int(np.prod(p.experts_shape)) for p in (layer.w13_weight, layer.w2_weight))
+    assert n == 32 * (5760 * 2880 + 2880 * 2880)                            # P/validate_conversion.py:187
+    with pytest.raises(ValueError):
+        pkg.B200NF4MoEConfig(group_size=128)
+
+
+def test_expert_weights_validation_and_bytes(pkg):
+    packed = torch.zeros(2, 64 * 128 // 2, 1, dtype=torch.uint8)
+    w = pkg.NF4ExpertWeights(packed, 64, 128, absmax=torch.zeros(2, 128))
+    assert w.num_experts == 2 and w.blocks_per_expert == 128 and not w.has_nested
+    assert w.nbytes(nested=False) == 4096 + 512 and w.nbytes(nested=True) == 4096 + 128 + 4
+    with pytest.raises(ValueError):
+        pkg.NF4ExpertWeights(packed, 64, 100, absmax=torch.zeros(2, 100))
+    with pytest.raises(ValueError):
+        pkg.NF4ExpertWeights(packed, 64, 128)
+    with pytest.raises(ValueError):
+        w.c_struct(nested=True)
+    # 20b sizes (SURVEY 8 header)
+    big = pkg.NF4ExpertWeights.__new__(pkg.NF4ExpertWeights)
+    big.rows, big.cols = 5760, 2880
+    assert big.blocks_per_expert == 259200 and big.nbytes(False) == 8294400 + 1036800
+    assert big.nbytes(True) == 8294400 + 259200 + 4 * 1013
+
+
+def test_no_cpu_fallback(pkg):
+    packed = torch.zeros(1, 64 * 64 // 2, 1, dtype=torch.uint8)
+    w = pkg.NF4ExpertWeights(packed, 64, 64, absmax=torch.ones(1, 64))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        w.dequantize()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        pkg.ops.route_topk(torch.zeros(2, 32, dtype=torch.float16), 4)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        pkg.ops.moe_forward(torch.zeros(2, 64, dtype=torch.float16), w, w, 4,
+                            router_logits=torch.zeros(2, 32, dtype=torch.float16))
+
+
+def test_product_never_imports_oracle():
+    pk = os.path.join(ROOT, "gpt-oss-vllm_b200")
+    for dirpath, _, files in os.walk(pk):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "nf4_oracle" not in src and not re.search(r"^\s*(from|import)\s+oracle", src, re.M), f
