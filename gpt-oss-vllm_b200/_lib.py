@@ -56,7 +56,7 @@ def _declare(lib):
     lib.nf4moe_dequant_absmax.argtypes = [qp, i32, vp, vp]
     lib.nf4moe_quantize.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.nf4moe_route_topk.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp]
-    lib.nf4moe_bucket.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp]
+    lib.nf4moe_bucket.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp]
     lib.nf4moe_permute_rows.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
     lib.nf4moe_combine.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp]
     lib.nf4moe_gemv_w13_swiglu.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]

@@ -1,5 +1,26 @@
-// Prefill-regime grouped GEMM (tcgen05 / TMEM).  Placeholder until the kernel lands: the entry points fail loudly.
+// Prefill-regime grouped GEMM on the 5th-generation tensor cores (tcgen05 + TMEM), NF4 weights dequantised on the fly.
+//
+//   D[n, m] = sum_k W_e[n, k] * X[m, k]      n: 128 weight rows of expert e (MMA M, one TMEM lane each)
+//                                             m: up to 256 routed tokens of expert e (MMA N, one TMEM column each)
+//
+// The WEIGHTS are the A operand and live in TENSOR MEMORY: a dequant thread owns one weight row, so the fp32 absmax of
+// a 64-wide NF4 block is a per-thread scalar, the 32 packed bytes of the block are two LDS.128, every byte is decoded
+// through a bank-conflict-free shared-memory table (byte -> the two fp32 NF4 codes), scaled in fp32 and rounded ONCE
+// to fp16 -- bit-identical to bitsandbytes' dequantize_4bit, so the tensor cores see exactly the fp16 matrix the
+// reference multiplies with -- and the 32 packed half2 go to TMEM with one tcgen05.st.32x32b.x32.  The ACTIVATIONS are
+// the B operand, loaded by TMA (128B swizzle, K-major) straight into the canonical UMMA layout.  Each dequantised
+// weight therefore feeds up to 256 tokens, half the dequant work of the usual "tokens = M" arrangement, and no
+// dequantised weight ever touches shared or global memory.
+//
+// Roles (384 threads, one persistent CTA per SM):
+//   warp 0      TMA producer: raw NF4 tiles [128 rows x 128 B] every 4th k-block + activation tiles [<=256 x 64] per k-block
+//   warp 1      TMEM allocator and the single MMA-issuing thread (tcgen05.mma kind::f16, A in TMEM, B in smem)
+//   warps 4-11  dequant (two groups of four warps, alternate k-blocks), then the epilogue: tcgen05.ld, gpt-oss clamped
+//               SwiGLU on adjacent lanes (rows 2j / 2j+1 = gate / up) for w13, scatter to (token, slot) order for w2
+// Replaces vLLM's dequantise-everything + Triton fused_experts (V/.../quantization/bitsandbytes.py:478-506, 588-603).
 #pragma once
+#include <cuda.h>
+
 #include <cstdio>
 
 #include "common.cuh"
@@ -7,17 +28,410 @@
 namespace nf4moe {
 
 constexpr int kGemmAutoThreshold = 64;  // tokens; above this nf4moe_moe_forward(AUTO) uses the tcgen05 path
-inline bool gemm_available() { return false; }
+constexpr int kGemmThreads = 384;
+constexpr int kGemmTokTile = 256;       // max MMA N
+constexpr int kGemmRowTile = 128;       // MMA M
+constexpr int kAStages = 4;             // A (dequantised weights) stages in TMEM, 32 columns each
+constexpr int kMaxBStages = 6;
+constexpr int kMaxWStages = 3;
+constexpr uint32_t kWStageBytes = 128 * 128;   // raw NF4: 128 rows x 4 k-blocks x 32 B
+constexpr uint32_t kGemmSmemBytes = 232448 - 1024;  // dynamic part; the kernel's static __shared__ control block takes the rest
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kTmemACol = 256;     // D occupies columns [0,256), A stages [256, 256 + 4*32)
 
-inline int gemm_w13_entry(const void*, const nf4moe_qweight*, const int32_t*, const int32_t*, const int32_t*, int, int,
-                          int, int, void*, void*, char* err, size_t err_len, int*) {
-  snprintf(err, err_len, "gemm_w13: tcgen05 grouped GEMM not built in this version");
-  return NF4MOE_EINVAL;
+inline bool gemm_available() { return true; }
+
+// ---- tcgen05 / TMA wrappers -------------------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-inline int gemm_w2_entry(const void*, const nf4moe_qweight*, const int32_t*, const int32_t*, const int32_t*,
-                         const int32_t*, int, int, int, void*, void*, char* err, size_t err_len, int*) {
-  snprintf(err, err_len, "gemm_w2: tcgen05 grouped GEMM not built in this version");
-  return NF4MOE_EINVAL;
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void tc_mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float2 lds_f32x2(uint32_t addr) {
+  float2 v;
+  asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+      "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+      "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+struct GemmArgs {
+  QW w;
+  void* out;                      // W13: h fp16 [rows, I] (or raw [rows, 2I]);  W2: y fp16 [T*k, rows]
+  const int32_t* sorted_pairs;    // W2 scatter
+  const int32_t* meta;            // meta[2] = number of token tiles
+  const int32_t* tile_list;       // (expert, first sorted row, rows, -) per token tile
+  int act;
+  int box_tokens;                 // rows of the activation TMA box (256, or 32 for small batches)
+};
+
+// instruction descriptor: D f32, A/B f16, both K-major, M = 128, N = n
+__device__ __forceinline__ uint32_t make_idesc(int n) {
+  return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kGemmRowTile >> 4) << 24);
+}
+// K-major 128B-swizzled operand tile: 8-row atoms of 1024 B (SBO), descriptor version 1, layout SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_bdesc(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// barrier slots inside s_bar[]
+constexpr int kBarWFull = 0, kBarWEmpty = kBarWFull + kMaxWStages, kBarBFull = kBarWEmpty + kMaxWStages,
+              kBarBEmpty = kBarBFull + kMaxBStages, kBarAFull = kBarBEmpty + kMaxBStages, kBarAEmpty = kBarAFull + kAStages,
+              kBarDFull = kBarAEmpty + kAStages, kBarDEmpty = kBarDFull + 1, kNumGemmBars = kBarDEmpty + 1;
+
+template <bool W13>
+__global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a, const __grid_constant__ CUtensorMap map_w,
+                                                              const __grid_constant__ CUtensorMap map_x) {
+  extern __shared__ __align__(1024) uint8_t dyn_smem[];
+  __shared__ __align__(8) uint64_t s_bar[kNumGemmBars];
+  __shared__ uint32_t s_tmem;
+  __shared__ uint32_t s_wst[kMaxWStages], s_bst[kMaxBStages];
+  __shared__ int s_nw, s_nb;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nkb = a.w.nkb;
+  const uint32_t b_bytes = (uint32_t)a.box_tokens * 128u;
+  const uint32_t base = smem_u32(dyn_smem);
+  const uint32_t lut = pin((base + 65535u) & ~65535u);   // 64 KB aligned: PRMT drops the byte into address bits 8..15
+  const uint32_t bar0 = smem_u32(s_bar);
+  auto bar = [&](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
+
+  // ---- one-time setup ----
+  if (tid == 0) {
+    // carve [base, lut) and [lut + 64K, end) into 1024-aligned stages: as many activation stages as fit with >= 2 raw-weight stages
+    const uint32_t lo[2] = {(base + 1023u) & ~1023u, lut + 65536u}, hi[2] = {lut, base + kGemmSmemBytes};
+    int best_b = -1, best_w = 0, pick[2] = {0, 0};
+    for (int n0 = 0; n0 <= kMaxBStages; ++n0)
+      for (int n1 = 0; n0 + n1 <= kMaxBStages; ++n1) {
+        int nw = 0;
+        bool ok = true;
+        const int nbr[2] = {n0, n1};
+        for (int r = 0; r < 2; ++r) {
+          const long long room = (long long)hi[r] - (long long)lo[r] - (long long)nbr[r] * b_bytes;
+          if (room < 0) ok = false; else nw += (int)(room / kWStageBytes);
+        }
+        if (!ok || nw < 2) continue;
+        nw = min(nw, kMaxWStages);
+        if (n0 + n1 > best_b || (n0 + n1 == best_b && nw > best_w)) { best_b = n0 + n1; best_w = nw; pick[0] = n0; pick[1] = n1; }
+      }
+    int ib = 0, iw = 0;
+    for (int r = 0; r < 2; ++r) {
+      uint32_t cur = lo[r];
+      for (int i = 0; i < pick[r]; ++i) { s_bst[ib++] = cur; cur += b_bytes; }
+      cur = (cur + 1023u) & ~1023u;
+      while (iw < best_w && cur + kWStageBytes <= hi[r]) { s_wst[iw++] = cur; cur += kWStageBytes; }
+    }
+    s_nb = ib; s_nw = iw;
+    for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 8); }
+    for (int i = 0; i < kMaxBStages; ++i) { mbar_init(bar(kBarBFull + i), 1); mbar_init(bar(kBarBEmpty + i), 1); }
+    for (int i = 0; i < kAStages; ++i) { mbar_init(bar(kBarAFull + i), 4); mbar_init(bar(kBarAEmpty + i), 1); }
+    mbar_init(bar(kBarDFull), 1);
+    mbar_init(bar(kBarDEmpty), 8);
+    fence_barrier_init();
+  }
+  for (int i = tid; i < 256 * 32; i += kGemmThreads) {
+    const int b = i >> 5, l = i & 31;
+    const uint32_t p = lut + (uint32_t)b * 256u + (uint32_t)l * 8u;
+    sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
+    sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s_tmem;
+  const int n_bst = s_nb, n_wst = s_nw;
+
+  const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
+  const int n_items = a.meta[2] * n_row_tiles;
+
+  if (warp == 0) {
+    // =============================== TMA producer ===============================
+    if (lane == 0) {
+      int sb = 0, sw = 0;
+      uint32_t phb = 0, phw = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+        const int e = a.tile_list[4 * tile], row0 = a.tile_list[4 * tile + 1];
+        const int wrow = e * a.w.rows + rt * kGemmRowTile;
+        for (int kb = 0; kb < nkb; ++kb) {
+          if ((kb & 3) == 0) {
+            mbar_wait(bar(kBarWEmpty + sw), phw ^ 1u);
+            mbar_expect_tx(bar(kBarWFull + sw), kWStageBytes);
+            tma_load_2d(s_wst[sw], &map_w, kb * 32, wrow, bar(kBarWFull + sw));
+            if (++sw == n_wst) { sw = 0; phw ^= 1u; }
+          }
+          mbar_wait(bar(kBarBEmpty + sb), phb ^ 1u);
+          mbar_expect_tx(bar(kBarBFull + sb), b_bytes);
+          tma_load_2d(s_bst[sb], &map_x, kb * kBlock, row0, bar(kBarBFull + sb));
+          if (++sb == n_bst) { sb = 0; phb ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // =============================== MMA issuer (one thread) ===============================
+    if (lane == 0) {
+      int sb = 0;
+      uint32_t phb = 0, pha = 0, phd = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int tile = item / n_row_tiles;
+        const int n_tok = a.tile_list[4 * tile + 2];
+        const uint32_t idesc = make_idesc(max(16, (n_tok + 15) & ~15));
+        mbar_wait(bar(kBarDEmpty), phd ^ 1u);     // epilogue of the previous tile has drained the accumulator
+        phd ^= 1u;
+        tc_fence_after();
+        for (int kb = 0; kb < nkb; ++kb) {
+          const int sa = kb & 3;
+          mbar_wait(bar(kBarAFull + sa), (pha >> sa) & 1u);
+          mbar_wait(bar(kBarBFull + sb), phb);
+          tc_fence_after();
+          const uint32_t a_t = tmem + kTmemACol + (uint32_t)sa * 32u;
+          const uint32_t b_s = s_bst[sb];
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            tc_mma_ts(tmem, a_t + 8u * kk, make_bdesc(b_s + 32u * kk), idesc, (uint32_t)(kb | kk));
+          tc_commit(bar(kBarAEmpty + sa));
+          tc_commit(bar(kBarBEmpty + sb));
+          if (kb == nkb - 1) tc_commit(bar(kBarDFull));
+          pha ^= 1u << sa;
+          if (++sb == n_bst) { sb = 0; phb ^= 1u; }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // =============================== dequant + epilogue ===============================
+    const int q = warp & 3, g = (warp - 4) >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t lut_lane = pin(lut | ((uint32_t)lane << 3));
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
+    const uint32_t swz = (uint32_t)(r & 7);
+    int sw = 0;
+    uint32_t phw = 0, phd = 0, use0 = 0, use1 = 0;   // use counts of this group's two A stages (g and g+2)
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+      const int e = a.tile_list[4 * tile], row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
+      const int n = rt * kGemmRowTile + r;
+      const long long blk0 = (long long)min(n, a.w.rows - 1) * nkb;
+      for (int kb0 = 0; kb0 < nkb; kb0 += 4) {
+        float am[2];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const int kb = kb0 + g + 2 * jj;
+          am[jj] = kb < nkb ? absmax_of(a.w, e, blk0 + kb) : 0.f;
+        }
+        mbar_wait(bar(kBarWFull + sw), phw);
+        const uint32_t wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const int j = g + 2 * jj;
+          if (kb0 + j < nkb) {
+            const uint4 v0 = lds128(wrow + (((uint32_t)(2 * j) ^ swz) << 4));
+            const uint4 v1 = lds128(wrow + (((uint32_t)(2 * j + 1) ^ swz) << 4));
+            const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            uint32_t regs[32];
+#pragma unroll
+            for (int wi = 0; wi < 8; ++wi)
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float2 f = lds_f32x2(prmt(wd[wi], lut_lane, 0x7604u | ((uint32_t)i << 4)));
+                regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am[jj]), __fmul_rn(f.y, am[jj]));
+              }
+            uint32_t& use = jj ? use1 : use0;
+            mbar_wait(bar(kBarAEmpty + j), (use & 1u) ^ 1u);   // the MMAs that read this stage last time are done
+            ++use;
+            tc_fence_after();
+            tmem_st32(t_lane + kTmemACol + (uint32_t)j * 32u, regs);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(kBarAFull + j));
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(kBarWEmpty + sw));
+        if (++sw == n_wst) { sw = 0; phw ^= 1u; }
+      }
+      // ---- epilogue: this warp's lane quarter, alternate 32-column chunks per group ----
+      mbar_wait(bar(kBarDFull), phd);
+      phd ^= 1u;
+      tc_fence_after();
+      const bool row_ok = n < a.w.rows;
+      for (int c0 = g * 32; c0 < n_tok; c0 += 64) {
+        uint32_t v[32];
+        tmem_ld32(t_lane + (uint32_t)c0, v);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (W13 && a.act == NF4MOE_ACT_SWIGLU_OAI) {
+          __half* h = reinterpret_cast<__half*>(a.out);
+          const int I = a.w.rows >> 1;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float mine = __half2float(__float2half_rn(__uint_as_float(v[i])));  // fp16 storage of the product
+            const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
+            if ((i & 1) == (lane & 1) && row_ok && c0 + i < n_tok) {
+              const float res = (lane & 1) ? swiglu_oai(other, mine) : swiglu_oai(mine, other);
+              h[(long long)(row0 + c0 + i) * I + (n >> 1)] = __float2half_rn(res);
+            }
+          }
+        } else if (W13) {
+          __half* raw = reinterpret_cast<__half*>(a.out);
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (row_ok && c0 + i < n_tok) raw[(long long)(row0 + c0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
+        } else {
+          __half* y = reinterpret_cast<__half*>(a.out);
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (row_ok && c0 + i < n_tok)
+              y[(long long)__ldg(a.sorted_pairs + row0 + c0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(kBarDEmpty));
+    }
+  }
+
+  // ---- teardown ----
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+        qr == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 2-D row-major tensor [rows, inner] of `elt`-byte elements, box [box_rows, box_inner], 128B swizzle, OOB reads as zero
+inline bool make_map_2d(CUtensorMap* m, const void* ptr, CUtensorMapDataType dt, int elt, uint64_t inner, uint64_t rows,
+                        uint32_t box_inner, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return false;
+  const cuuint64_t dims[2] = {inner, rows};
+  const cuuint64_t strides[1] = {inner * (uint64_t)elt};
+  const cuuint32_t box[2] = {box_inner, box_rows};
+  const cuuint32_t es[2] = {1, 1};
+  return fn(m, dt, 2, const_cast<void*>(ptr), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+inline int gemm_tile_tokens(int T, int k, int E) {
+  // small batches: 32-token tiles keep the activation stages at 4 KB; otherwise the full 256-column accumulator
+  return ((long long)T * k <= 32ll * E) ? 32 : kGemmTokTile;
+}
+
+template <bool W13>
+int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
+                const int32_t* tile_list, int T, int k, int E, int act, void* out, void* stream, char* err, size_t err_len,
+                int* launches) {
+  const char* name = W13 ? "gemm_w13" : "gemm_w2";
+  auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
+  if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
+  if (!W13 && !sorted_pairs) return fail(NF4MOE_EINVAL, "sorted_pairs required");
+  if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "cols must be a multiple of 64");
+  if (W13 && (w->rows & 1)) return fail(NF4MOE_EINVAL, "w13 rows must be even");
+  if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "absmax missing");
+  if ((reinterpret_cast<uintptr_t>(act_in) & 15u) || (reinterpret_cast<uintptr_t>(w->packed) & 15u))
+    return fail(NF4MOE_EALIGN, "activations and packed weights must be 16-byte aligned");
+  if (W13 && act != NF4MOE_ACT_SWIGLU_OAI && act != NF4MOE_ACT_CHUNK_SILU) return fail(NF4MOE_EINVAL, "bad activation");
+  if (T == 0) return 0;
+  int dev = 0, sms = 0, cc = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&cc, cudaDevAttrComputeCapabilityMajor, dev);
+  if (cc != 10) return fail(NF4MOE_EARCH, "needs an sm_100 device");
+  GemmArgs a;
+  a.w = make_qw(*w);
+  a.out = out;
+  a.sorted_pairs = sorted_pairs;
+  a.meta = meta;
+  a.tile_list = tile_list;
+  a.act = act;
+  a.box_tokens = gemm_tile_tokens(T, k, E);
+  CUtensorMap map_w, map_x;
+  if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
+    return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
+  if (!make_map_2d(&map_x, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, (uint32_t)a.box_tokens))
+    return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
+  static thread_local bool attr_set = false;
+  auto kern = gemm_kernel<W13>;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
+    if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
+    attr_set = true;
+  }
+  kern<<<sms, kGemmThreads, kGemmSmemBytes, (cudaStream_t)stream>>>(a, map_w, map_x);
+  ++*launches;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }
+  return 0;
+}
+
+inline int gemm_w13_entry(const void* x_sorted, const nf4moe_qweight* w13, const int32_t*, const int32_t* meta,
+                          const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted, void* stream, char* err,
+                          size_t err_len, int* launches) {
+  return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, h_sorted, stream, err, err_len, launches);
+}
+inline int gemm_w2_entry(const void* h_sorted, const nf4moe_qweight* w2, const int32_t*, const int32_t* sorted_pairs,
+                         const int32_t* meta, const int32_t* tile_list, int T, int k, int E, void* y, void* stream, char* err,
+                         size_t err_len, int* launches) {
+  return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, y, stream, err, err_len, launches);
 }
 
 }  // namespace nf4moe

@@ -80,7 +80,7 @@ __device__ __forceinline__ void block_step(const uint2 w0, const uint2 w1, const
 // NKB_T : compile-time K/64 (45 for gpt-oss: every bound and offset becomes an immediate) or 0 for a runtime K.
 template <int NT, int KBW, bool W13, bool NESTED, int NKB_T>
 __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a) {
-  extern __shared__ __align__(128) uint8_t dyn_smem[];
+  extern __shared__ __align__(1024) uint8_t dyn_smem[];
   constexpr int TW = 45 / KBW;                 // warps per team
   constexpr int NTEAMS = kGemvConsumers / TW;  // teams per CTA
   constexpr int NRED = 4 * NT;                 // reducer warps per item (one table hole each)

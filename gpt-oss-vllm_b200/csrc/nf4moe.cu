@@ -86,7 +86,7 @@ Workspace carve(void* base, int T, int E, int H, int I, int k) {
   char* p = reinterpret_cast<char*>(base);
   size_t off = 0;
   const size_t n = (size_t)T * k;
-  const size_t n_pad = align_up(n, 128) + 128;
+  const size_t n_pad = align_up(n, 256) + 256;
   auto take = [&](size_t bytes) {
     char* r = p ? p + off : nullptr;
     off += align_up(bytes, 256);
@@ -98,7 +98,7 @@ Workspace carve(void* base, int T, int E, int H, int I, int k) {
   w.sorted = (int32_t*)take(n_pad * 4);
   w.active = (int32_t*)take((size_t)E * 4);
   w.meta = (int32_t*)take(64);
-  w.tiles = (int32_t*)take((n / 128 + E + 2) * 8);
+  w.tiles = (int32_t*)take((n / 16 + E + 2) * 16);
   w.h = (__half*)take(n_pad * I * 2);
   w.raw = (__half*)take(n_pad * 2 * I * 2);
   w.xs = (__half*)take(n_pad * H * 2);
@@ -250,9 +250,12 @@ int nf4moe_route_topk(const void* logits, int dtype, int T, int E, int k, int32_
 }
 
 int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* sorted_pairs,
-                  int32_t* active_experts, int32_t* meta, int32_t* tile_list, void* stream) {
+                  int32_t* active_experts, int32_t* meta, int32_t* tile_list, int tile_rows, void* stream) {
   if (!ids || !expert_offsets || !sorted_pairs || !active_experts || !meta || T < 0 || k <= 0 || E <= 0 || E > 255)
     return fail(NF4MOE_EINVAL, "bucket: bad arguments (E must be <= 255)");
+  if (tile_rows == 0) tile_rows = gemm_tile_tokens(T, k, E);
+  if (tile_rows < 16 || tile_rows > kGemmTokTile || tile_rows % 16)
+    return fail(NF4MOE_EINVAL, "bucket: tile_rows must be a multiple of 16 in 16..256 (or 0 = automatic)");
   const long long n = (long long)T * k;
   const size_t smem = (size_t)((n + 31) & ~31ll);
   if (smem > 200 * 1024) return fail(NF4MOE_EINVAL, "bucket: T*k = %lld exceeds the single-CTA limit of 204800 pairs", n);
@@ -263,7 +266,7 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
     attr_set = true;
   }
   bucket_kernel<<<1, kBucketThreads, smem, (cudaStream_t)stream>>>(ids, (int)n, E, expert_offsets, sorted_pairs,
-                                                                  active_experts, meta, tile_list);
+                                                                  active_experts, meta, tile_list, tile_rows);
   CHECK_LAUNCH("bucket_kernel");
   return 0;
 }
@@ -391,7 +394,7 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
   }
   if (regime == NF4MOE_REGIME_AUTO) regime = gemm_available() && T > kGemmAutoThreshold ? NF4MOE_REGIME_GEMM : NF4MOE_REGIME_GEMV;
   const bool gemm = regime == NF4MOE_REGIME_GEMM;
-  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, stream)) return rc;
+  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, 0, stream)) return rc;
   launches += g_launches; g_launches = 0;
   __half* h_dst = act == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
   if (gemm) {

@@ -70,14 +70,13 @@ __global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict_
 // P/unsloth_to_vllm_converter.py:298-305.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kBucketThreads = 1024;
-constexpr int kTileRows = 128;  // M tile of the grouped GEMM
 
 __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* __restrict__ ids, int n_pairs, int E,
                                                                 int32_t* __restrict__ expert_offsets,
                                                                 int32_t* __restrict__ sorted_pairs,
                                                                 int32_t* __restrict__ active_experts,
                                                                 int32_t* __restrict__ meta,
-                                                                int32_t* __restrict__ tile_list) {
+                                                                int32_t* __restrict__ tile_list, int tile_rows) {
   extern __shared__ uint8_t s_ids[];  // n_pairs rounded up to 32
   __shared__ int s_count[256];
   __shared__ int s_off[257];
@@ -119,10 +118,16 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
       if (c > 0) {
         active_experts[na++] = e;
         mx = max(mx, c);
+        // token tiles of the grouped GEMM: an expert's rows split into ceil(c / tile_rows) near-equal tiles (multiples of 16)
+        const int ntl = (c + tile_rows - 1) / tile_rows;
+        const int sz = (((c + ntl - 1) / ntl) + 15) & ~15;
         if (tile_list)
-          for (int r = 0; r < c; r += kTileRows) { tile_list[2 * nt] = e; tile_list[2 * nt + 1] = s_off[e] + r; ++nt; }
+          for (int r = 0; r < c; r += sz) {
+            tile_list[4 * nt] = e; tile_list[4 * nt + 1] = s_off[e] + r; tile_list[4 * nt + 2] = min(sz, c - r); tile_list[4 * nt + 3] = 0;
+            ++nt;
+          }
         else
-          nt += (c + kTileRows - 1) / kTileRows;
+          nt += (c + sz - 1) / sz;
       }
     }
     for (int i = na; i < E; ++i) active_experts[i] = -1;

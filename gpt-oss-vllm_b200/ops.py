@@ -43,7 +43,7 @@ def route_topk(logits: torch.Tensor, k: int) -> tuple[torch.Tensor, torch.Tensor
     return ids, w
 
 
-def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True) -> dict[str, torch.Tensor]:
+def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True, tile_rows: int = 0) -> dict[str, torch.Tensor]:
     """Stable counting sort of the (token,slot) pairs by expert -> offsets / sorted_pairs / active / meta / tiles."""
     _require_cuda(ids, "topk_ids")
     T, k = ids.shape
@@ -51,22 +51,22 @@ def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True) -> dict[str, torc
     n = T * k
     out = {
         "expert_offsets": torch.empty(E + 1, dtype=torch.int32, device=dev),
-        "sorted_pairs": torch.full(((n + 127) // 128 * 128 + 128,), -1, dtype=torch.int32, device=dev),
+        "sorted_pairs": torch.full(((n + 255) // 256 * 256 + 256,), -1, dtype=torch.int32, device=dev),
         "active_experts": torch.empty(E, dtype=torch.int32, device=dev),
         "meta": torch.zeros(16, dtype=torch.int32, device=dev),
-        "tile_list": torch.full((2 * (n // 128 + E + 2),), -1, dtype=torch.int32, device=dev) if want_tiles else None,
+        "tile_list": torch.full((4 * (n // 16 + E + 2),), -1, dtype=torch.int32, device=dev) if want_tiles else None,
     }
     with torch.cuda.device(dev):
         _lib.check(_lib.load_library().nf4moe_bucket(
             ids.data_ptr(), T, k, E, out["expert_offsets"].data_ptr(), out["sorted_pairs"].data_ptr(),
             out["active_experts"].data_ptr(), out["meta"].data_ptr(),
-            out["tile_list"].data_ptr() if want_tiles else None, _stream_ptr(dev)))
+            out["tile_list"].data_ptr() if want_tiles else None, tile_rows, _stream_ptr(dev)))
     return out
 
 
 def permute_rows(x: torch.Tensor, b: dict, k: int) -> torch.Tensor:
     T, H = x.shape
-    xs = torch.empty((T * k + 127) // 128 * 128 + 128, H, dtype=torch.float16, device=x.device)
+    xs = torch.empty((T * k + 255) // 256 * 256 + 256, H, dtype=torch.float16, device=x.device)
     with torch.cuda.device(x.device):
         _lib.check(_lib.load_library().nf4moe_permute_rows(x.data_ptr(), b["sorted_pairs"].data_ptr(), b["meta"].data_ptr(),
                                                            T, k, H, xs.data_ptr(), _stream_ptr(x.device)))
@@ -90,7 +90,7 @@ def expert_w13(x: torch.Tensor, w13: NF4ExpertWeights, b: dict, T: int, k: int, 
     lib = _lib.load_library()
     E = w13.num_experts
     width = w13.rows // 2 if act == _lib.ACT_SWIGLU_OAI else w13.rows
-    h = torch.zeros((T * k + 127) // 128 * 128 + 128, width, dtype=torch.float16, device=x.device)
+    h = torch.zeros((T * k + 255) // 256 * 256 + 256, width, dtype=torch.float16, device=x.device)
     q = w13.c_struct(nested)
     with torch.cuda.device(x.device):
         if regime == _lib.REGIME_GEMM:

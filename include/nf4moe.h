@@ -111,10 +111,13 @@ int nf4moe_route_topk(const void* logits, int logits_dtype, int T, int E, int k,
  *   expert_offsets[E+1]  exclusive prefix of per-expert pair counts
  *   sorted_pairs[T*k]    pair index t*k+slot, grouped by expert, ascending within an expert
  *   active_experts[E]    experts with >=1 pair, ascending;  meta[0] = how many, meta[1] = total kept pairs,
- *                        meta[2] = number of (expert, 128-row tile) entries, meta[3] = largest per-expert count
- *   tile_list[2*(ceil(T*k/128)+E)]  (expert, first sorted row) per 128-row tile of the grouped GEMM */
+ *                        meta[2] = number of token tiles, meta[3] = largest per-expert count
+ *   tile_list[4*(T*k/16+E+2)]  (expert, first sorted row, rows, 0) per token tile of the grouped GEMM: an expert with c
+ *                        rows gets ceil(c/tile_rows) near-equal tiles, each a multiple of 16 rows except the last.
+ *                        tile_rows: multiple of 16 in 16..256, or 0 = what nf4moe_gemm_* expect for this (T, k, E).
+ *                        tile_list may be NULL (decode regime). */
 int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offsets, int32_t* sorted_pairs,
-                  int32_t* active_experts, int32_t* meta, int32_t* tile_list, void* stream);
+                  int32_t* active_experts, int32_t* meta, int32_t* tile_list, int tile_rows, void* stream);
 
 /* x_sorted[s, :] = x[sorted_pairs[s] / k, :]  (fp16, H % 8 == 0); rows s >= meta[1] are zero-filled. */
 int nf4moe_permute_rows(const void* x, const int32_t* sorted_pairs, const int32_t* meta, int T, int k, int H,
@@ -138,8 +141,10 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
                    const int32_t* sorted_pairs, const int32_t* active_experts, const int32_t* meta, int T, int k, int E,
                    void* y, void* stream);
 
-/* Prefill regime: the same two products as tcgen05 grouped GEMMs over 128-row tiles of x_sorted (from
- * nf4moe_permute_rows), NF4 tiles dequantised into shared memory, accumulators in TMEM. */
+/* Prefill regime: the same two products as tcgen05 grouped GEMMs.  Weight rows are the MMA M dimension (128 per tile),
+ * the token tiles of `tile_list` (built by nf4moe_bucket with tile_rows = 0) the N dimension; NF4 blocks are dequantised
+ * bit-exactly (fp32 multiply, one rounding to fp16) straight into TENSOR MEMORY as the A operand, activations arrive by
+ * TMA, accumulators live in TMEM.  x_sorted / h_sorted: fp16 [>= T*k rows, cols], rows grouped by expert. */
 int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
                            const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted,
                            void* stream);

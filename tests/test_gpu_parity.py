@@ -144,9 +144,15 @@ def test_bucket_stable_sort(pkg, cuda_device, T, k, E):
     active = np.nonzero(counts)[0]
     assert meta[0] == active.size and meta[1] == keep.sum() and meta[3] == counts.max()
     assert np.array_equal(b["active_experts"].cpu().numpy()[:active.size], active)
-    tiles = b["tile_list"].cpu().numpy()[:2 * meta[2]].reshape(-1, 2)
-    exp_tiles = [(e, off[e] + r) for e in active for r in range(0, counts[e], 128)]
-    assert tiles.tolist() == [list(t) for t in exp_tiles]
+    tile_rows = 32 if T * k <= 32 * E else 256            # what the grouped GEMM expects for this (T, k, E)
+    tiles = b["tile_list"].cpu().numpy()[:4 * meta[2]].reshape(-1, 4)
+    exp_tiles = []
+    for e in active:
+        c = int(counts[e])
+        ntl = -(-c // tile_rows)
+        sz = (-(-c // ntl) + 15) // 16 * 16
+        exp_tiles += [[e, off[e] + r, min(sz, c - r), 0] for r in range(0, c, sz)]
+    assert tiles.tolist() == exp_tiles
 
 
 def test_permute_and_combine(pkg, cuda_device):
@@ -389,3 +395,76 @@ def test_errors_are_loud(pkg, cuda_device):
                             router_logits=torch.zeros(4, 8, dtype=torch.float16, device=cuda_device))
     with pytest.raises(pkg.Nf4MoeError):       # more experts than the router kernel supports
         pkg.ops.route_topk(torch.zeros(4, 300, dtype=torch.float16, device=cuda_device), 4)
+
+
+# ------------------------------------------------------------------------------------------------- prefill regime (tcgen05)
+def _gemm_stage_check(pkg, dev, T, E, H, I, k, nested, seed):
+    st13, st2, w13, w2 = make_layer(pkg, dev, seed, E, H, I)
+    rng = np.random.default_rng(200 + T)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    ids = np.stack([rng.choice(E, size=k, replace=False) for _ in range(T)]).astype(np.int32)
+    b = pkg.ops.bucket(torch.from_numpy(ids).to(dev), E)
+    xd = torch.from_numpy(x).to(dev)
+    xs = pkg.ops.permute_rows(xd, b, k)
+    h = pkg.ops.expert_w13(xs, w13, b, T, k, nested=nested, regime=pkg.REGIME_GEMM)
+    y = pkg.ops.expert_w2(h, w2, b, T, k, nested=nested, regime=pkg.REGIME_GEMM).cpu().numpy()
+    h = h.cpu().numpy()
+    sp = b["sorted_pairs"].cpu().numpy()[:T * k]
+    off = b["expert_offsets"].cpu().numpy()
+    d13 = np.stack([orc.dequant_state(s) for s in st13])
+    d2 = np.stack([orc.dequant_state(s) for s in st2])
+    for e in range(E):
+        rows = sp[off[e]:off[e + 1]]
+        if rows.size == 0:
+            continue
+        xe = x[rows // k]
+        h_ref = orc.swiglu_oai(orc._mm_f16_f32acc(xe, d13[e]).astype(np.float16).astype(np.float32)).astype(np.float16)
+        assert_moe_close(h[off[e]:off[e + 1]], h_ref)
+        y_ref = orc._mm_f16_f32acc(h[off[e]:off[e + 1]], d2[e]).astype(np.float16)
+        assert_moe_close(y[rows], y_ref)
+
+
+@pytest.mark.parametrize("T,E,H,I,k", [(3, 8, 64, 64, 2), (40, 8, 256, 192, 4), (300, 8, 256, 192, 4), (700, 4, 192, 320, 2),
+                                       (1100, 4, 128, 64, 1)])
+@pytest.mark.parametrize("nested", [False, True])
+def test_gemm_stages_vs_oracle(pkg, cuda_device, T, E, H, I, k, nested):
+    """tcgen05 grouped GEMMs (w13+SwiGLU, w2) against the oracle's per-expert fp16 matmul: ragged token tiles, row tiles
+    that end inside the next expert (rows % 128 != 0), K tails that are not a multiple of the 4-block raw stage."""
+    _gemm_stage_check(pkg, cuda_device, T, E, H, I, k, nested, 51)
+
+
+@pytest.mark.parametrize("T,E,H,I,k", [(65, 32, 128, 128, 4), (333, 8, 192, 128, 4), (1024, 32, 256, 128, 4)])
+def test_moe_forward_gemm_regime_vs_oracle(pkg, cuda_device, T, E, H, I, k):
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 53, E, H, I)
+    rng = np.random.default_rng(T)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    xd, lgd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(lg).to(cuda_device)
+    out = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_GEMM)
+    ref = orc.moe_forward_from_states(x, lg, st13, st2, k=k)
+    assert_moe_close(out.cpu().numpy(), ref)
+    out_n = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_GEMM, nested=True)
+    assert torch.equal(out, out_n)
+    # the two regimes differ only in fp32 summation order
+    out_v = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_GEMV)
+    assert_moe_close(out.cpu().numpy(), out_v.cpu().numpy())
+    out_a = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_AUTO)
+    assert torch.equal(out_a, out)
+
+
+def test_gemm_operand_is_bit_exact_dequant(pkg, cuda_device):
+    """With one-hot activations the grouped GEMM returns the dequantised weight columns themselves: the A operand the
+    tensor cores see must be bit-identical to bnb's dequantize_4bit (fp32 multiply, one rounding)."""
+    E, H, I, k = 2, 128, 64, 1
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 57, E, H, I)
+    T = H
+    x = np.eye(H, dtype=np.float16)
+    ids = np.zeros((T, 1), dtype=np.int32)
+    ids[T // 2:] = 1
+    b = pkg.ops.bucket(torch.from_numpy(ids).to(cuda_device), E)
+    xs = pkg.ops.permute_rows(torch.from_numpy(x).to(cuda_device), b, k)
+    raw = pkg.ops.expert_w13(xs, w13, b, T, k, act=pkg.ACT_CHUNK_SILU, regime=pkg.REGIME_GEMM).cpu().numpy()[:T]
+    d13 = np.stack([orc.dequant_state(s) for s in st13])      # [E, 2I, H]
+    for t in range(T):
+        e = 0 if t < T // 2 else 1
+        assert np.array_equal(raw[t].view(np.uint16), d13[e][:, t].view(np.uint16))
