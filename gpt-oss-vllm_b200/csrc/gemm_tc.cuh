@@ -1,7 +1,7 @@
 // Prefill-regime grouped GEMM on the 5th-generation tensor cores (tcgen05 + TMEM), NF4 weights dequantised on the fly.
 //
 //   D[n, m] = sum_k W_e[n, k] * X[m, k]      n: 128 weight rows of expert e (MMA M, one TMEM lane each)
-//                                             m: up to 256 routed tokens of expert e (MMA N, one TMEM column each)
+//                                             m: up to 192 routed tokens of expert e (MMA N, one TMEM column each)
 //
 // The WEIGHTS are the A operand and live in TENSOR MEMORY: a dequant thread owns one weight row, so the fp32 absmax of
 // a 64-wide NF4 block is a per-thread scalar, the 32 packed bytes of the block are two LDS.128, every byte is decoded
@@ -9,14 +9,18 @@
 // to fp16 -- bit-identical to bitsandbytes' dequantize_4bit, so the tensor cores see exactly the fp16 matrix the
 // reference multiplies with -- and the 32 packed half2 go to TMEM with one tcgen05.st.32x32b.x32.  The ACTIVATIONS are
 // the B operand, loaded by TMA (128B swizzle, K-major) straight into the canonical UMMA layout.  Each dequantised
-// weight therefore feeds up to 256 tokens, half the dequant work of the usual "tokens = M" arrangement, and no
+// weight therefore feeds up to 192 tokens, 1.5x fewer dequants than the usual "tokens = M = 128" arrangement, and no
 // dequantised weight ever touches shared or global memory.
 //
-// Roles (384 threads, one persistent CTA per SM):
-//   warp 0      TMA producer: raw NF4 tiles [128 rows x 128 B] every 4th k-block + activation tiles [<=256 x 64] per k-block
-//   warp 1      TMEM allocator and the single MMA-issuing thread (tcgen05.mma kind::f16, A in TMEM, B in smem)
-//   warps 4-11  dequant (two groups of four warps, alternate k-blocks), then the epilogue: tcgen05.ld, gpt-oss clamped
-//               SwiGLU on adjacent lanes (rows 2j / 2j+1 = gate / up) for w13, scatter to (token, slot) order for w2
+// Roles (512 threads, one persistent CTA per SM, registers re-balanced per warpgroup with setmaxnreg):
+//   warp 0       TMA producer: activation tiles [<=192 tokens x 64] per k-block, as 32-row boxes matching the ragged tile
+//   warp 1       TMEM allocator and the single MMA-issuing thread (tcgen05.mma kind::f16, A in TMEM, B in smem)
+//   warp 2       TMA producer: the tile's absmax (one bulk copy per tile, double-buffered) and raw NF4 tiles [128 rows x 128 B]
+//                per 4 k-blocks, on their own rings so they run ahead of the MMA
+//   warps 4-11   dequant: two groups of four warps (one lane quarter each) on alternate k-blocks
+//   warps 12-15  epilogue: tcgen05.ld of one of the TWO accumulators while the next tile's main loop fills the other;
+//                gpt-oss clamped SwiGLU on adjacent lanes (rows 2j / 2j+1 = gate / up) for w13, scatter to (token, slot)
+//                order for w2
 // Replaces vLLM's dequantise-everything + Triton fused_experts (V/.../quantization/bitsandbytes.py:478-506, 588-603).
 #pragma once
 #include <cuda.h>
@@ -28,16 +32,17 @@
 namespace nf4moe {
 
 constexpr int kGemmAutoThreshold = 64;  // tokens; above this nf4moe_moe_forward(AUTO) uses the tcgen05 path
-constexpr int kGemmThreads = 384;
-constexpr int kGemmTokTile = 256;       // max MMA N
+constexpr int kGemmThreads = 512;
+constexpr int kGemmTokTile = 192;       // max MMA N: two accumulators of 192 columns + four A stages fill the 512 TMEM columns
 constexpr int kGemmRowTile = 128;       // MMA M
+constexpr int kGemmBoxRows = 32;        // token rows per activation TMA box (a tile is ceil(rows/32) boxes)
 constexpr int kAStages = 4;             // A (dequantised weights) stages in TMEM, 32 columns each
 constexpr int kMaxBStages = 6;
 constexpr int kMaxWStages = 3;
 constexpr uint32_t kWStageBytes = 128 * 128;   // raw NF4: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kGemmSmemBytes = 232448 - 1024;  // dynamic part; the kernel's static __shared__ control block takes the rest
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kTmemACol = 256;     // D occupies columns [0,256), A stages [256, 256 + 4*32)
+constexpr uint32_t kTmemACol = 2 * kGemmTokTile;   // accumulators at columns 0 and 192, A stages at [384, 384 + 4*32)
 
 inline bool gemm_available() { return true; }
 
@@ -101,7 +106,7 @@ struct GemmArgs {
   const int32_t* meta;            // meta[2] = number of token tiles
   const int32_t* tile_list;       // (expert, first sorted row, rows, -) per token tile
   int act;
-  int box_tokens;                 // rows of the activation TMA box (256, or 32 for small batches)
+  int tile_tokens;                // largest token tile (256, or 32 for small batches): sizes the activation stages
 };
 
 // instruction descriptor: D f32, A/B f16, both K-major, M = 128, N = n
@@ -116,7 +121,13 @@ __device__ __forceinline__ uint64_t make_bdesc(uint32_t smem_addr) {
 // barrier slots inside s_bar[]
 constexpr int kBarWFull = 0, kBarWEmpty = kBarWFull + kMaxWStages, kBarBFull = kBarWEmpty + kMaxWStages,
               kBarBEmpty = kBarBFull + kMaxBStages, kBarAFull = kBarBEmpty + kMaxBStages, kBarAEmpty = kBarAFull + kAStages,
-              kBarDFull = kBarAEmpty + kAStages, kBarDEmpty = kBarDFull + 1, kNumGemmBars = kBarDEmpty + 1;
+              kBarDFull = kBarAEmpty + kAStages, kBarDEmpty = kBarDFull + 2, kBarMFull = kBarDEmpty + 2,
+              kBarMEmpty = kBarMFull + 2, kNumGemmBars = kBarMEmpty + 2;
+
+template <int N>
+__device__ __forceinline__ void set_max_regs_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void set_max_regs_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
 template <bool W13>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a, const __grid_constant__ CUtensorMap map_w,
@@ -124,11 +135,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumGemmBars];
   __shared__ uint32_t s_tmem;
-  __shared__ uint32_t s_wst[kMaxWStages], s_bst[kMaxBStages];
+  __shared__ uint32_t s_wst[kMaxWStages], s_bst[kMaxBStages], s_mst[2];
   __shared__ int s_nw, s_nb;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nkb = a.w.nkb;
-  const uint32_t b_bytes = (uint32_t)a.box_tokens * 128u;
+  const bool nested = a.w.absmax_f32 == nullptr;
+  const uint32_t b_bytes = (uint32_t)a.tile_tokens * 128u;
+  // absmax stage: the tile's [128 rows x nkb] absmax (fp32, or u8 + the expert's 1 KB code2 table when nested)
+  const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
+  const uint32_t m_code2 = (m_tile + 15u) & ~15u;            // offset of code2 inside the stage
+  const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
   const uint32_t base = smem_u32(dyn_smem);
   const uint32_t lut = pin((base + 65535u) & ~65535u);   // 64 KB aligned: PRMT drops the byte into address bits 8..15
   const uint32_t bar0 = smem_u32(s_bar);
@@ -136,35 +152,41 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
 
   // ---- one-time setup ----
   if (tid == 0) {
-    // carve [base, lut) and [lut + 64K, end) into 1024-aligned stages: as many activation stages as fit with >= 2 raw-weight stages
+    // carve [base, lut) and [lut + 64K, end) into 1024-aligned stages: two absmax stages, >= 2 raw-weight stages and as
+    // many activation stages as still fit
     const uint32_t lo[2] = {(base + 1023u) & ~1023u, lut + 65536u}, hi[2] = {lut, base + kGemmSmemBytes};
-    int best_b = -1, best_w = 0, pick[2] = {0, 0};
-    for (int n0 = 0; n0 <= kMaxBStages; ++n0)
-      for (int n1 = 0; n0 + n1 <= kMaxBStages; ++n1) {
-        int nw = 0;
-        bool ok = true;
-        const int nbr[2] = {n0, n1};
-        for (int r = 0; r < 2; ++r) {
-          const long long room = (long long)hi[r] - (long long)lo[r] - (long long)nbr[r] * b_bytes;
-          if (room < 0) ok = false; else nw += (int)(room / kWStageBytes);
+    int best_b = -1, best_w = 0, pick[2] = {0, 0}, pick_m[2] = {0, 0};
+    for (int m0 = 0; m0 <= 2; ++m0)
+      for (int n0 = 0; n0 <= kMaxBStages; ++n0)
+        for (int n1 = 0; n0 + n1 <= kMaxBStages; ++n1) {
+          int nw = 0;
+          bool ok = true;
+          const int nbr[2] = {n0, n1}, nmr[2] = {m0, 2 - m0};
+          for (int r = 0; r < 2; ++r) {
+            const long long room = (long long)hi[r] - (long long)lo[r] - (long long)nbr[r] * b_bytes - (long long)nmr[r] * m_bytes;
+            if (room < 0) ok = false; else nw += (int)(room / kWStageBytes);
+          }
+          if (!ok || nw < 2) continue;
+          nw = min(nw, kMaxWStages);
+          if (n0 + n1 > best_b || (n0 + n1 == best_b && nw > best_w)) {
+            best_b = n0 + n1; best_w = nw; pick[0] = n0; pick[1] = n1; pick_m[0] = m0; pick_m[1] = 2 - m0;
+          }
         }
-        if (!ok || nw < 2) continue;
-        nw = min(nw, kMaxWStages);
-        if (n0 + n1 > best_b || (n0 + n1 == best_b && nw > best_w)) { best_b = n0 + n1; best_w = nw; pick[0] = n0; pick[1] = n1; }
-      }
-    int ib = 0, iw = 0;
+    int ib = 0, iw = 0, im = 0;
     for (int r = 0; r < 2; ++r) {
       uint32_t cur = lo[r];
       for (int i = 0; i < pick[r]; ++i) { s_bst[ib++] = cur; cur += b_bytes; }
-      cur = (cur + 1023u) & ~1023u;
+      for (int i = 0; i < pick_m[r]; ++i) { s_mst[im++] = cur; cur += m_bytes; }
       while (iw < best_w && cur + kWStageBytes <= hi[r]) { s_wst[iw++] = cur; cur += kWStageBytes; }
     }
     s_nb = ib; s_nw = iw;
     for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 8); }
     for (int i = 0; i < kMaxBStages; ++i) { mbar_init(bar(kBarBFull + i), 1); mbar_init(bar(kBarBEmpty + i), 1); }
     for (int i = 0; i < kAStages; ++i) { mbar_init(bar(kBarAFull + i), 4); mbar_init(bar(kBarAEmpty + i), 1); }
-    mbar_init(bar(kBarDFull), 1);
-    mbar_init(bar(kBarDEmpty), 8);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(kBarDFull + i), 1); mbar_init(bar(kBarDEmpty + i), 4);
+      mbar_init(bar(kBarMFull + i), 1); mbar_init(bar(kBarMEmpty + i), 8);
+    }
     fence_barrier_init();
   }
   for (int i = tid; i < 256 * 32; i += kGemmThreads) {
@@ -184,42 +206,68 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   const int n_bst = s_nb, n_wst = s_nw;
 
   const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
-  const int n_items = a.meta[2] * n_row_tiles;
+  const int n_items = n_bst > 0 ? a.meta[2] * n_row_tiles : 0;   // (n_bst == 0: K too large for the stage budget; host rejects it)
 
-  if (warp == 0) {
-    // =============================== TMA producer ===============================
-    if (lane == 0) {
-      int sb = 0, sw = 0;
-      uint32_t phb = 0, phw = 0;
+  if (warp < 4) {
+    set_max_regs_dec<56>();
+    if (warp == 0 && lane == 0) {
+      // =============================== TMA producer: activation tiles, one stage per k-block ===============================
+      int sb = 0;
+      uint32_t phb = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-        const int e = a.tile_list[4 * tile], row0 = a.tile_list[4 * tile + 1];
-        const int wrow = e * a.w.rows + rt * kGemmRowTile;
+        const int tile = item / n_row_tiles;
+        const int row0 = a.tile_list[4 * tile + 1], n_box = (a.tile_list[4 * tile + 2] + kGemmBoxRows - 1) / kGemmBoxRows;
         for (int kb = 0; kb < nkb; ++kb) {
-          if ((kb & 3) == 0) {
-            mbar_wait(bar(kBarWEmpty + sw), phw ^ 1u);
-            mbar_expect_tx(bar(kBarWFull + sw), kWStageBytes);
-            tma_load_2d(s_wst[sw], &map_w, kb * 32, wrow, bar(kBarWFull + sw));
-            if (++sw == n_wst) { sw = 0; phw ^= 1u; }
-          }
           mbar_wait(bar(kBarBEmpty + sb), phb ^ 1u);
-          mbar_expect_tx(bar(kBarBFull + sb), b_bytes);
-          tma_load_2d(s_bst[sb], &map_x, kb * kBlock, row0, bar(kBarBFull + sb));
+          mbar_expect_tx(bar(kBarBFull + sb), (uint32_t)n_box * (kGemmBoxRows * 128u));
+          const uint32_t dst = s_bst[sb];
+          for (int bx = 0; bx < n_box; ++bx)   // only the 32-row boxes the tile really has: L2 -> SM traffic follows the ragged tile
+            tma_load_2d(dst + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, kb * kBlock, row0 + bx * kGemmBoxRows, bar(kBarBFull + sb));
           if (++sb == n_bst) { sb = 0; phb ^= 1u; }
         }
       }
-    }
-  } else if (warp == 1) {
-    // =============================== MMA issuer (one thread) ===============================
-    if (lane == 0) {
-      int sb = 0;
-      uint32_t phb = 0, pha = 0, phd = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    } else if (warp == 2 && lane == 0) {
+      // ============ TMA producer: the tile's absmax (one bulk copy per item, double-buffered) and the raw NF4 bytes, one
+      // stage per 4 k-blocks, on their own rings so they run ahead of the MMA ============
+      int sw = 0;
+      uint32_t phw = 0;
+      const uint64_t pol = l2_policy_evict_last();
+      const uint32_t am_elt = nested ? 1u : 4u;
+      const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
+      int it = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+        const int e = a.tile_list[4 * tile];
+        const int wrow = e * a.w.rows + rt * kGemmRowTile;
+        {
+          const int mb = it & 1;
+          const uint32_t mph = (uint32_t)(it >> 1) & 1u;
+          const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
+          const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
+          mbar_wait(bar(kBarMEmpty + mb), mph ^ 1u);
+          mbar_expect_tx(bar(kBarMFull + mb), bytes + (nested ? 1024u : 0u));
+          bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
+                   bar(kBarMFull + mb), pol);
+          if (nested) bulk_g2s(s_mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kBarMFull + mb), pol);
+        }
+        for (int kb = 0; kb < nkb; kb += 4) {
+          mbar_wait(bar(kBarWEmpty + sw), phw ^ 1u);
+          mbar_expect_tx(bar(kBarWFull + sw), kWStageBytes);
+          tma_load_2d(s_wst[sw], &map_w, kb * 32, wrow, bar(kBarWFull + sw));
+          if (++sw == n_wst) { sw = 0; phw ^= 1u; }
+        }
+      }
+    } else if (warp == 1 && lane == 0) {
+      // =============================== MMA issuer (one thread) ===============================
+      int sb = 0, it = 0;
+      uint32_t phb = 0, pha = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         const int tile = item / n_row_tiles;
         const int n_tok = a.tile_list[4 * tile + 2];
         const uint32_t idesc = make_idesc(max(16, (n_tok + 15) & ~15));
-        mbar_wait(bar(kBarDEmpty), phd ^ 1u);     // epilogue of the previous tile has drained the accumulator
-        phd ^= 1u;
+        const int db = it & 1;
+        const uint32_t d_t = tmem + (uint32_t)db * kGemmTokTile;
+        mbar_wait(bar(kBarDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
         tc_fence_after();
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = kb & 3;
@@ -230,42 +278,60 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           const uint32_t b_s = s_bst[sb];
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            tc_mma_ts(tmem, a_t + 8u * kk, make_bdesc(b_s + 32u * kk), idesc, (uint32_t)(kb | kk));
+            tc_mma_ts(d_t, a_t + 8u * kk, make_bdesc(b_s + 32u * kk), idesc, (uint32_t)(kb | kk));
           tc_commit(bar(kBarAEmpty + sa));
           tc_commit(bar(kBarBEmpty + sb));
-          if (kb == nkb - 1) tc_commit(bar(kBarDFull));
+          if (kb == nkb - 1) tc_commit(bar(kBarDFull + db));
           pha ^= 1u << sa;
           if (++sb == n_bst) { sb = 0; phb ^= 1u; }
         }
       }
     }
-  } else if (warp >= 4) {
-    // =============================== dequant + epilogue ===============================
+  }
+  else if (warp < 12) {
+    // =============================== dequant: NF4 -> fp16 A operand in TMEM ===============================
+    set_max_regs_inc<168>();
     const int q = warp & 3, g = (warp - 4) >> 2;
     const int r = q * 32 + lane;
     const uint32_t lut_lane = pin(lut | ((uint32_t)lane << 3));
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
     const uint32_t swz = (uint32_t)(r & 7);
-    int sw = 0;
-    uint32_t phw = 0, phd = 0, use0 = 0, use1 = 0;   // use counts of this group's two A stages (g and g+2)
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    int sw = 0, it = 0;
+    uint32_t phw = 0, use0 = 0, use1 = 0;   // use counts of this group's two A stages (g and g+2)
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-      const int e = a.tile_list[4 * tile], row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
+      const int e = a.tile_list[4 * tile];
       const int n = rt * kGemmRowTile + r;
-      const long long blk0 = (long long)min(n, a.w.rows - 1) * nkb;
+      const int mb = it & 1;
+      // nested absmax: code2[u8] * absmax2[blk >> 8] + offset; this row's 45 blocks touch at most two absmax2 entries
+      float a2_lo = 0.f, a2_hi = 0.f, off_e = 0.f;
+      long long blk_hi = 0;   // first block index that uses a2_hi
+      if (nested) {
+        const long long blk0 = (long long)min(n, a.w.rows - 1) * nkb;
+        const long long i2 = blk0 >> 8;
+        a2_lo = __ldg(a.w.absmax2 + (long long)e * a.w.n2 + i2);
+        a2_hi = __ldg(a.w.absmax2 + (long long)e * a.w.n2 + min(i2 + 1, a.w.n2 - 1));
+        off_e = __ldg(a.w.offset + e);
+        blk_hi = ((i2 + 1) << 8) - blk0;   // relative to this row's first block
+      }
+      mbar_wait(bar(kBarMFull + mb), (uint32_t)(it >> 1) & 1u);
+      const uint32_t m_st = pin(s_mst[mb]);
+      const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       for (int kb0 = 0; kb0 < nkb; kb0 += 4) {
-        float am[2];
-#pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
-          const int kb = kb0 + g + 2 * jj;
-          am[jj] = kb < nkb ? absmax_of(a.w, e, blk0 + kb) : 0.f;
-        }
         mbar_wait(bar(kBarWFull + sw), phw);
         const uint32_t wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
           const int j = g + 2 * jj;
-          if (kb0 + j < nkb) {
+          const int kb = kb0 + j;
+          if (kb < nkb) {
+            float am;
+            if (nested) {
+              const float c = lds_f32(m_st + m_code2 + 4u * lds_u8(m_row + (uint32_t)kb));
+              am = __fadd_rn(__fmul_rn(c, kb < blk_hi ? a2_lo : a2_hi), off_e);
+            } else {
+              am = lds_f32(m_row + 4u * (uint32_t)kb);
+            }
             const uint4 v0 = lds128(wrow + (((uint32_t)(2 * j) ^ swz) << 4));
             const uint4 v1 = lds128(wrow + (((uint32_t)(2 * j + 1) ^ swz) << 4));
             const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
@@ -275,7 +341,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 const float2 f = lds_f32x2(prmt(wd[wi], lut_lane, 0x7604u | ((uint32_t)i << 4)));
-                regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am[jj]), __fmul_rn(f.y, am[jj]));
+                regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am), __fmul_rn(f.y, am));
               }
             uint32_t& use = jj ? use1 : use0;
             mbar_wait(bar(kBarAEmpty + j), (use & 1u) ^ 1u);   // the MMAs that read this stage last time are done
@@ -292,14 +358,27 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
         if (lane == 0) mbar_arrive(bar(kBarWEmpty + sw));
         if (++sw == n_wst) { sw = 0; phw ^= 1u; }
       }
-      // ---- epilogue: this warp's lane quarter, alternate 32-column chunks per group ----
-      mbar_wait(bar(kBarDFull), phd);
-      phd ^= 1u;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(kBarMEmpty + mb));
+    }
+  } else {
+    // =============================== epilogue: TMEM -> registers -> global, overlapped with the next tile's main loop ======
+    set_max_regs_dec<112>();
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
+    int it = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+      const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
+      const int n = rt * kGemmRowTile + r;
+      const int db = it & 1;
+      mbar_wait(bar(kBarDFull + db), (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
       const bool row_ok = n < a.w.rows;
-      for (int c0 = g * 32; c0 < n_tok; c0 += 64) {
+      for (int c0 = 0; c0 < n_tok; c0 += 32) {
         uint32_t v[32];
-        tmem_ld32(t_lane + (uint32_t)c0, v);
+        tmem_ld32(t_lane + (uint32_t)(db * kGemmTokTile + c0), v);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         if (W13 && a.act == NF4MOE_ACT_SWIGLU_OAI) {
           __half* h = reinterpret_cast<__half*>(a.out);
@@ -328,7 +407,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar(kBarDEmpty));
+      if (lane == 0) mbar_arrive(bar(kBarDEmpty + db));
     }
   }
 
@@ -387,8 +466,11 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "cols must be a multiple of 64");
   if (W13 && (w->rows & 1)) return fail(NF4MOE_EINVAL, "w13 rows must be even");
   if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "absmax missing");
-  if ((reinterpret_cast<uintptr_t>(act_in) & 15u) || (reinterpret_cast<uintptr_t>(w->packed) & 15u))
-    return fail(NF4MOE_EALIGN, "activations and packed weights must be 16-byte aligned");
+  if (w->rows % 16 || w->cols > 4096) return fail(NF4MOE_EINVAL, "the tcgen05 regime needs rows % 16 == 0 and cols <= 4096");
+  if ((reinterpret_cast<uintptr_t>(act_in) & 15u) || (reinterpret_cast<uintptr_t>(w->packed) & 15u) ||
+      (reinterpret_cast<uintptr_t>(w->absmax_f32) & 15u) || (reinterpret_cast<uintptr_t>(w->absmax_u8) & 15u) ||
+      (!w->absmax_f32 && ((reinterpret_cast<uintptr_t>(w->code2) & 15u) || (w->code2_stride & 3))))
+    return fail(NF4MOE_EALIGN, "activations, packed weights, absmax and code2 must be 16-byte aligned");
   if (W13 && act != NF4MOE_ACT_SWIGLU_OAI && act != NF4MOE_ACT_CHUNK_SILU) return fail(NF4MOE_EINVAL, "bad activation");
   if (T == 0) return 0;
   int dev = 0, sms = 0, cc = 0;
@@ -403,11 +485,11 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.meta = meta;
   a.tile_list = tile_list;
   a.act = act;
-  a.box_tokens = gemm_tile_tokens(T, k, E);
+  a.tile_tokens = gemm_tile_tokens(T, k, E);
   CUtensorMap map_w, map_x;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
-  if (!make_map_2d(&map_x, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, (uint32_t)a.box_tokens))
+  if (!make_map_2d(&map_x, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, kGemmBoxRows))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
   static thread_local bool attr_set = false;
   auto kern = gemm_kernel<W13>;

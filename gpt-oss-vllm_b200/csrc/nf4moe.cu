@@ -254,7 +254,7 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
   if (!ids || !expert_offsets || !sorted_pairs || !active_experts || !meta || T < 0 || k <= 0 || E <= 0 || E > 255)
     return fail(NF4MOE_EINVAL, "bucket: bad arguments (E must be <= 255)");
   if (tile_rows == 0) tile_rows = gemm_tile_tokens(T, k, E);
-  if (tile_rows < 16 || tile_rows > kGemmTokTile || tile_rows % 16)
+  if (tile_rows < 16 || tile_rows > 256 || tile_rows % 16)
     return fail(NF4MOE_EINVAL, "bucket: tile_rows must be a multiple of 16 in 16..256 (or 0 = automatic)");
   const long long n = (long long)T * k;
   const size_t smem = (size_t)((n + 31) & ~31ll);
