@@ -37,10 +37,12 @@ constexpr int kGemmTokTile = 192;       // max MMA N: two accumulators of 192 co
 constexpr int kGemmRowTile = 128;       // MMA M
 constexpr int kGemmBoxRows = 32;        // token rows per activation TMA box (a tile is ceil(rows/32) boxes)
 constexpr int kAStages = 4;             // A (dequantised weights) stages in TMEM, 32 columns each
-constexpr int kMaxBStages = 6;
-constexpr int kMaxWStages = 3;
+constexpr int kMaxBStages = 4;          // activation stages: exactly kAStages, stage = k-block & 3
+constexpr int kGemmWPrefetch = 6;        // raw-weight stages requested into L2 ahead of the shared-memory ring
+constexpr int kMaxWStages = 4;
 constexpr uint32_t kWStageBytes = 128 * 128;   // raw NF4: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kGemmSmemBytes = 232448 - 1024;  // dynamic part; the kernel's static __shared__ control block takes the rest
+constexpr uint32_t kGemmLutBytes = 32768;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemACol = 2 * kGemmTokTile;   // accumulators at columns 0 and 192, A stages at [384, 384 + 4*32)
 
@@ -66,6 +68,18 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
       ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
+}
+// One lane of a CONVERGED warp.  The single-thread roles run their loops warp-uniformly and predicate only the
+// tcgen05 / TMA instruction on this: operands then stay in uniform registers (a `lane == 0` branch makes ptxas emit an
+// ELECT + R2UR waterfall loop around every UTCHMMA / UTMALDG, ~100 cycles each).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
@@ -106,6 +120,7 @@ struct GemmArgs {
   const int32_t* meta;            // meta[2] = number of token tiles
   const int32_t* tile_list;       // (expert, first sorted row, rows, -) per token tile
   int act;
+  long long* dbg;                 // optional [64] cycle counters written by CTA 0 (profiling builds of the caller only)
   int tile_tokens;                // largest token tile (256, or 32 for small batches): sizes the activation stages
 };
 
@@ -118,9 +133,19 @@ __device__ __forceinline__ uint64_t make_bdesc(uint32_t smem_addr) {
   return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 
+#define GEMM_DBG_T0() long long dbg_t = dbg_on ? clock64() : 0
+#define GEMM_DBG_ADD(slot)                                  \
+  do {                                                      \
+    if (dbg_on) {                                           \
+      const long long now__ = clock64();                    \
+      dbg_acc[slot] += now__ - dbg_t;                       \
+      dbg_t = now__;                                        \
+    }                                                       \
+  } while (0)
+
 // barrier slots inside s_bar[]
 constexpr int kBarWFull = 0, kBarWEmpty = kBarWFull + kMaxWStages, kBarBFull = kBarWEmpty + kMaxWStages,
-              kBarBEmpty = kBarBFull + kMaxBStages, kBarAFull = kBarBEmpty + kMaxBStages, kBarAEmpty = kBarAFull + kAStages,
+              kBarAFull = kBarBFull + kMaxBStages, kBarAEmpty = kBarAFull + kAStages,
               kBarDFull = kBarAEmpty + kAStages, kBarDEmpty = kBarDFull + 2, kBarMFull = kBarDEmpty + 2,
               kBarMEmpty = kBarMFull + 2, kNumGemmBars = kBarMEmpty + 2;
 
@@ -146,42 +171,40 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   const uint32_t m_code2 = (m_tile + 15u) & ~15u;            // offset of code2 inside the stage
   const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
   const uint32_t base = smem_u32(dyn_smem);
-  const uint32_t lut = pin((base + 65535u) & ~65535u);   // 64 KB aligned: PRMT drops the byte into address bits 8..15
+  // decode table: byte -> (fp32 code of the high nibble, fp32 code of the low nibble), one 8-byte copy per lane of a
+  // half-warp (an LDS.64 is served 16 lanes per wavefront), 32 KB, 32 KB-aligned so the address is (byte << 7) | lane bits
+  const uint32_t lut = pin((base + kGemmLutBytes - 1u) & ~(kGemmLutBytes - 1u));
   const uint32_t bar0 = smem_u32(s_bar);
   auto bar = [&](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
 
   // ---- one-time setup ----
   if (tid == 0) {
-    // carve [base, lut) and [lut + 64K, end) into 1024-aligned stages: two absmax stages, >= 2 raw-weight stages and as
-    // many activation stages as still fit
-    const uint32_t lo[2] = {(base + 1023u) & ~1023u, lut + 65536u}, hi[2] = {lut, base + kGemmSmemBytes};
-    int best_b = -1, best_w = 0, pick[2] = {0, 0}, pick_m[2] = {0, 0};
-    for (int m0 = 0; m0 <= 2; ++m0)
-      for (int n0 = 0; n0 <= kMaxBStages; ++n0)
-        for (int n1 = 0; n0 + n1 <= kMaxBStages; ++n1) {
-          int nw = 0;
-          bool ok = true;
-          const int nbr[2] = {n0, n1}, nmr[2] = {m0, 2 - m0};
-          for (int r = 0; r < 2; ++r) {
-            const long long room = (long long)hi[r] - (long long)lo[r] - (long long)nbr[r] * b_bytes - (long long)nmr[r] * m_bytes;
-            if (room < 0) ok = false; else nw += (int)(room / kWStageBytes);
-          }
-          if (!ok || nw < 2) continue;
-          nw = min(nw, kMaxWStages);
-          if (n0 + n1 > best_b || (n0 + n1 == best_b && nw > best_w)) {
-            best_b = n0 + n1; best_w = nw; pick[0] = n0; pick[1] = n1; pick_m[0] = m0; pick_m[1] = 2 - m0;
-          }
-        }
+    // carve [base, lut) and [lut + 32K, end) into 1024-aligned blocks: 4 activation stages, 2 absmax stages, 2 raw-weight
+    // stages, then more raw-weight stages while they fit
+    uint32_t cur[2] = {(base + 1023u) & ~1023u, lut + kGemmLutBytes};
+    const uint32_t hi[2] = {lut, base + kGemmSmemBytes};
     int ib = 0, iw = 0, im = 0;
-    for (int r = 0; r < 2; ++r) {
-      uint32_t cur = lo[r];
-      for (int i = 0; i < pick[r]; ++i) { s_bst[ib++] = cur; cur += b_bytes; }
-      for (int i = 0; i < pick_m[r]; ++i) { s_mst[im++] = cur; cur += m_bytes; }
-      while (iw < best_w && cur + kWStageBytes <= hi[r]) { s_wst[iw++] = cur; cur += kWStageBytes; }
-    }
+    auto place = [&](uint32_t bytes) -> uint32_t {
+      int best = -1;
+      uint32_t best_room = 0;
+      for (int r = 0; r < 2; ++r) {   // best fit: the region with the least room that still takes the block
+        const uint32_t room = hi[r] > cur[r] ? hi[r] - cur[r] : 0u;
+        if (room >= bytes && (best < 0 || room < best_room)) { best = r; best_room = room; }
+      }
+      if (best < 0) return 0u;
+      const uint32_t at = cur[best];
+      cur[best] += bytes;
+      return at;
+    };
+    bool ok = true;
+    for (int i = 0; i < kMaxBStages && ok; ++i) { const uint32_t at = place(b_bytes); if (at) s_bst[ib++] = at; else ok = false; }
+    for (int i = 0; i < 2 && ok; ++i) { const uint32_t at = place(m_bytes); if (at) s_mst[im++] = at; else ok = false; }
+    for (int i = 0; i < 2 && ok; ++i) { const uint32_t at = place(kWStageBytes); if (at) s_wst[iw++] = at; else ok = false; }
+    while (ok && iw < kMaxWStages) { const uint32_t at = place(kWStageBytes); if (!at) break; s_wst[iw++] = at; }
+    if (!ok) ib = 0;
     s_nb = ib; s_nw = iw;
     for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 8); }
-    for (int i = 0; i < kMaxBStages; ++i) { mbar_init(bar(kBarBFull + i), 1); mbar_init(bar(kBarBEmpty + i), 1); }
+    for (int i = 0; i < kMaxBStages; ++i) mbar_init(bar(kBarBFull + i), 1);
     for (int i = 0; i < kAStages; ++i) { mbar_init(bar(kBarAFull + i), 4); mbar_init(bar(kBarAEmpty + i), 1); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kBarDFull + i), 1); mbar_init(bar(kBarDEmpty + i), 4);
@@ -189,9 +212,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
     }
     fence_barrier_init();
   }
-  for (int i = tid; i < 256 * 32; i += kGemmThreads) {
-    const int b = i >> 5, l = i & 31;
-    const uint32_t p = lut + (uint32_t)b * 256u + (uint32_t)l * 8u;
+  for (int i = tid; i < 256 * 16; i += kGemmThreads) {
+    const int b = i >> 4, l = i & 15;
+    const uint32_t p = lut + (uint32_t)b * 128u + (uint32_t)l * 8u;
     sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
     sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
   }
@@ -205,28 +228,37 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   const uint32_t tmem = s_tmem;
   const int n_bst = s_nb, n_wst = s_nw;
 
+  const bool dbg_on = a.dbg != nullptr && blockIdx.x == 0 && lane == 0;
+  long long dbg_acc[6] = {0, 0, 0, 0, 0, 0};
   const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
   const int n_items = n_bst > 0 ? a.meta[2] * n_row_tiles : 0;   // (n_bst == 0: K too large for the stage budget; host rejects it)
 
   if (warp < 4) {
     set_max_regs_dec<56>();
-    if (warp == 0 && lane == 0) {
+    if (warp == 0) {
       // =============================== TMA producer: activation tiles, one stage per k-block ===============================
-      int sb = 0;
-      uint32_t phb = 0;
+      uint32_t phb = 0;   // one phase bit per stage; stage = k-block & 3, the same slot the A operand of that k-block uses
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int tile = item / n_row_tiles;
         const int row0 = a.tile_list[4 * tile + 1], n_box = (a.tile_list[4 * tile + 2] + kGemmBoxRows - 1) / kGemmBoxRows;
         for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(bar(kBarBEmpty + sb), phb ^ 1u);
-          mbar_expect_tx(bar(kBarBFull + sb), (uint32_t)n_box * (kGemmBoxRows * 128u));
+          const int sb = kb & 3;
+          GEMM_DBG_T0();
+          mbar_wait(bar(kBarAEmpty + sb), ((phb >> sb) & 1u) ^ 1u);
+          GEMM_DBG_ADD(0);
           const uint32_t dst = s_bst[sb];
-          for (int bx = 0; bx < n_box; ++bx)   // only the 32-row boxes the tile really has: L2 -> SM traffic follows the ragged tile
-            tma_load_2d(dst + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, kb * kBlock, row0 + bx * kGemmBoxRows, bar(kBarBFull + sb));
-          if (++sb == n_bst) { sb = 0; phb ^= 1u; }
+          if (elect_one()) {
+            mbar_expect_tx(bar(kBarBFull + sb), (uint32_t)n_box * (kGemmBoxRows * 128u));
+            for (int bx = 0; bx < n_box; ++bx)   // only the 32-row boxes the tile really has: L2 -> SM traffic follows the ragged tile
+              tma_load_2d(dst + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, kb * kBlock, row0 + bx * kGemmBoxRows, bar(kBarBFull + sb));
+          }
+          __syncwarp();
+          phb ^= 1u << sb;
+          GEMM_DBG_ADD(1);
         }
       }
-    } else if (warp == 2 && lane == 0) {
+      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[0 + i] = dbg_acc[i];
+    } else if (warp == 2) {
       // ============ TMA producer: the tile's absmax (one bulk copy per item, double-buffered) and the raw NF4 bytes, one
       // stage per 4 k-blocks, on their own rings so they run ahead of the MMA ============
       int sw = 0;
@@ -234,58 +266,89 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       const uint64_t pol = l2_policy_evict_last();
       const uint32_t am_elt = nested ? 1u : 4u;
       const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
-      int it = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+      const int spi = (nkb + 3) >> 2;                       // raw-weight stages per item
+      const int my_items = n_items > (int)blockIdx.x ? (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+      const int total_st = my_items * spi;
+      auto stage_coords = [&](int st, int& c0, int& c1) {   // global stage number -> TMA coordinates (byte column, weight row)
+        const int it_s = st / spi, item = (int)blockIdx.x + it_s * (int)gridDim.x;
         const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-        const int e = a.tile_list[4 * tile];
-        const int wrow = e * a.w.rows + rt * kGemmRowTile;
-        {
+        c0 = (st - it_s * spi) * 128;
+        c1 = a.tile_list[4 * tile] * a.w.rows + rt * kGemmRowTile;
+      };
+      int pf = 0;                                           // L2 prefetch cursor: kGemmWPrefetch stages ahead of the loads
+      for (int st = 0; st < total_st; ++st) {
+        for (; pf < total_st && pf <= st + kGemmWPrefetch; ++pf) {
+          int c0, c1;
+          stage_coords(pf, c0, c1);
+          if (elect_one())
+            asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(&map_w), "r"(c0), "r"(c1) : "memory");
+        }
+        if (st % spi == 0) {
+          const int it = st / spi, item = (int)blockIdx.x + it * (int)gridDim.x;
+          const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+          const int e = a.tile_list[4 * tile];
           const int mb = it & 1;
           const uint32_t mph = (uint32_t)(it >> 1) & 1u;
           const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
           const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
           mbar_wait(bar(kBarMEmpty + mb), mph ^ 1u);
-          mbar_expect_tx(bar(kBarMFull + mb), bytes + (nested ? 1024u : 0u));
-          bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
-                   bar(kBarMFull + mb), pol);
-          if (nested) bulk_g2s(s_mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kBarMFull + mb), pol);
+          if (elect_one()) {
+            mbar_expect_tx(bar(kBarMFull + mb), bytes + (nested ? 1024u : 0u));
+            bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
+                     bar(kBarMFull + mb), pol);
+            if (nested) bulk_g2s(s_mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kBarMFull + mb), pol);
+          }
+          __syncwarp();
         }
-        for (int kb = 0; kb < nkb; kb += 4) {
-          mbar_wait(bar(kBarWEmpty + sw), phw ^ 1u);
+        int c0, c1;
+        stage_coords(st, c0, c1);
+        GEMM_DBG_T0();
+        mbar_wait(bar(kBarWEmpty + sw), phw ^ 1u);
+        GEMM_DBG_ADD(0);
+        if (elect_one()) {
           mbar_expect_tx(bar(kBarWFull + sw), kWStageBytes);
-          tma_load_2d(s_wst[sw], &map_w, kb * 32, wrow, bar(kBarWFull + sw));
-          if (++sw == n_wst) { sw = 0; phw ^= 1u; }
+          tma_load_2d(s_wst[sw], &map_w, c0, c1, bar(kBarWFull + sw));
         }
+        __syncwarp();
+        if (++sw == n_wst) { sw = 0; phw ^= 1u; }
       }
-    } else if (warp == 1 && lane == 0) {
+      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[8 + i] = dbg_acc[i];
+    } else if (warp == 1) {
       // =============================== MMA issuer (one thread) ===============================
-      int sb = 0, it = 0;
-      uint32_t phb = 0, pha = 0;
+      int it = 0;
+      uint32_t pha = 0;   // one phase bit per stage (A in TMEM and B in smem of k-block kb both live in slot kb & 3)
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         const int tile = item / n_row_tiles;
         const int n_tok = a.tile_list[4 * tile + 2];
         const uint32_t idesc = make_idesc(max(16, (n_tok + 15) & ~15));
         const int db = it & 1;
         const uint32_t d_t = tmem + (uint32_t)db * kGemmTokTile;
+        GEMM_DBG_T0();
         mbar_wait(bar(kBarDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
+        GEMM_DBG_ADD(0);
         tc_fence_after();
         for (int kb = 0; kb < nkb; ++kb) {
           const int sa = kb & 3;
           mbar_wait(bar(kBarAFull + sa), (pha >> sa) & 1u);
-          mbar_wait(bar(kBarBFull + sb), phb);
+          GEMM_DBG_ADD(1);
+          mbar_wait(bar(kBarBFull + sa), (pha >> sa) & 1u);
+          GEMM_DBG_ADD(2);
           tc_fence_after();
           const uint32_t a_t = tmem + kTmemACol + (uint32_t)sa * 32u;
-          const uint32_t b_s = s_bst[sb];
+          const uint32_t b_s = s_bst[sa];
+          if (elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk)
-            tc_mma_ts(d_t, a_t + 8u * kk, make_bdesc(b_s + 32u * kk), idesc, (uint32_t)(kb | kk));
-          tc_commit(bar(kBarAEmpty + sa));
-          tc_commit(bar(kBarBEmpty + sb));
-          if (kb == nkb - 1) tc_commit(bar(kBarDFull + db));
+            for (int kk = 0; kk < 4; ++kk)
+              tc_mma_ts(d_t, a_t + 8u * kk, make_bdesc(b_s + 32u * kk), idesc, (uint32_t)(kb | kk));
+            tc_commit(bar(kBarAEmpty + sa));     // frees the A stage (dequant warps) and the B stage (TMA producer) together
+            if (kb == nkb - 1) tc_commit(bar(kBarDFull + db));
+          }
+          __syncwarp();
           pha ^= 1u << sa;
-          if (++sb == n_bst) { sb = 0; phb ^= 1u; }
+          GEMM_DBG_ADD(3);
         }
       }
+      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[16 + i] = dbg_acc[i];
     }
   }
   else if (warp < 12) {
@@ -293,7 +356,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
     set_max_regs_inc<168>();
     const int q = warp & 3, g = (warp - 4) >> 2;
     const int r = q * 32 + lane;
-    const uint32_t lut_lane = pin(lut | ((uint32_t)lane << 3));
+    const uint32_t lut_lane = pin(lut | ((uint32_t)(lane & 15) << 3));
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
     const uint32_t swz = (uint32_t)(r & 7);
     int sw = 0, it = 0;
@@ -314,11 +377,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
         off_e = __ldg(a.w.offset + e);
         blk_hi = ((i2 + 1) << 8) - blk0;   // relative to this row's first block
       }
+      GEMM_DBG_T0();
       mbar_wait(bar(kBarMFull + mb), (uint32_t)(it >> 1) & 1u);
+      GEMM_DBG_ADD(0);
       const uint32_t m_st = pin(s_mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       for (int kb0 = 0; kb0 < nkb; kb0 += 4) {
         mbar_wait(bar(kBarWFull + sw), phw);
+        GEMM_DBG_ADD(1);
         const uint32_t wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
@@ -340,11 +406,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
             for (int wi = 0; wi < 8; ++wi)
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const float2 f = lds_f32x2(prmt(wd[wi], lut_lane, 0x7604u | ((uint32_t)i << 4)));
+                const uint32_t sh = i == 0 ? wd[wi] << 7 : wd[wi] >> (8 * i - 7);
+                const float2 f = lds_f32x2((sh & 0x7F80u) | lut_lane);
                 regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am), __fmul_rn(f.y, am));
               }
             uint32_t& use = jj ? use1 : use0;
+            GEMM_DBG_ADD(2);
             mbar_wait(bar(kBarAEmpty + j), (use & 1u) ^ 1u);   // the MMAs that read this stage last time are done
+            GEMM_DBG_ADD(3);
             ++use;
             tc_fence_after();
             tmem_st32(t_lane + kTmemACol + (uint32_t)j * 32u, regs);
@@ -352,6 +421,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar(kBarAFull + j));
+            GEMM_DBG_ADD(4);
           }
         }
         __syncwarp();
@@ -361,6 +431,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kBarMEmpty + mb));
     }
+    if (dbg_on && (warp == 4 || warp == 8)) for (int i = 0; i < 6; ++i) a.dbg[(warp == 4 ? 24 : 32) + i] = dbg_acc[i];
   } else {
     // =============================== epilogue: TMEM -> registers -> global, overlapped with the next tile's main loop ======
     set_max_regs_dec<112>();
@@ -373,7 +444,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
       const int n = rt * kGemmRowTile + r;
       const int db = it & 1;
+      GEMM_DBG_T0();
       mbar_wait(bar(kBarDFull + db), (uint32_t)(it >> 1) & 1u);
+      GEMM_DBG_ADD(0);
       tc_fence_after();
       const bool row_ok = n < a.w.rows;
       for (int c0 = 0; c0 < n_tok; c0 += 32) {
@@ -381,16 +454,26 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
         tmem_ld32(t_lane + (uint32_t)(db * kGemmTokTile + c0), v);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         if (W13 && a.act == NF4MOE_ACT_SWIGLU_OAI) {
+          // rows 2j / 2j+1 (gate / up) sit in adjacent lanes.  Per column pair (i, i+1) the two lanes swap one value, after
+          // which the even lane owns (gate, up) of column i and the odd lane of column i+1: 16 shuffles, 16 activations
+          // and 16 stores per lane and chunk, all independent so they pipeline.
           __half* h = reinterpret_cast<__half*>(a.out);
           const int I = a.w.rows >> 1;
+          const bool odd = lane & 1;
+          float gt[16], up[16];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float mine = __half2float(__float2half_rn(__uint_as_float(v[i])));  // fp16 storage of the product
-            const float other = __shfl_xor_sync(0xffffffffu, mine, 1);
-            if ((i & 1) == (lane & 1) && row_ok && c0 + i < n_tok) {
-              const float res = (lane & 1) ? swiglu_oai(other, mine) : swiglu_oai(mine, other);
-              h[(long long)(row0 + c0 + i) * I + (n >> 1)] = __float2half_rn(res);
-            }
+          for (int pr = 0; pr < 16; ++pr) {
+            const float v0 = __half2float(__float2half_rn(__uint_as_float(v[2 * pr])));      // fp16 storage of the product
+            const float v1 = __half2float(__float2half_rn(__uint_as_float(v[2 * pr + 1])));
+            const float got = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
+            gt[pr] = odd ? got : v0;
+            up[pr] = odd ? v1 : got;
+          }
+          __half* dst = h + (long long)(row0 + c0 + (odd ? 1 : 0)) * I + (n >> 1);
+#pragma unroll
+          for (int pr = 0; pr < 16; ++pr) {
+            const __half res = __float2half_rn(swiglu_oai(gt[pr], up[pr]));
+            if (row_ok && c0 + 2 * pr + (odd ? 1 : 0) < n_tok) dst[(long long)(2 * pr) * I] = res;
           }
         } else if (W13) {
           __half* raw = reinterpret_cast<__half*>(a.out);
@@ -408,7 +491,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kBarDEmpty + db));
+      GEMM_DBG_ADD(1);
     }
+    if (dbg_on && warp == 12) for (int i = 0; i < 6; ++i) a.dbg[40 + i] = dbg_acc[i];
   }
 
   // ---- teardown ----
@@ -450,6 +535,11 @@ inline bool make_map_2d(CUtensorMap* m, const void* ptr, CUtensorMapDataType dt,
             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+inline long long*& gemm_debug_buffer() {
+  static long long* p = nullptr;
+  return p;
+}
+
 inline int gemm_tile_tokens(int T, int k, int E) {
   // small batches: 32-token tiles keep the activation stages at 4 KB; otherwise the full 256-column accumulator
   return ((long long)T * k <= 32ll * E) ? 32 : kGemmTokTile;
@@ -486,6 +576,7 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.tile_list = tile_list;
   a.act = act;
   a.tile_tokens = gemm_tile_tokens(T, k, E);
+  a.dbg = gemm_debug_buffer();
   CUtensorMap map_w, map_x;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");

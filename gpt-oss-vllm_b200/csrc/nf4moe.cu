@@ -170,6 +170,8 @@ int check_gemv_tokens(int T, int k, int E, const char* name) {
 extern "C" {
 
 int nf4moe_version(void) { return NF4MOE_VERSION; }
+// profiling hook (not part of the public header): 64 int64 cycle counters written by CTA 0 of the tcgen05 kernels
+void nf4moe_debug_set_gemm_counters(long long* dev_ptr) { gemm_debug_buffer() = dev_ptr; }
 const char* nf4moe_last_error(void) { return g_err; }
 int nf4moe_last_launch_count(void) { return g_launches; }
 
