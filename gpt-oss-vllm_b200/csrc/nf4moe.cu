@@ -6,6 +6,7 @@
 
 #include "common.cuh"
 #include "dequant.cuh"
+#include "ep.cuh"
 #include "gemm_tc.cuh"
 #include "gemv.cuh"
 #include "route.cuh"
@@ -366,6 +367,45 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
                        &g_launches);
 }
 
+// bucket -> (permute) -> w13 (+activation) -> w2 for the (row, slot) pairs of `ids` [T, k]; y fp16 [T*k, H] in pair order.
+static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* y, int T,
+                       int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (regime == NF4MOE_REGIME_AUTO) regime = gemm_available() && T > kGemmAutoThreshold ? NF4MOE_REGIME_GEMM : NF4MOE_REGIME_GEMV;
+  const bool gemm = regime == NF4MOE_REGIME_GEMM;
+  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, 0, stream)) return rc;
+  *launches += g_launches; g_launches = 0;
+  __half* h_dst = act == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
+  if (gemm) {
+    if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
+    *launches += g_launches; g_launches = 0;
+    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act, h_dst, stream)) return rc;
+  } else {
+    if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act, h_dst, stream)) return rc;
+  }
+  *launches += g_launches; g_launches = 0;
+  if (act == NF4MOE_ACT_CHUNK_SILU) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    chunk_silu_kernel<<<di.sms * 4, 256, 0, st>>>(ws.raw, ws.meta, I, ws.h);
+    CHECK_LAUNCH("chunk_silu_kernel");
+    *launches += g_launches; g_launches = 0;
+  }
+  if (gemm) {
+    if (int rc = nf4moe_gemm_w2(ws.h, w2, ws.offsets, ws.sorted, ws.meta, ws.tiles, T, k, E, y, stream)) return rc;
+  } else {
+    if (int rc = nf4moe_gemv_w2(ws.h, w2, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, y, stream)) return rc;
+  }
+  *launches += g_launches; g_launches = 0;
+  return 0;
+}
+
+static int check_layer_shapes(const char* name, const nf4moe_qweight* w13, const nf4moe_qweight* w2, int H, int I) {
+  if (w13->rows != 2 * I || w13->cols != H || w2->rows != H || w2->cols != I)
+    return fail(NF4MOE_EINVAL, "%s: weight shapes must be w13 [2I,H] = [%d,%d], w2 [H,I] = [%d,%d]", name, 2 * I, H, H, I);
+  return 0;
+}
+
 int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtype, const int32_t* topk_ids,
                        const float* topk_weights, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* out, int T,
                        int E, int H, int I, int k, int act, int regime, void* workspace, size_t workspace_bytes,
@@ -375,14 +415,12 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
     return fail(NF4MOE_EINVAL, "moe_forward: bad arguments");
   if (!router_logits && !(topk_ids && topk_weights))
     return fail(NF4MOE_EINVAL, "moe_forward: give router_logits or (topk_ids, topk_weights)");
-  if (w13->rows != 2 * I || w13->cols != H || w2->rows != H || w2->cols != I)
-    return fail(NF4MOE_EINVAL, "moe_forward: weight shapes must be w13 [2I,H] = [%d,%d], w2 [H,I] = [%d,%d]", 2 * I, H, H, I);
+  if (int rc = check_layer_shapes("moe_forward", w13, w2, H, I)) return rc;
   if (T == 0) return 0;
   const Workspace ws = carve(workspace, T, E, H, I, k);
   if (!workspace || workspace_bytes < ws.total)
     return fail(NF4MOE_EWORKSPACE, "moe_forward: workspace needs %zu bytes, got %zu", ws.total, workspace_bytes);
   if (!aligned16(workspace)) return fail(NF4MOE_EALIGN, "moe_forward: workspace must be 16-byte aligned");
-  cudaStream_t st = (cudaStream_t)stream;
   int launches = 0;
   const int32_t* ids = topk_ids;
   const float* wts = topk_weights;
@@ -394,34 +432,63 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
     ids = ids_w;
     wts = wts_w;
   }
-  if (regime == NF4MOE_REGIME_AUTO) regime = gemm_available() && T > kGemmAutoThreshold ? NF4MOE_REGIME_GEMM : NF4MOE_REGIME_GEMV;
-  const bool gemm = regime == NF4MOE_REGIME_GEMM;
-  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, 0, stream)) return rc;
-  launches += g_launches; g_launches = 0;
-  __half* h_dst = act == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
-  if (gemm) {
-    if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
-    launches += g_launches; g_launches = 0;
-    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act, h_dst, stream)) return rc;
-  } else {
-    if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act, h_dst, stream)) return rc;
-  }
-  launches += g_launches; g_launches = 0;
-  if (act == NF4MOE_ACT_CHUNK_SILU) {
-    DevInfo di;
-    if (int rc = device_info(&di)) return rc;
-    chunk_silu_kernel<<<di.sms * 4, 256, 0, st>>>(ws.raw, ws.meta, I, ws.h);
-    CHECK_LAUNCH("chunk_silu_kernel");
-    launches += g_launches; g_launches = 0;
-  }
-  if (gemm) {
-    if (int rc = nf4moe_gemm_w2(ws.h, w2, ws.offsets, ws.sorted, ws.meta, ws.tiles, T, k, E, ws.y, stream)) return rc;
-  } else {
-    if (int rc = nf4moe_gemv_w2(ws.h, w2, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, ws.y, stream)) return rc;
-  }
-  launches += g_launches; g_launches = 0;
+  if (int rc = run_experts(x, ids, w13, w2, ws.y, T, E, H, I, k, act, regime, ws, stream, &launches)) return rc;
   if (int rc = nf4moe_combine(ws.y, wts, ids, E, T, k, H, out, stream)) return rc;
   g_launches += launches;
+  return 0;
+}
+
+int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
+                       void* y_rows, int n_rows, int E, int H, int I, int act, int regime, void* workspace,
+                       size_t workspace_bytes, void* stream) {
+  g_launches = 0;
+  if (!rows || !row_expert || !y_rows || !w13 || !w2 || n_rows < 0 || E <= 0 || H <= 0 || I <= 0)
+    return fail(NF4MOE_EINVAL, "expert_rows: bad arguments");
+  if (int rc = check_layer_shapes("expert_rows", w13, w2, H, I)) return rc;
+  if (n_rows == 0) return 0;
+  const Workspace ws = carve(workspace, n_rows, E, H, I, 1);
+  if (!workspace || workspace_bytes < ws.total)
+    return fail(NF4MOE_EWORKSPACE, "expert_rows: workspace needs %zu bytes, got %zu", ws.total, workspace_bytes);
+  if (!aligned16(workspace) || !aligned16(rows) || !aligned16(y_rows))
+    return fail(NF4MOE_EALIGN, "expert_rows: rows, y_rows and workspace must be 16-byte aligned");
+  int launches = 0;
+  if (int rc = run_experts(rows, row_expert, w13, w2, y_rows, n_rows, E, H, I, 1, act, regime, ws, stream, &launches)) return rc;
+  g_launches += launches;
+  return 0;
+}
+
+int nf4moe_ep_pack(const void* x, const int32_t* ids, const int32_t* expert_offsets, const int32_t* sorted_pairs, int T, int k,
+                   int E, int H, int world, int cap, void* send_rows, int32_t* send_ids, int32_t* pair_slot,
+                   int32_t* status, void* stream) {
+  if (!x || !ids || !expert_offsets || !sorted_pairs || !send_rows || !send_ids || !pair_slot || !status || T < 0 || k <= 0 ||
+      E <= 0 || H <= 0 || H % 8 || world <= 0 || cap <= 0 || E % world)
+    return fail(NF4MOE_EINVAL, "ep_pack: bad arguments (E must be a multiple of world, H of 8)");
+  if (!aligned16(x) || !aligned16(send_rows)) return fail(NF4MOE_EALIGN, "ep_pack: 16-byte alignment required");
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(pair_slot, 0xFF, (size_t)T * k * 4, st);   // -1: dropped / not dispatched
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(pair_slot)");
+  const long long slots = (long long)world * cap;
+  const int grid = (int)std::min<long long>((slots + 7) / 8, (long long)di.sms * 8);
+  ep_pack_kernel<<<grid, 256, 0, st>>>((const __half*)x, ids, expert_offsets, sorted_pairs, k, H, world, E / world, cap,
+                                      (__half*)send_rows, send_ids, pair_slot, status);
+  CHECK_LAUNCH("ep_pack_kernel");
+  return 0;
+}
+
+int nf4moe_combine_indexed(const void* y, const float* weights, const int32_t* pair_slot, int T, int k, int H, void* out,
+                           void* stream) {
+  if (!y || !weights || !pair_slot || !out || T < 0 || k <= 0 || H <= 0 || H % 8)
+    return fail(NF4MOE_EINVAL, "combine_indexed: bad arguments");
+  if (!aligned16(y) || !aligned16(out)) return fail(NF4MOE_EALIGN, "combine_indexed: 16-byte alignment required");
+  if (T == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  const long long total = (long long)T * (H / 8);
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 8);
+  combine_indexed_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y, weights, pair_slot, T, k, H, (__half*)out);
+  CHECK_LAUNCH("combine_indexed_kernel");
   return 0;
 }
 

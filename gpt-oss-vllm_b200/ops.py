@@ -172,3 +172,43 @@ def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, to
 
 def last_launch_count() -> int:
     return int(_lib.load_library().nf4moe_last_launch_count())
+
+
+# ---- expert parallelism (nf4moe_ep_pack / nf4moe_expert_rows / nf4moe_combine_indexed) ---------------------------------
+def ep_pack(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: int, cap: int, send_rows: torch.Tensor,
+            send_ids: torch.Tensor, pair_slot: torch.Tensor, status: torch.Tensor) -> None:
+    """Write the dispatch all-to-all's send buffer straight from x (no separate pack pass)."""
+    T, H = x.shape
+    k = ids.shape[1]
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load_library().nf4moe_ep_pack(
+            x.data_ptr(), ids.data_ptr(), b["expert_offsets"].data_ptr(), b["sorted_pairs"].data_ptr(), T, k, E, H, world,
+            cap, send_rows.data_ptr(), send_ids.data_ptr(), pair_slot.data_ptr(), status.data_ptr(), _stream_ptr(x.device)))
+
+
+def expert_rows(rows: torch.Tensor, row_expert: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights,
+                y_rows: torch.Tensor, act: int = _lib.ACT_SWIGLU_OAI, regime: int = _lib.REGIME_AUTO,
+                nested: bool | None = None, workspace: torch.Tensor | None = None) -> torch.Tensor:
+    """y_rows[r] = W2[e] act(W13[e] rows[r]) for e = row_expert[r] in [0, E_local); other rows are left untouched."""
+    _require_cuda(rows, "rows")
+    n, H = rows.shape
+    E, I = w13.num_experts, w13.rows // 2
+    if workspace is None:
+        workspace = get_workspace(rows.device, n, E, H, I, 1)
+    q13, q2 = w13.c_struct(nested), w2.c_struct(nested)
+    with torch.cuda.device(rows.device):
+        _lib.check(_lib.load_library().nf4moe_expert_rows(
+            rows.data_ptr(), row_expert.data_ptr(), C.byref(q13), C.byref(q2), y_rows.data_ptr(), n, E, H, I, act, regime,
+            workspace.data_ptr(), workspace.numel(), _stream_ptr(rows.device)))
+    return y_rows
+
+
+def combine_indexed(y: torch.Tensor, weights: torch.Tensor, pair_slot: torch.Tensor, out: torch.Tensor | None = None):
+    T, k = weights.shape
+    H = y.shape[-1]
+    if out is None:
+        out = torch.empty(T, H, dtype=torch.float16, device=y.device)
+    with torch.cuda.device(y.device):
+        _lib.check(_lib.load_library().nf4moe_combine_indexed(y.data_ptr(), weights.data_ptr(), pair_slot.data_ptr(), T, k, H,
+                                                              out.data_ptr(), _stream_ptr(y.device)))
+    return out

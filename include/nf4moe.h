@@ -162,7 +162,32 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
                        int E, int H, int I, int k, int act, int regime, void* workspace, size_t workspace_bytes,
                        int32_t* topk_ids_out, float* topk_weights_out, void* stream);
 
-/* Number of kernels the last nf4moe_moe_forward on this thread launched (bench.py's gpu_launches). */
+/* ---- expert parallelism (one process per GPU; experts [r*E/world, (r+1)*E/world) live on rank r) ------------------------
+ * The reference is single-GPU (P/gpt_oss_server.py:25 pins CUDA_VISIBLE_DEVICES=0); these entry points are what the
+ * per-(token,k) expert loop of P/unsloth_to_vllm_converter.py:298-323 becomes when the experts of that loop are sharded.
+ * The all-to-all itself is issued by the host (NCCL via torch.distributed) between these calls. */
+
+/* Dispatch side.  `expert_offsets` / `sorted_pairs` come from nf4moe_bucket over the GLOBAL expert ids.  Writes, for peer
+ * p and its j-th routed pair:  send_rows[p*cap + j, :] = x[pair/k, :] (fp16 [world*cap, H]),  send_ids[p*cap + j] = expert id
+ * local to p (-1 in unused slots),  pair_slot[pair] = p*cap + j (-1 for pairs not dispatched).  status[0] |= 1 if a peer
+ * got more than `cap` pairs (the excess is dropped; cap = T*k can never overflow). */
+int nf4moe_ep_pack(const void* x, const int32_t* ids, const int32_t* expert_offsets, const int32_t* sorted_pairs, int T, int k,
+                   int E, int H, int world, int cap, void* send_rows, int32_t* send_ids, int32_t* pair_slot,
+                   int32_t* status, void* stream);
+
+/* Expert side.  y_rows[r, :] = W2[e] * act(W13[e] * rows[r, :]) with e = row_expert[r] in [0, E) (rows with any other id are
+ * skipped and their y is left untouched).  E, w13, w2 are the LOCAL experts.  Workspace: nf4moe_workspace_bytes(n_rows, E,
+ * H, I, 1). */
+int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
+                       void* y_rows, int n_rows, int E, int H, int I, int act, int regime, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
+/* Combine side.  out[t, :] = fp16( sum_slot weights[t,slot] * y[pair_slot[t*k+slot], :] ) -- nf4moe_combine's arithmetic and
+ * order, reading each pair's row where the return all-to-all left it. */
+int nf4moe_combine_indexed(const void* y, const float* weights, const int32_t* pair_slot, int T, int k, int H, void* out,
+                           void* stream);
+
+/* Number of kernels the last nf4moe_moe_forward / nf4moe_expert_rows on this thread launched (bench.py's gpu_launches). */
 int nf4moe_last_launch_count(void);
 
 #ifdef __cplusplus

@@ -13,12 +13,13 @@ p.add_argument("--reps", type=int, default=5)
 p.add_argument("--experts", type=int, default=32)
 p.add_argument("--absmax", nargs="+", default=["nested", "flat"])
 p.add_argument("--cfg", type=int, nargs="+", default=[0])
+p.add_argument("--regime", default="gemv", choices=["gemv", "gemm"])
 a = p.parse_args()
 if len(a.cfg) > 1:   # the library reads the override once per process: fan out
     import subprocess
     for c in a.cfg:
         argv = [sys.executable, __file__, "--cfg", str(c), "--layers", str(a.layers), "--reps", str(a.reps), "--experts",
-                str(a.experts), "--tokens", *map(str, a.tokens), "--absmax", *a.absmax]
+                str(a.experts), "--regime", a.regime, "--tokens", *map(str, a.tokens), "--absmax", *a.absmax]
         subprocess.run(argv, check=True)
     sys.exit(0)
 os.environ["NF4MOE_GEMV_CFG"] = str(a.cfg[0])
@@ -43,17 +44,20 @@ for T in a.tokens:
     x = torch.randn(T, H, generator=g, device=dev).half()
     lg = torch.randn(T, E, generator=g, device=dev).half()
     ids, wts = pkg.ops.route_topk(lg, 4)
-    b = pkg.ops.bucket(ids, E, want_tiles=False)
+    gemm = a.regime == "gemm"
+    regime = pkg.REGIME_GEMM if gemm else pkg.REGIME_GEMV
+    b = pkg.ops.bucket(ids, E, want_tiles=gemm)
+    xin = pkg.ops.permute_rows(x, b, 4) if gemm else x
     ea = int(b["meta"][0].item())
     for mode in a.absmax:
         nested = mode == "nested"
         # CUDA-graph replay: a Python/ctypes launch costs more CPU time than these kernels take on the GPU
         def run13():
-            return [pkg.ops.expert_w13(x, w13, b, T, 4, nested=nested) for w13, _ in stack]
+            return [pkg.ops.expert_w13(xin, w13, b, T, 4, nested=nested, regime=regime) for w13, _ in stack]
 
         def run2(hs):
             for h, (_, w2) in zip(hs, stack):
-                pkg.ops.expert_w2(h, w2, b, T, 4, nested=nested)
+                pkg.ops.expert_w2(h, w2, b, T, 4, nested=nested, regime=regime)
         hs = run13(); run2(hs); torch.cuda.synchronize()
         g13, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         side = torch.cuda.Stream()
@@ -74,5 +78,5 @@ for T in a.tokens:
         b13, b2 = ea * stack[0][0].nbytes(nested), ea * stack[0][1].nbytes(nested)
         m13, m2 = min(t13), min(t2)
         a13, a2 = sum(t13) / len(t13), sum(t2) / len(t2)
-        print(f"cfg={a.cfg[0]:2d} T={T:3d} E_act={ea:2d} {mode:6s} w13 {a13:7.1f} us (min {m13:6.1f}) {b13 / a13 / 1e3:7.1f} GB/s | "
+        print(f"{a.regime} cfg={a.cfg[0]:2d} T={T:3d} E_act={ea:2d} {mode:6s} w13 {a13:7.1f} us (min {m13:6.1f}) {b13 / a13 / 1e3:7.1f} GB/s | "
               f"w2 {a2:7.1f} us (min {m2:6.1f}) {b2 / a2 / 1e3:7.1f} GB/s | both {(b13 + b2) / (a13 + a2) / 1e3:7.1f} GB/s", flush=True)

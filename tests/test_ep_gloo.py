@@ -1,0 +1,86 @@
+"""CPU, world_size 2 over gloo: the expert-parallel choreography of gpt-oss-vllm_b200/ep.py (plan, fixed-capacity send
+buffers, three all-to-alls, slot maps) with the device steps played by the oracle (tests/ep_oracle_ops.py).  The result on
+every rank must equal the single-process oracle layer on that rank's tokens (to the last fp16 bit or two: CPU matmul blocking)."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+E, H, I, K, T = 8, 128, 64, 4, 11
+
+
+def _inputs():
+    from oracle import nf4_oracle as orc
+    rng = np.random.default_rng(77)
+    st13 = [orc.quantize_nf4((rng.standard_normal((2 * I, H)) * 0.05).astype(np.float16)) for _ in range(E)]
+    st2 = [orc.quantize_nf4((rng.standard_normal((H, I)) * 0.05).astype(np.float16)) for _ in range(E)]
+    d13 = np.stack([orc.dequant_state(s) for s in st13])
+    d2 = np.stack([orc.dequant_state(s) for s in st2])
+    return rng, d13, d2
+
+
+def _worker(rank, world, port, skew, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ep_oracle_ops import OracleEPOps
+        from oracle import nf4_oracle as orc
+        ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+        rng, d13, d2 = _inputs()
+        xs = [rng.standard_normal((T - r, H)).astype(np.float16) for r in range(world)]     # ragged: ranks differ in T
+        lgs = [rng.standard_normal((T - r, E)).astype(np.float16) for r in range(world)]
+        if skew:                                                                          # everything to rank 0's experts
+            for lg in lgs:
+                lg[:, : E // world] += 8
+        plan = ep.EPPlan(rank, world, E)
+        lo, hi = plan.local_experts.start, plan.local_experts.stop
+        layer = ep.EPMoELayer(None, None, plan, K, H, T, "cpu", device_ops=OracleEPOps(d13[lo:hi], d2[lo:hi]))
+        out = layer.forward(torch.from_numpy(xs[rank]), router_logits=torch.from_numpy(lgs[rank]))
+        layer.check_overflow()
+        ref = orc.moe_forward_ref(xs[rank], lgs[rank], d13, d2, k=K)
+        got = out.numpy().astype(np.float32)
+        # torch's CPU matmul may block rows differently for different batch sizes (the owner multiplies rows of several
+        # ranks at once), so allow last-bit fp16 differences; a choreography error would be O(1)
+        q.put((rank, float(np.abs(got - ref.astype(np.float32)).max()), float(np.mean(got == ref.astype(np.float32))), layer.cap,
+               int((layer.send_ids >= 0).sum())))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("skew", [False, True])
+def test_ep_world2_matches_single_process_oracle(skew):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000) + (7 if skew else 0)
+    procs = [ctx.Process(target=_worker, args=(r, world, port, skew, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, max_abs, frac_equal, cap, used in res:
+        assert max_abs <= 1e-3 and frac_equal >= 0.98, f"rank {rank} differs from the single-process oracle: {max_abs} {frac_equal}"
+        assert cap == T * K and used == (T - rank) * K
+
+
+def test_plan_partition_and_capacity():
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    p = ep.EPPlan(3, 8, 32)
+    assert list(p.local_experts) == [12, 13, 14, 15] and p.owner(12) == 3 and p.owner(31) == 7 and p.experts_per_rank == 4
+    assert p.capacity(32, 4) == 128                       # worst case: cannot overflow
+    assert p.capacity(32, 4, factor=2.0) == 32            # 2 x the mean load of 16, multiple of 16
+    assert ep.EPPlan(0, 8, 128).experts_per_rank == 16    # the 120b shape
+    with pytest.raises(ValueError):
+        ep.EPPlan(0, 3, 32)
+    with pytest.raises(RuntimeError):                     # no CPU fallback unless a device_ops object is injected
+        ep.EPMoELayer(None, None, p, 4, 64, 8, "cpu")
