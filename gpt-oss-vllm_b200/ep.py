@@ -317,5 +317,10 @@ def bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, m
                              "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": wbytes,
                              "avg_launch_us": d * 1e6}}
         print(json.dumps(line), flush=True)
-    dist.barrier()
-    dist.destroy_process_group()
+    # Leave without NCCL teardown: destroying a communicator that a live CUDA graph captured can block forever, and a
+    # benchmark process has nothing left to release.  Every rank has finished its collectives at this point.
+    torch.cuda.synchronize()
+    import sys
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
