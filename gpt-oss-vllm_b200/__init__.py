@@ -7,7 +7,7 @@ The directory name has hyphens (it follows the reference's name), so import it w
 or through the alias module `nf4moe_b200` at the repo root.
 """
 from . import _lib, ops  # noqa: F401
-from ._lib import (ACT_CHUNK_SILU, ACT_SWIGLU_OAI, REGIME_AUTO, REGIME_GEMM, REGIME_GEMV, Nf4MoeError,  # noqa: F401
+from ._lib import (ACT_CHUNK_SILU, ACT_SWIGLU_OAI, REGIME_AUTO, REGIME_GEMM, REGIME_GEMM_FAST, REGIME_GEMV, Nf4MoeError,  # noqa: F401
                    load_library)
 from .moe_method import B200NF4MoEConfig, B200NF4MoEMethod, NF4MoELayer  # noqa: F401
 from .quant import BLOCKSIZE, NESTED_BLOCKSIZE, NF4ExpertWeights  # noqa: F401

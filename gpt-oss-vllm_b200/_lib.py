@@ -13,7 +13,8 @@ LIB_PATH = os.path.join(_HERE, "libnf4moe.so")
 
 ACT_SWIGLU_OAI = 0
 ACT_CHUNK_SILU = 1
-REGIME_AUTO, REGIME_GEMV, REGIME_GEMM = 0, 1, 2
+REGIME_AUTO, REGIME_GEMV, REGIME_GEMM, REGIME_GEMM_FAST = 0, 1, 2, 3
+GEMM_EXACT, GEMM_FAST = 0, 1
 LOGITS_DTYPE = {"float16": 0, "float32": 1, "bfloat16": 2}
 
 # every symbol include/nf4moe.h declares (tests check the library exports exactly these)
@@ -61,8 +62,8 @@ def _declare(lib):
     lib.nf4moe_combine.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp, vp]
     lib.nf4moe_gemv_w13_swiglu.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
     lib.nf4moe_gemv_w2.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
-    lib.nf4moe_gemm_w13_swiglu.argtypes = [vp, qp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
-    lib.nf4moe_gemm_w2.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
+    lib.nf4moe_gemm_w13_swiglu.argtypes = [vp, qp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]
+    lib.nf4moe_gemm_w2.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
     lib.nf4moe_moe_forward.argtypes = [vp, vp, i32, vp, vp, qp, qp, vp, i32, i32, i32, i32, i32, i32, i32, vp, sz, vp,
                                        vp, vp]
     lib.nf4moe_ep_pack.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp]

@@ -202,6 +202,17 @@ __device__ __forceinline__ float swiglu_oai(float g, float u) {
   const float glu = g * (1.0f / (1.0f + __expf(-1.702f * g)));
   return (u + 1.0f) * glu;
 }
+// Two (gate, up) pairs packed as half2 -> two results packed as half2.  The clamps are exact in fp16; everything after them
+// is the fp32 arithmetic of swiglu_oai above, so the result is bit-identical to the scalar form.
+__device__ __forceinline__ uint32_t swiglu_oai_h2(uint32_t g2, uint32_t u2) {
+  const __half2 lim = __float2half2_rn(7.0f), nlim = __float2half2_rn(-7.0f);
+  const __half2 g = __hmin2(*reinterpret_cast<const __half2*>(&g2), lim);
+  const __half2 u = __hmax2(__hmin2(*reinterpret_cast<const __half2*>(&u2), lim), nlim);
+  const float2 gf = __half22float2(g), uf = __half22float2(u);
+  const float r0 = (uf.x + 1.0f) * (gf.x * (1.0f / (1.0f + __expf(-1.702f * gf.x))));
+  const float r1 = (uf.y + 1.0f) * (gf.y * (1.0f / (1.0f + __expf(-1.702f * gf.y))));
+  return pack_half2(r0, r1);
+}
 // the reference wrapper's own variant, P/unsloth_to_vllm_converter.py:312-315
 __device__ __forceinline__ float silu_mul(float g, float u) { return g / (1.0f + __expf(-g)) * u; }
 

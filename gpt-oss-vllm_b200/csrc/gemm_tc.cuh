@@ -25,26 +25,28 @@
 #pragma once
 #include <cuda.h>
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 
 namespace nf4moe {
 
 constexpr int kGemmAutoThreshold = 64;  // tokens; above this nf4moe_moe_forward(AUTO) uses the tcgen05 path
-constexpr int kGemmThreads = 512;
-constexpr int kGemmTokTile = 192;       // max MMA N: two accumulators of 192 columns + four A stages fill the 512 TMEM columns
+constexpr int kDqGroups = 3;            // dequant warpgroups; k-block c of a CTA belongs to group c % 3
+constexpr int kGemmThreads = (4 + 4 * kDqGroups + 4) * 32;   // 640: control WG, 3 dequant WGs, epilogue WG
+constexpr int kGemmTokTile = 160;       // largest MMA N: two accumulators of 160 columns leave 192 TMEM columns = 3 slots of 2 k-blocks
 constexpr int kGemmRowTile = 128;       // MMA M
 constexpr int kGemmBoxRows = 32;        // token rows per activation TMA box (a tile is ceil(rows/32) boxes)
-constexpr int kAStages = 4;             // A (dequantised weights) stages in TMEM, 32 columns each
-constexpr int kMaxBStages = 4;          // activation stages: exactly kAStages, stage = k-block & 3
-constexpr int kGemmWPrefetch = 6;        // raw-weight stages requested into L2 ahead of the shared-memory ring
+constexpr int kMaxAStages = 12;         // A (dequantised weights) stages in TMEM, 32 columns each: (512 - 2*tile) / 32
+constexpr int kMaxBStages = 12;         // activation stages in shared memory (own ring, own empty barriers)
+constexpr int kGemmWPrefetch = 6;       // raw-weight stages requested into L2 ahead of the shared-memory ring
 constexpr int kMaxWStages = 4;
 constexpr uint32_t kWStageBytes = 128 * 128;   // raw NF4: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kGemmSmemBytes = 232448 - 1024;  // dynamic part; the kernel's static __shared__ control block takes the rest
-constexpr uint32_t kGemmLutBytes = 32768;
+constexpr uint32_t kGemmLutBytes = 65536;
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kTmemACol = 2 * kGemmTokTile;   // accumulators at columns 0 and 192, A stages at [384, 384 + 4*32)
 
 inline bool gemm_available() { return true; }
 
@@ -86,6 +88,11 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ uint32_t lds32_volatile(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ float2 lds_f32x2(uint32_t addr) {
   float2 v;
   asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
@@ -121,7 +128,11 @@ struct GemmArgs {
   const int32_t* tile_list;       // (expert, first sorted row, rows, -) per token tile
   int act;
   long long* dbg;                 // optional [64] cycle counters written by CTA 0 (profiling builds of the caller only)
-  int tile_tokens;                // largest token tile (256, or 32 for small batches): sizes the activation stages
+  int tile_tokens;                // largest token tile in tile_list (multiple of 32): sizes the activation stages and the accumulators
+  int kps;                        // k-blocks per pipeline slot (2 or 4): one barrier wait and one commit serve kps k-blocks
+  int n_a;                        // slots in TMEM: (512 - 2 * tile_tokens) / (32 * kps), each kps x 32 columns of A operand
+  int want_b;                     // activation stages wanted (the kernel takes fewer if shared memory runs out, never below 2)
+  int exp;                        // timing experiments (NF4MOE_GEMM_EXP; results are wrong when non-zero)
 };
 
 // instruction descriptor: D f32, A/B f16, both K-major, M = 128, N = n
@@ -144,46 +155,101 @@ __device__ __forceinline__ uint64_t make_bdesc(uint32_t smem_addr) {
   } while (0)
 
 // barrier slots inside s_bar[]
-constexpr int kBarWFull = 0, kBarWEmpty = kBarWFull + kMaxWStages, kBarBFull = kBarWEmpty + kMaxWStages,
-              kBarAFull = kBarBFull + kMaxBStages, kBarAEmpty = kBarAFull + kAStages,
-              kBarDFull = kBarAEmpty + kAStages, kBarDEmpty = kBarDFull + 2, kBarMFull = kBarDEmpty + 2,
-              kBarMEmpty = kBarMFull + 2, kNumGemmBars = kBarMEmpty + 2;
+// The main loop moves in SLOTS of kps k-blocks (kps = 2 for big token tiles, 4 for decode-sized ones).  With c = the CTA's
+// running k-block count (each item padded to a multiple of kps), k-block c lives in slot (c / kps) % n_a, sub-block c % kps:
+//   full[slot]  <- 4 dequant warps per sub-block (A operand written to TMEM) + the activation producer's expect_tx and
+//                  TMA bytes: ONE wait per slot on the MMA thread.  Every mbarrier / tcgen05 / TMA instruction costs a
+//                  single-thread role 100-300 cycles of latency here (measured), so they are rationed per slot, not per k-block
+//   empty[slot] <- ONE tcgen05.commit per slot; waited on by the dequant warps (TMEM reuse, n_a slots later) and by the
+//                  activation producer (shared-memory reuse, n_b / kps <= n_a slots later)
+constexpr int kBarWFull = 0, kBarWEmpty = kBarWFull + kMaxWStages, kBarFull = kBarWEmpty + kMaxWStages,
+              kBarEmpty = kBarFull + kMaxAStages, kBarDFull = kBarEmpty + kMaxAStages, kBarDEmpty = kBarDFull + 2,
+              kBarMFull = kBarDEmpty + 2, kBarMEmpty = kBarMFull + 2, kNumGemmBars = kBarMEmpty + 2;
 
 template <int N>
 __device__ __forceinline__ void set_max_regs_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N>
 __device__ __forceinline__ void set_max_regs_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
-template <bool W13>
+__device__ __forceinline__ uint32_t hmul2_u32(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+
+// One weight row x one 64-wide NF4 block (32 packed bytes in v0, v1) -> 32 half2 registers in K order.
+// Every byte is one table look-up; PRMT drops the byte into bits 8..15 of the 64 KB-aligned table address.
+//   EXACT: entry = the two fp32 NF4 codes; each is scaled in fp32 and rounded ONCE to fp16: bit-identical to bitsandbytes'
+//          dequantize_4bit (fp32 multiply, store as half), so the tensor cores see the very matrix the reference multiplies.
+//   FAST : entry = the two codes as half2, scaled by fp16(absmax) with one HMUL2: half the shared-memory wavefronts and
+//          3 instead of 5 instructions per byte; differs from EXACT by fp16 roundings of code and absmax (~2^-11 relative).
+template <bool FAST>
+__device__ __forceinline__ void decode_block(const uint4 v0, const uint4 v1, const uint32_t lut_lane, const float am,
+                                             uint32_t (&regs)[32], const bool skip_lut = false) {
+  const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+  const uint32_t am2 = FAST ? pack_half2(am, am) : 0u;
+#pragma unroll
+  for (int wi = 0; wi < 8; ++wi)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t addr = prmt(wd[wi], lut_lane, 0x7604u | ((uint32_t)i << 4));
+      if (FAST) {
+        regs[wi * 4 + i] = hmul2_u32(skip_lut ? addr : lds32(addr), am2);
+      } else {
+        const float2 f = lds_f32x2(addr);
+        regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am), __fmul_rn(f.y, am));
+      }
+    }
+}
+
+// Warp roles (640 threads, one persistent CTA per SM, registers re-balanced per warpgroup with setmaxnreg):
+//   warp 0        TMA producer: activation tiles [<= tile_tokens x 64] per k-block as 32-row boxes, own ring of n_b stages
+//   warp 1        TMEM allocator and the single MMA-issuing thread (tcgen05.mma kind::f16, A in TMEM, B in smem)
+//   warp 2        TMA producer: the tile's absmax (one bulk copy per item, double-buffered) and raw NF4 stages
+//                 [128 rows x 128 B] = 4 k-blocks, L2-prefetched kGemmWPrefetch stages ahead
+//   warps 4-15    dequant: three warpgroups; k-block c (counted over the CTA's whole run) belongs to group c % 3, A stage c % n_a.
+//                 A thread owns one weight row: absmax is a per-thread scalar, the result goes to TMEM with one tcgen05.st.x32
+//   warps 16-19   epilogue: tcgen05.ld of one accumulator while the next item's main loop fills the other
+template <bool W13, bool FAST>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a, const __grid_constant__ CUtensorMap map_w,
-                                                              const __grid_constant__ CUtensorMap map_x) {
+                                                              const __grid_constant__ CUtensorMap map_x,
+                                                              const __grid_constant__ CUtensorMap map_xw) {
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumGemmBars];
   __shared__ uint32_t s_tmem;
-  __shared__ uint32_t s_wst[kMaxWStages], s_bst[kMaxBStages], s_mst[2];
+  __shared__ uint32_t s_wst[kMaxWStages], s_mst[2];
   __shared__ int s_nw, s_nb;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nkb = a.w.nkb;
+  const int n_a = a.n_a, kps = a.kps;
+  const int nslot = (nkb + kps - 1) / kps;                  // slots per item (the last one may be partly padding)
   const bool nested = a.w.absmax_f32 == nullptr;
   const uint32_t b_bytes = (uint32_t)a.tile_tokens * 128u;
+  const uint32_t acol0 = 2u * (uint32_t)a.tile_tokens;      // TMEM: accumulators at columns 0 and tile_tokens, A stages after them
   // absmax stage: the tile's [128 rows x nkb] absmax (fp32, or u8 + the expert's 1 KB code2 table when nested)
   const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
   const uint32_t m_code2 = (m_tile + 15u) & ~15u;            // offset of code2 inside the stage
   const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
   const uint32_t base = smem_u32(dyn_smem);
-  // decode table: byte -> (fp32 code of the high nibble, fp32 code of the low nibble), one 8-byte copy per lane of a
-  // half-warp (an LDS.64 is served 16 lanes per wavefront), 32 KB, 32 KB-aligned so the address is (byte << 7) | lane bits
+  // decode table: 256 rows of 256 B, row b = one entry per lane (EXACT: 8 B = fp32 codes of the high and low nibble,
+  // FAST: 4 B = the same two codes as half2), 64 KB-aligned so a table address is [hi16 | byte | lane offset]
   const uint32_t lut = pin((base + kGemmLutBytes - 1u) & ~(kGemmLutBytes - 1u));
-  const uint32_t bar0 = smem_u32(s_bar);
+  const uint32_t bar0 = pin(smem_u32(s_bar));   // pinned: otherwise every use re-derives it from SR_CgaCtaId
   auto bar = [&](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
+  const uint32_t b_ring = pin(lut + kGemmLutBytes);   // activation stage i lives at b_ring + i * b_bytes
 
   // ---- one-time setup ----
   if (tid == 0) {
-    // carve [base, lut) and [lut + 32K, end) into 1024-aligned blocks: 4 activation stages, 2 absmax stages, 2 raw-weight
-    // stages, then more raw-weight stages while they fit
-    uint32_t cur[2] = {(base + 1023u) & ~1023u, lut + kGemmLutBytes};
-    const uint32_t hi[2] = {lut, base + kGemmSmemBytes};
-    int ib = 0, iw = 0, im = 0;
+    // Shared memory around the 64 KB-aligned table: the activation ring is ONE contiguous block right above it (stage
+    // addresses are then base + i * b_bytes: no table look-up on the single-thread roles); raw-weight stages fill the rest
+    // above; the two absmax stages and more raw-weight stages go below.
+    const uint32_t above0 = lut + kGemmLutBytes, above1 = base + kGemmSmemBytes;
+    int nb = min(min(a.want_b, kMaxBStages), n_a * a.kps);     // n_b / kps <= n_a keeps the shared slots in phase
+    nb = min(nb, (int)((above1 - above0) / b_bytes));
+    nb -= nb % a.kps;                                          // whole slots only
+    uint32_t cur[2] = {(base + 1023u) & ~1023u, above0 + (uint32_t)nb * b_bytes};
+    const uint32_t hi[2] = {lut, above1};
+    int iw = 0, im = 0;
     auto place = [&](uint32_t bytes) -> uint32_t {
       int best = -1;
       uint32_t best_room = 0;
@@ -196,27 +262,27 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       cur[best] += bytes;
       return at;
     };
-    bool ok = true;
-    for (int i = 0; i < kMaxBStages && ok; ++i) { const uint32_t at = place(b_bytes); if (at) s_bst[ib++] = at; else ok = false; }
-    for (int i = 0; i < 2 && ok; ++i) { const uint32_t at = place(m_bytes); if (at) s_mst[im++] = at; else ok = false; }
-    for (int i = 0; i < 2 && ok; ++i) { const uint32_t at = place(kWStageBytes); if (at) s_wst[iw++] = at; else ok = false; }
-    while (ok && iw < kMaxWStages) { const uint32_t at = place(kWStageBytes); if (!at) break; s_wst[iw++] = at; }
-    if (!ok) ib = 0;
-    s_nb = ib; s_nw = iw;
-    for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 8); }
-    for (int i = 0; i < kMaxBStages; ++i) mbar_init(bar(kBarBFull + i), 1);
-    for (int i = 0; i < kAStages; ++i) { mbar_init(bar(kBarAFull + i), 4); mbar_init(bar(kBarAEmpty + i), 1); }
+    for (int i = 0; i < 2; ++i) { const uint32_t at = place(m_bytes); if (at) s_mst[im++] = at; }
+    for (int i = 0; i < kMaxWStages; ++i) { const uint32_t at = place(kWStageBytes); if (at) s_wst[iw++] = at; else break; }
+    s_nb = (im == 2 && iw >= 2 && nb >= a.kps) ? nb : 0;
+    s_nw = iw;
+    for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 4 * kDqGroups); }
+    for (int i = 0; i < kMaxAStages; ++i) { mbar_init(bar(kBarFull + i), 4 * a.kps + 1); mbar_init(bar(kBarEmpty + i), 1); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kBarDFull + i), 1); mbar_init(bar(kBarDEmpty + i), 4);
-      mbar_init(bar(kBarMFull + i), 1); mbar_init(bar(kBarMEmpty + i), 8);
+      mbar_init(bar(kBarMFull + i), 1); mbar_init(bar(kBarMEmpty + i), 4 * kDqGroups);
     }
     fence_barrier_init();
   }
-  for (int i = tid; i < 256 * 16; i += kGemmThreads) {
-    const int b = i >> 4, l = i & 15;
-    const uint32_t p = lut + (uint32_t)b * 128u + (uint32_t)l * 8u;
-    sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
-    sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
+  for (int i = tid; i < 256 * 32; i += kGemmThreads) {
+    const int b = i >> 5, l = i & 31;
+    if (FAST) {
+      sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
+    } else {
+      const uint32_t p = lut + (uint32_t)b * 256u + (uint32_t)l * 8u;
+      sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
+      sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
+    }
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
@@ -234,64 +300,76 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   const int n_items = n_bst > 0 ? a.meta[2] * n_row_tiles : 0;   // (n_bst == 0: K too large for the stage budget; host rejects it)
 
   if (warp < 4) {
-    set_max_regs_dec<56>();
+    set_max_regs_dec<48>();
     if (warp == 0) {
-      // =============================== TMA producer: activation tiles, one stage per k-block ===============================
-      uint32_t phb = 0;   // one phase bit per stage; stage = k-block & 3, the same slot the A operand of that k-block uses
+      // =============================== TMA producer: activation tiles, kps stages per slot ===============================
+      // A lone warp runs dependent instructions at ~6 cycles each, so this loop is kept to a few dozen instructions per slot:
+      // running addresses instead of index arithmetic, no shared-memory look-ups, one wait and one expect_tx per slot.
+      const int lead = n_bst / kps;                       // slots the shared-memory ring holds
+      const uint32_t full0 = bar(kBarFull), full_end = bar(kBarFull + n_a);
+      const uint32_t empty0 = bar(kBarEmpty), empty_end = bar(kBarEmpty + n_a);
+      const uint32_t slot_bytes = (uint32_t)kps * b_bytes, ring_end = b_ring + (uint32_t)n_bst * b_bytes;
+      uint32_t full_a = full0, empty_a = empty0, dst = b_ring, pe = 0;
+      int cs = 0;                                         // slots issued so far
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int tile = item / n_row_tiles;
-        const int row0 = a.tile_list[4 * tile + 1], n_box = (a.tile_list[4 * tile + 2] + kGemmBoxRows - 1) / kGemmBoxRows;
-        for (int kb = 0; kb < nkb; ++kb) {
-          const int sb = kb & 3;
-          GEMM_DBG_T0();
-          mbar_wait(bar(kBarAEmpty + sb), ((phb >> sb) & 1u) ^ 1u);
-          GEMM_DBG_ADD(0);
-          const uint32_t dst = s_bst[sb];
+        const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
+        const bool whole = n_tok == a.tile_tokens;   // a full tile is one box; a ragged one only the 32-row boxes it really has
+        const int n_box = (n_tok + kGemmBoxRows - 1) / kGemmBoxRows;
+        const uint32_t kb_bytes = whole ? b_bytes : (uint32_t)n_box * (kGemmBoxRows * 128u);
+        for (int kb0 = 0; kb0 < nkb; kb0 += kps, ++cs) {
+          if (cs >= lead) {                          // the MMAs that read these B stages (slot cs - lead) are done
+            mbar_wait(empty_a, pe);
+            empty_a += 8u;
+            if (empty_a == empty_end) { empty_a = empty0; pe ^= 1u; }
+          }
+          const int nreal = min(kps, nkb - kb0);
           if (elect_one()) {
-            mbar_expect_tx(bar(kBarBFull + sb), (uint32_t)n_box * (kGemmBoxRows * 128u));
-            for (int bx = 0; bx < n_box; ++bx)   // only the 32-row boxes the tile really has: L2 -> SM traffic follows the ragged tile
-              tma_load_2d(dst + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, kb * kBlock, row0 + bx * kGemmBoxRows, bar(kBarBFull + sb));
+            mbar_expect_tx(full_a, (uint32_t)nreal * kb_bytes);
+            for (int u = 0; u < nreal; ++u) {
+              if (whole) {
+                tma_load_2d(dst + (uint32_t)u * b_bytes, &map_xw, (kb0 + u) * kBlock, row0, full_a);
+              } else {
+                for (int bx = 0; bx < n_box; ++bx)
+                  tma_load_2d(dst + (uint32_t)u * b_bytes + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, (kb0 + u) * kBlock,
+                              row0 + bx * kGemmBoxRows, full_a);
+              }
+            }
           }
           __syncwarp();
-          phb ^= 1u << sb;
-          GEMM_DBG_ADD(1);
+          dst += slot_bytes;
+          if (dst == ring_end) dst = b_ring;
+          full_a += 8u;
+          if (full_a == full_end) full_a = full0;
         }
       }
-      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[0 + i] = dbg_acc[i];
     } else if (warp == 2) {
       // ============ TMA producer: the tile's absmax (one bulk copy per item, double-buffered) and the raw NF4 bytes, one
-      // stage per 4 k-blocks, on their own rings so they run ahead of the MMA ============
-      int sw = 0;
-      uint32_t phw = 0;
+      // stage per 4 k-blocks, on their own ring so they run ahead of the MMA.  Lean on purpose (see the activation producer):
+      // per-item coordinates are computed once, the per-stage work is a wait, an expect_tx, a TMA and an L2 prefetch. ======
       const uint64_t pol = l2_policy_evict_last();
       const uint32_t am_elt = nested ? 1u : 4u;
       const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
       const int spi = (nkb + 3) >> 2;                       // raw-weight stages per item
-      const int my_items = n_items > (int)blockIdx.x ? (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-      const int total_st = my_items * spi;
-      auto stage_coords = [&](int st, int& c0, int& c1) {   // global stage number -> TMA coordinates (byte column, weight row)
-        const int it_s = st / spi, item = (int)blockIdx.x + it_s * (int)gridDim.x;
+      const uint32_t wfull0 = bar(kBarWFull), wempty0 = bar(kBarWEmpty);
+      int sw = 0, it = 0;
+      uint32_t phw = 0;
+      // L2 prefetch runs kGemmWPrefetch stages ahead: (pf_item, pf_st) is its cursor, pf_row the weight row of pf_item's tile
+      int pf_item = blockIdx.x, pf_st = 0, pf_ahead = 0, pf_row = 0;
+      auto item_row = [&](int item) -> int {
         const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-        c0 = (st - it_s * spi) * 128;
-        c1 = a.tile_list[4 * tile] * a.w.rows + rt * kGemmRowTile;
+        return a.tile_list[4 * tile] * a.w.rows + rt * kGemmRowTile;
       };
-      int pf = 0;                                           // L2 prefetch cursor: kGemmWPrefetch stages ahead of the loads
-      for (int st = 0; st < total_st; ++st) {
-        for (; pf < total_st && pf <= st + kGemmWPrefetch; ++pf) {
-          int c0, c1;
-          stage_coords(pf, c0, c1);
-          if (elect_one())
-            asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(&map_w), "r"(c0), "r"(c1) : "memory");
-        }
-        if (st % spi == 0) {
-          const int it = st / spi, item = (int)blockIdx.x + it * (int)gridDim.x;
-          const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-          const int e = a.tile_list[4 * tile];
+      if (pf_item < n_items) pf_row = item_row(pf_item);
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+        const int e = a.tile_list[4 * tile];
+        const int c1 = e * a.w.rows + rt * kGemmRowTile;
+        {
           const int mb = it & 1;
-          const uint32_t mph = (uint32_t)(it >> 1) & 1u;
           const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
           const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
-          mbar_wait(bar(kBarMEmpty + mb), mph ^ 1u);
+          mbar_wait(bar(kBarMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(bar(kBarMFull + mb), bytes + (nested ? 1024u : 0u));
             bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
@@ -300,67 +378,90 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           }
           __syncwarp();
         }
-        int c0, c1;
-        stage_coords(st, c0, c1);
-        GEMM_DBG_T0();
-        mbar_wait(bar(kBarWEmpty + sw), phw ^ 1u);
-        GEMM_DBG_ADD(0);
-        if (elect_one()) {
-          mbar_expect_tx(bar(kBarWFull + sw), kWStageBytes);
-          tma_load_2d(s_wst[sw], &map_w, c0, c1, bar(kBarWFull + sw));
+        for (int st = 0; st < spi; ++st) {
+          while (pf_ahead <= kGemmWPrefetch && pf_item < n_items) {
+            if (elect_one())
+              asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(&map_w), "r"(pf_st * 128), "r"(pf_row) : "memory");
+            ++pf_ahead;
+            if (++pf_st == spi) {
+              pf_st = 0;
+              pf_item += gridDim.x;
+              if (pf_item < n_items) pf_row = item_row(pf_item);
+            }
+          }
+          --pf_ahead;
+          mbar_wait(wempty0 + 8u * (uint32_t)sw, phw ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(wfull0 + 8u * (uint32_t)sw, kWStageBytes);
+            tma_load_2d(s_wst[sw], &map_w, st * 128, c1, wfull0 + 8u * (uint32_t)sw);
+          }
+          __syncwarp();
+          if (++sw == n_wst) { sw = 0; phw ^= 1u; }
         }
-        __syncwarp();
-        if (++sw == n_wst) { sw = 0; phw ^= 1u; }
       }
-      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[8 + i] = dbg_acc[i];
     } else if (warp == 1) {
       // =============================== MMA issuer (one thread) ===============================
+      // Per slot: ONE barrier wait, 4 * kps MMAs, ONE commit; running addresses / descriptors, nothing looked up.
+      const uint32_t full0 = bar(kBarFull), full_end = bar(kBarFull + n_a);
+      const uint32_t d_empty0 = bar(kBarDEmpty), d_full0 = bar(kBarDFull);
+      const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);            // SBO 1024 B, descriptor version 1, SWIZZLE_128B
+      const uint32_t blo0 = (b_ring & 0x3FFFFu) >> 4, blo_step = b_bytes >> 4, blo_end = blo0 + (uint32_t)n_bst * blo_step;
+      const uint32_t a_t0 = tmem + acol0, a_step = (uint32_t)kps * 32u, a_end = a_t0 + (uint32_t)n_a * a_step;
+      uint32_t full_a = full0, pha = 0, b_lo = blo0, a_t = a_t0;
       int it = 0;
-      uint32_t pha = 0;   // one phase bit per stage (A in TMEM and B in smem of k-block kb both live in slot kb & 3)
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         const int tile = item / n_row_tiles;
         const int n_tok = a.tile_list[4 * tile + 2];
         const uint32_t idesc = make_idesc(max(16, (n_tok + 15) & ~15));
         const int db = it & 1;
-        const uint32_t d_t = tmem + (uint32_t)db * kGemmTokTile;
-        GEMM_DBG_T0();
-        mbar_wait(bar(kBarDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
-        GEMM_DBG_ADD(0);
+        const uint32_t d_t = tmem + (uint32_t)(db * a.tile_tokens);
+        mbar_wait(d_empty0 + 8u * (uint32_t)db, (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
         tc_fence_after();
-        for (int kb = 0; kb < nkb; ++kb) {
-          const int sa = kb & 3;
-          mbar_wait(bar(kBarAFull + sa), (pha >> sa) & 1u);
-          GEMM_DBG_ADD(1);
-          mbar_wait(bar(kBarBFull + sa), (pha >> sa) & 1u);
-          GEMM_DBG_ADD(2);
+        for (int kb0 = 0; kb0 < nkb; kb0 += kps) {
+          mbar_wait(full_a, pha);
           tc_fence_after();
-          const uint32_t a_t = tmem + kTmemACol + (uint32_t)sa * 32u;
-          const uint32_t b_s = s_bst[sa];
+          const int nreal = min(kps, nkb - kb0);
           if (elect_one()) {
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              tc_mma_ts(d_t, a_t + 8u * kk, make_bdesc(b_s + 32u * kk), idesc, (uint32_t)(kb | kk));
-            tc_commit(bar(kBarAEmpty + sa));     // frees the A stage (dequant warps) and the B stage (TMA producer) together
-            if (kb == nkb - 1) tc_commit(bar(kBarDFull + db));
+            for (int u = 0; u < 4; ++u) {
+              if (u < nreal) {
+                const uint64_t desc = ((uint64_t)desc_hi << 32) | (uint64_t)(b_lo + (uint32_t)u * blo_step);
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  tc_mma_ts(d_t, a_t + (uint32_t)(u * 32 + 8 * kk), desc + (uint64_t)(2 * kk), idesc, (uint32_t)(kb0 | u | kk));
+              }
+            }
+            tc_commit(full_a + 8u * (uint32_t)(kBarEmpty - kBarFull));   // frees the slot's A operand and activation stages
+            if (kb0 + kps >= nkb) tc_commit(d_full0 + 8u * (uint32_t)db);
           }
           __syncwarp();
-          pha ^= 1u << sa;
-          GEMM_DBG_ADD(3);
+          full_a += 8u;
+          a_t += a_step;
+          if (full_a == full_end) { full_a = full0; a_t = a_t0; pha ^= 1u; }
+          b_lo += (uint32_t)kps * blo_step;
+          if (b_lo == blo_end) b_lo = blo0;
         }
       }
-      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[16 + i] = dbg_acc[i];
+      (void)a_end;
     }
   }
-  else if (warp < 12) {
+  else if (warp < 4 + 4 * kDqGroups) {
     // =============================== dequant: NF4 -> fp16 A operand in TMEM ===============================
-    set_max_regs_inc<168>();
+    set_max_regs_inc<112>();
     const int q = warp & 3, g = (warp - 4) >> 2;
     const int r = q * 32 + lane;
-    const uint32_t lut_lane = pin(lut | ((uint32_t)(lane & 15) << 3));
-    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
+    const uint32_t lut_lane = pin(lut | ((uint32_t)lane << (FAST ? 2 : 3)));
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0;
     const uint32_t swz = (uint32_t)(r & 7);
-    int sw = 0, it = 0;
-    uint32_t phw = 0, use0 = 0, use1 = 0;   // use counts of this group's two A stages (g and g+2)
+    const uint32_t full0 = bar(kBarFull), empty0 = bar(kBarEmpty);
+    const int vkb = nslot * kps;                 // k-blocks per item including the padding of the last slot
+    const int spi = (nkb + 3) >> 2;              // raw-weight stages per item
+    // This group owns the virtual k-blocks c = g, g + 3, g + 6, ... of the CTA's run; (sl, sub, pha) track slot, sub-block and
+    // slot-use parity of the NEXT owned one, v its index inside the current item.
+    int sw = 0, it = 0, sl = 0, sub = 0, v = g;
+    uint32_t phw = 0, pha = 0;
+    while (sub >= kps) { sub -= kps; ++sl; }
+    sub = g % kps; sl = g / kps;                 // g < 3 <= n_a * kps
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
       const int e = a.tile_list[4 * tile];
@@ -382,59 +483,63 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       GEMM_DBG_ADD(0);
       const uint32_t m_st = pin(s_mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
-      for (int kb0 = 0; kb0 < nkb; kb0 += 4) {
-        mbar_wait(bar(kBarWFull + sw), phw);
-        GEMM_DBG_ADD(1);
-        const uint32_t wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
-#pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
-          const int j = g + 2 * jj;
-          const int kb = kb0 + j;
-          if (kb < nkb) {
-            float am;
-            if (nested) {
-              const float c = lds_f32(m_st + m_code2 + 4u * lds_u8(m_row + (uint32_t)kb));
-              am = __fadd_rn(__fmul_rn(c, kb < blk_hi ? a2_lo : a2_hi), off_e);
-            } else {
-              am = lds_f32(m_row + 4u * (uint32_t)kb);
-            }
-            const uint4 v0 = lds128(wrow + (((uint32_t)(2 * j) ^ swz) << 4));
-            const uint4 v1 = lds128(wrow + (((uint32_t)(2 * j + 1) ^ swz) << 4));
-            const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-            uint32_t regs[32];
-#pragma unroll
-            for (int wi = 0; wi < 8; ++wi)
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint32_t sh = i == 0 ? wd[wi] << 7 : wd[wi] >> (8 * i - 7);
-                const float2 f = lds_f32x2((sh & 0x7F80u) | lut_lane);
-                regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am), __fmul_rn(f.y, am));
-              }
-            uint32_t& use = jj ? use1 : use0;
-            GEMM_DBG_ADD(2);
-            mbar_wait(bar(kBarAEmpty + j), (use & 1u) ^ 1u);   // the MMAs that read this stage last time are done
-            GEMM_DBG_ADD(3);
-            ++use;
-            tc_fence_after();
-            tmem_st32(t_lane + kTmemACol + (uint32_t)j * 32u, regs);
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar(kBarAFull + j));
-            GEMM_DBG_ADD(4);
-          }
+      int ws = 0;                                // raw-weight stage of the item this warp has reached (not yet released)
+      mbar_wait(bar(kBarWFull + sw), phw);
+      uint32_t wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
+      for (; v < vkb; v += kDqGroups) {
+        const bool real = v < nkb;
+        const int ws_need = real ? (v >> 2) : spi - 1;
+        while (ws < ws_need) {                   // release the stages this warp is done with, wait for the next one
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(kBarWEmpty + sw));
+          if (++sw == n_wst) { sw = 0; phw ^= 1u; }
+          ++ws;
+          mbar_wait(bar(kBarWFull + sw), phw);
+          wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
         }
+        GEMM_DBG_ADD(1);
+        uint32_t regs[32];
+        if (real) {
+          float am;
+          if (nested) {
+            const float c = lds_f32(m_st + m_code2 + 4u * lds_u8(m_row + (uint32_t)v));
+            am = __fadd_rn(__fmul_rn(c, v < blk_hi ? a2_lo : a2_hi), off_e);
+          } else {
+            am = lds_f32(m_row + 4u * (uint32_t)v);
+          }
+          const uint32_t j2 = (uint32_t)(v & 3) * 2u;
+          const uint4 v0 = lds128(wrow + ((j2 ^ swz) << 4));
+          const uint4 v1 = lds128(wrow + (((j2 + 1u) ^ swz) << 4));
+          decode_block<FAST>(v0, v1, lut_lane, am, regs, (a.exp & 1) != 0);
+        }
+        GEMM_DBG_ADD(2);
+        mbar_wait(empty0 + 8u * (uint32_t)sl, pha ^ 1u);   // the MMAs that read this slot last time are done
+        GEMM_DBG_ADD(3);
+        if (real) {
+          tc_fence_after();
+          tmem_st32(t_lane + (uint32_t)(sl * kps + sub) * 32u, regs);
+          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+          tc_fence_before();
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(full0 + 8u * (uint32_t)sl);   // padding sub-blocks arrive too, so the slot completes
+        GEMM_DBG_ADD(4);
+        sub += kDqGroups;
+        while (sub >= kps) { sub -= kps; if (++sl == n_a) { sl = 0; pha ^= 1u; } }
+      }
+      v -= vkb;                                  // position of the next owned k-block inside the next item
+      while (ws < spi) {                         // release the item's remaining raw-weight stages
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(kBarWEmpty + sw));
         if (++sw == n_wst) { sw = 0; phw ^= 1u; }
+        if (++ws < spi) mbar_wait(bar(kBarWFull + sw), phw);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kBarMEmpty + mb));
     }
-    if (dbg_on && (warp == 4 || warp == 8)) for (int i = 0; i < 6; ++i) a.dbg[(warp == 4 ? 24 : 32) + i] = dbg_acc[i];
+    if (dbg_on && q == 0) for (int i = 0; i < 6; ++i) a.dbg[24 + 8 * g + i] = dbg_acc[i];
   } else {
     // =============================== epilogue: TMEM -> registers -> global, overlapped with the next tile's main loop ======
-    set_max_regs_dec<112>();
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
@@ -451,29 +556,40 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       const bool row_ok = n < a.w.rows;
       for (int c0 = 0; c0 < n_tok; c0 += 32) {
         uint32_t v[32];
-        tmem_ld32(t_lane + (uint32_t)(db * kGemmTokTile + c0), v);
+        tmem_ld32(t_lane + (uint32_t)(db * a.tile_tokens + c0), v);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         if (W13 && a.act == NF4MOE_ACT_SWIGLU_OAI) {
-          // rows 2j / 2j+1 (gate / up) sit in adjacent lanes.  Per column pair (i, i+1) the two lanes swap one value, after
-          // which the even lane owns (gate, up) of column i and the odd lane of column i+1: 16 shuffles, 16 activations
-          // and 16 stores per lane and chunk, all independent so they pipeline.
+          // Rows 2j / 2j+1 (gate / up) sit in adjacent lanes.  The products are rounded to fp16 (the reference stores the GEMM
+          // result as fp16 before the activation) and packed two tokens per register; the even lane then takes tokens
+          // 0..15 of the chunk and the odd lane tokens 16..31, so ONE exchange of 8 packed registers gives each lane the
+          // (gate, up) pairs of its 16 tokens.  Clamps run in half2 (exact), the sigmoid in fp32.
           __half* h = reinterpret_cast<__half*>(a.out);
           const int I = a.w.rows >> 1;
           const bool odd = lane & 1;
-          float gt[16], up[16];
+          uint32_t p[16];
 #pragma unroll
-          for (int pr = 0; pr < 16; ++pr) {
-            const float v0 = __half2float(__float2half_rn(__uint_as_float(v[2 * pr])));      // fp16 storage of the product
-            const float v1 = __half2float(__float2half_rn(__uint_as_float(v[2 * pr + 1])));
-            const float got = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
-            gt[pr] = odd ? got : v0;
-            up[pr] = odd ? v1 : got;
+          for (int i = 0; i < 16; ++i) p[i] = pack_half2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+          uint32_t gt[8], up[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? p[i] : p[8 + i], 1);
+            gt[i] = odd ? got : p[i];
+            up[i] = odd ? p[8 + i] : got;
           }
-          __half* dst = h + (long long)(row0 + c0 + (odd ? 1 : 0)) * I + (n >> 1);
+          const int t0 = c0 + (odd ? 16 : 0);                       // first token of this lane's 16
+          __half* dst = h + (long long)(row0 + t0) * I + (n >> 1);
+          const bool full = row_ok && t0 + 16 <= n_tok;
 #pragma unroll
-          for (int pr = 0; pr < 16; ++pr) {
-            const __half res = __float2half_rn(swiglu_oai(gt[pr], up[pr]));
-            if (row_ok && c0 + 2 * pr + (odd ? 1 : 0) < n_tok) dst[(long long)(2 * pr) * I] = res;
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t r2 = swiglu_oai_h2(gt[i], up[i]);
+            const __half lo = __ushort_as_half((unsigned short)(r2 & 0xFFFFu)), hi = __ushort_as_half((unsigned short)(r2 >> 16));
+            if (full) {
+              dst[(long long)(2 * i) * I] = lo;
+              dst[(long long)(2 * i + 1) * I] = hi;
+            } else if (row_ok) {
+              if (t0 + 2 * i < n_tok) dst[(long long)(2 * i) * I] = lo;
+              if (t0 + 2 * i + 1 < n_tok) dst[(long long)(2 * i + 1) * I] = hi;
+            }
           }
         } else if (W13) {
           __half* raw = reinterpret_cast<__half*>(a.out);
@@ -493,7 +609,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       if (lane == 0) mbar_arrive(bar(kBarDEmpty + db));
       GEMM_DBG_ADD(1);
     }
-    if (dbg_on && warp == 12) for (int i = 0; i < 6; ++i) a.dbg[40 + i] = dbg_acc[i];
+    if (dbg_on && q == 0) for (int i = 0; i < 6; ++i) a.dbg[56 + i] = dbg_acc[i];
   }
 
   // ---- teardown ----
@@ -540,19 +656,24 @@ inline long long*& gemm_debug_buffer() {
   return p;
 }
 
-inline int gemm_tile_tokens(int T, int k, int E) {
-  // small batches: 32-token tiles keep the activation stages at 4 KB; otherwise the full 256-column accumulator
-  return ((long long)T * k <= 32ll * E) ? 32 : kGemmTokTile;
+// Token-tile size (multiple of 32).  Small batches: 32-token tiles (4 KB activation stages, three 4-k-block slots in TMEM).
+// Otherwise 160: two 160-column accumulators leave 192 TMEM columns = three 2-k-block slots, and four 20 KB activation
+// stages fit beside the 64 KB decode table and two 23 KB flat-absmax stages.
+inline int gemm_tile_tokens(int T, int k, int E, bool nested = false) {
+  (void)nested;
+  if ((long long)T * k <= 32ll * E) return 32;
+  return 160;
 }
 
 template <bool W13>
 int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
-                const int32_t* tile_list, int T, int k, int E, int act, void* out, void* stream, char* err, size_t err_len,
-                int* launches) {
+                const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err,
+                size_t err_len, int* launches) {
   const char* name = W13 ? "gemm_w13" : "gemm_w2";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
   if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
   if (!W13 && !sorted_pairs) return fail(NF4MOE_EINVAL, "sorted_pairs required");
+  if (mode != NF4MOE_GEMM_EXACT && mode != NF4MOE_GEMM_FAST) return fail(NF4MOE_EINVAL, "mode must be NF4MOE_GEMM_EXACT or NF4MOE_GEMM_FAST");
   if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "cols must be a multiple of 64");
   if (W13 && (w->rows & 1)) return fail(NF4MOE_EINVAL, "w13 rows must be even");
   if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "absmax missing");
@@ -575,21 +696,30 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.meta = meta;
   a.tile_list = tile_list;
   a.act = act;
-  a.tile_tokens = gemm_tile_tokens(T, k, E);
+  a.tile_tokens = gemm_tile_tokens(T, k, E, w->absmax_f32 == nullptr);
+  a.kps = a.tile_tokens <= 32 ? 4 : 2;
+  a.n_a = std::min(kMaxAStages, (512 - 2 * a.tile_tokens) / (32 * a.kps));
+  a.want_b = a.tile_tokens <= 32 ? 12 : 4;
   a.dbg = gemm_debug_buffer();
+  static const int exp_env = getenv("NF4MOE_GEMM_EXP") ? atoi(getenv("NF4MOE_GEMM_EXP")) : 0;
+  a.exp = exp_env;
   CUtensorMap map_w, map_x;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
   if (!make_map_2d(&map_x, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, kGemmBoxRows))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
-  static thread_local bool attr_set = false;
-  auto kern = gemm_kernel<W13>;
-  if (!attr_set) {
+  CUtensorMap map_xw;   // whole-tile boxes [tile_tokens x 64] for full tiles
+  if (!make_map_2d(&map_xw, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, (uint32_t)a.tile_tokens))
+    return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activation tiles");
+  const bool fast = mode == NF4MOE_GEMM_FAST;
+  auto kern = fast ? gemm_kernel<W13, true> : gemm_kernel<W13, false>;
+  static thread_local bool attr_set[2] = {false, false};
+  if (!attr_set[fast]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
     if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
-    attr_set = true;
+    attr_set[fast] = true;
   }
-  kern<<<sms, kGemmThreads, kGemmSmemBytes, (cudaStream_t)stream>>>(a, map_w, map_x);
+  kern<<<sms, kGemmThreads, kGemmSmemBytes, (cudaStream_t)stream>>>(a, map_w, map_x, map_xw);
   ++*launches;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }
@@ -597,14 +727,14 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
 }
 
 inline int gemm_w13_entry(const void* x_sorted, const nf4moe_qweight* w13, const int32_t*, const int32_t* meta,
-                          const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted, void* stream, char* err,
-                          size_t err_len, int* launches) {
-  return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, h_sorted, stream, err, err_len, launches);
+                          const int32_t* tile_list, int T, int k, int E, int act, int mode, void* h_sorted, void* stream,
+                          char* err, size_t err_len, int* launches) {
+  return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, err, err_len, launches);
 }
 inline int gemm_w2_entry(const void* h_sorted, const nf4moe_qweight* w2, const int32_t*, const int32_t* sorted_pairs,
-                         const int32_t* meta, const int32_t* tile_list, int T, int k, int E, void* y, void* stream, char* err,
-                         size_t err_len, int* launches) {
-  return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, y, stream, err, err_len, launches);
+                         const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int mode, void* y, void* stream,
+                         char* err, size_t err_len, int* launches) {
+  return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, err, err_len, launches);
 }
 
 }  // namespace nf4moe

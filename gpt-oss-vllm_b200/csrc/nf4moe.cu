@@ -256,7 +256,7 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
                   int32_t* active_experts, int32_t* meta, int32_t* tile_list, int tile_rows, void* stream) {
   if (!ids || !expert_offsets || !sorted_pairs || !active_experts || !meta || T < 0 || k <= 0 || E <= 0 || E > 255)
     return fail(NF4MOE_EINVAL, "bucket: bad arguments (E must be <= 255)");
-  if (tile_rows == 0) tile_rows = gemm_tile_tokens(T, k, E);
+  if (tile_rows == 0) tile_rows = gemm_tile_tokens(T, k, E);   // the size that suits either absmax form
   if (tile_rows < 16 || tile_rows > 256 || tile_rows % 16)
     return fail(NF4MOE_EINVAL, "bucket: tile_rows must be a multiple of 16 in 16..256 (or 0 = automatic)");
   const long long n = (long long)T * k;
@@ -354,17 +354,17 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 }
 
 int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
-                           const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted,
-                           void* stream) {
-  return gemm_w13_entry(x_sorted, w13, expert_offsets, meta, tile_list, T, k, E, act, h_sorted, stream, g_err, sizeof(g_err),
-                        &g_launches);
+                           const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, int mode,
+                           void* h_sorted, void* stream) {
+  return gemm_w13_entry(x_sorted, w13, expert_offsets, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err,
+                        sizeof(g_err), &g_launches);
 }
 
 int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
                    const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
-                   void* y, void* stream) {
-  return gemm_w2_entry(h_sorted, w2, expert_offsets, sorted_pairs, meta, tile_list, T, k, E, y, stream, g_err, sizeof(g_err),
-                       &g_launches);
+                   int mode, void* y, void* stream) {
+  return gemm_w2_entry(h_sorted, w2, expert_offsets, sorted_pairs, meta, tile_list, T, k, E, mode, y, stream, g_err,
+                       sizeof(g_err), &g_launches);
 }
 
 // bucket -> (permute) -> w13 (+activation) -> w2 for the (row, slot) pairs of `ids` [T, k]; y fp16 [T*k, H] in pair order.
@@ -372,14 +372,18 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
                        int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches) {
   cudaStream_t st = (cudaStream_t)stream;
   if (regime == NF4MOE_REGIME_AUTO) regime = gemm_available() && T > kGemmAutoThreshold ? NF4MOE_REGIME_GEMM : NF4MOE_REGIME_GEMV;
-  const bool gemm = regime == NF4MOE_REGIME_GEMM;
-  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, 0, stream)) return rc;
+  if (regime != NF4MOE_REGIME_GEMV && regime != NF4MOE_REGIME_GEMM && regime != NF4MOE_REGIME_GEMM_FAST)
+    return fail(NF4MOE_EINVAL, "unknown regime %d", regime);
+  const bool gemm = regime != NF4MOE_REGIME_GEMV;
+  const int mode = regime == NF4MOE_REGIME_GEMM_FAST ? NF4MOE_GEMM_FAST : NF4MOE_GEMM_EXACT;
+  const int tile_rows = gemm ? gemm_tile_tokens(T, k, E, w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr) : 0;
+  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
   *launches += g_launches; g_launches = 0;
   __half* h_dst = act == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
   if (gemm) {
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
-    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act, h_dst, stream)) return rc;
+    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act, mode, h_dst, stream)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act, h_dst, stream)) return rc;
   }
@@ -392,7 +396,7 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     *launches += g_launches; g_launches = 0;
   }
   if (gemm) {
-    if (int rc = nf4moe_gemm_w2(ws.h, w2, ws.offsets, ws.sorted, ws.meta, ws.tiles, T, k, E, y, stream)) return rc;
+    if (int rc = nf4moe_gemm_w2(ws.h, w2, ws.offsets, ws.sorted, ws.meta, ws.tiles, T, k, E, mode, y, stream)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w2(ws.h, w2, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, y, stream)) return rc;
   }

@@ -93,9 +93,10 @@ def expert_w13(x: torch.Tensor, w13: NF4ExpertWeights, b: dict, T: int, k: int, 
     h = torch.zeros((T * k + 255) // 256 * 256 + 256, width, dtype=torch.float16, device=x.device)
     q = w13.c_struct(nested)
     with torch.cuda.device(x.device):
-        if regime == _lib.REGIME_GEMM:
+        if regime in (_lib.REGIME_GEMM, _lib.REGIME_GEMM_FAST):
+            mode = _lib.GEMM_FAST if regime == _lib.REGIME_GEMM_FAST else _lib.GEMM_EXACT
             _lib.check(lib.nf4moe_gemm_w13_swiglu(x.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
-                                                  b["meta"].data_ptr(), b["tile_list"].data_ptr(), T, k, E, act,
+                                                  b["meta"].data_ptr(), b["tile_list"].data_ptr(), T, k, E, act, mode,
                                                   h.data_ptr(), _stream_ptr(x.device)))
         else:
             _lib.check(lib.nf4moe_gemv_w13_swiglu(x.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
@@ -113,10 +114,11 @@ def expert_w2(h: torch.Tensor, w2: NF4ExpertWeights, b: dict, T: int, k: int, ne
     y = torch.zeros(T * k, w2.rows, dtype=torch.float16, device=h.device)
     q = w2.c_struct(nested)
     with torch.cuda.device(h.device):
-        if regime == _lib.REGIME_GEMM:
+        if regime in (_lib.REGIME_GEMM, _lib.REGIME_GEMM_FAST):
+            mode = _lib.GEMM_FAST if regime == _lib.REGIME_GEMM_FAST else _lib.GEMM_EXACT
             _lib.check(lib.nf4moe_gemm_w2(h.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
                                           b["sorted_pairs"].data_ptr(), b["meta"].data_ptr(), b["tile_list"].data_ptr(),
-                                          T, k, E, y.data_ptr(), _stream_ptr(h.device)))
+                                          T, k, E, mode, y.data_ptr(), _stream_ptr(h.device)))
         else:
             _lib.check(lib.nf4moe_gemv_w2(h.data_ptr(), C.byref(q), b["expert_offsets"].data_ptr(),
                                           b["sorted_pairs"].data_ptr(), b["active_experts"].data_ptr(),

@@ -58,7 +58,13 @@ extern "C" {
 /* regime selector for nf4moe_moe_forward */
 #define NF4MOE_REGIME_AUTO 0
 #define NF4MOE_REGIME_GEMV 1  /* decode: HBM-bound NF4 streaming kernel */
-#define NF4MOE_REGIME_GEMM 2  /* prefill: tcgen05 grouped GEMM */
+#define NF4MOE_REGIME_GEMM 2  /* tcgen05 grouped GEMM, NF4MOE_GEMM_EXACT operand */
+#define NF4MOE_REGIME_GEMM_FAST 3 /* tcgen05 grouped GEMM, NF4MOE_GEMM_FAST operand */
+
+/* how the tcgen05 kernels turn an NF4 block into the fp16 MMA operand */
+#define NF4MOE_GEMM_EXACT 0 /* fp16_rn(fp32(code) * fp32(absmax)): bit-identical to bnb dequantize_4bit */
+#define NF4MOE_GEMM_FAST 1  /* fp16(code) * fp16(absmax) in half2 arithmetic: ~2^-11 relative per weight, inside the MoE
+                               output tolerance (1e-2 abs / 2e-3 rel), half the shared-memory traffic of EXACT */
 
 /* One fused NF4 expert matrix set: E experts, each [rows, cols] row-major, cols % 64 == 0.
  * Quantisation blocks (64) run along the flat row-major index, so block b of expert e covers
@@ -143,14 +149,14 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 
 /* Prefill regime: the same two products as tcgen05 grouped GEMMs.  Weight rows are the MMA M dimension (128 per tile),
  * the token tiles of `tile_list` (built by nf4moe_bucket with tile_rows = 0) the N dimension; NF4 blocks are dequantised
- * bit-exactly (fp32 multiply, one rounding to fp16) straight into TENSOR MEMORY as the A operand, activations arrive by
- * TMA, accumulators live in TMEM.  x_sorted / h_sorted: fp16 [>= T*k rows, cols], rows grouped by expert. */
+ * (mode NF4MOE_GEMM_EXACT: fp32 multiply, one rounding to fp16, bit-exact; NF4MOE_GEMM_FAST: half2 arithmetic) straight
+ * into TENSOR MEMORY as the A operand, activations arrive by TMA, accumulators live in TMEM.  x_sorted / h_sorted: fp16 [>= T*k rows, cols], rows grouped by expert. */
 int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
-                           const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, void* h_sorted,
-                           void* stream);
+                           const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, int mode,
+                           void* h_sorted, void* stream);
 int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
                    const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
-                   void* y, void* stream);
+                   int mode, void* y, void* stream);
 
 /* ---- the whole layer ---------------------------------------------------------------------------------------------- */
 

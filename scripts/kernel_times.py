@@ -13,7 +13,7 @@ p.add_argument("--reps", type=int, default=5)
 p.add_argument("--experts", type=int, default=32)
 p.add_argument("--absmax", nargs="+", default=["nested", "flat"])
 p.add_argument("--cfg", type=int, nargs="+", default=[0])
-p.add_argument("--regime", default="gemv", choices=["gemv", "gemm"])
+p.add_argument("--regime", default="gemv", choices=["gemv", "gemm", "gemm_fast"])
 a = p.parse_args()
 if len(a.cfg) > 1:   # the library reads the override once per process: fan out
     import subprocess
@@ -44,8 +44,8 @@ for T in a.tokens:
     x = torch.randn(T, H, generator=g, device=dev).half()
     lg = torch.randn(T, E, generator=g, device=dev).half()
     ids, wts = pkg.ops.route_topk(lg, 4)
-    gemm = a.regime == "gemm"
-    regime = pkg.REGIME_GEMM if gemm else pkg.REGIME_GEMV
+    gemm = a.regime != "gemv"
+    regime = {"gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "gemm_fast": pkg.REGIME_GEMM_FAST}[a.regime]
     b = pkg.ops.bucket(ids, E, want_tiles=gemm)
     xin = pkg.ops.permute_rows(x, b, 4) if gemm else x
     ea = int(b["meta"][0].item())

@@ -31,7 +31,7 @@ for _ in range(a.layers):
     stack.append((w13, w2))
 x = torch.randn(a.tokens, H, generator=g, device=dev).half()
 lg = torch.randn(a.tokens, a.experts, generator=g, device=dev).half()
-regime = {"gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "auto": pkg.REGIME_AUTO}[a.regime]
+regime = {"gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "gemm_fast": pkg.REGIME_GEMM_FAST, "auto": pkg.REGIME_AUTO}[a.regime]
 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 for it in range(a.iters):
     if it == a.iters - 1:

@@ -18,6 +18,7 @@ p.add_argument("--experts", type=int, default=32)
 p.add_argument("--reps", type=int, default=5)
 p.add_argument("--absmax", default="flat")
 p.add_argument("--check", action="store_true")
+p.add_argument("--regime", default="gemm", choices=["gemm", "gemm_fast"])
 a = p.parse_args()
 pkg = importlib.import_module("gpt-oss-vllm_b200")
 dev = torch.device("cuda:0")
@@ -28,6 +29,7 @@ code2 = torch.from_numpy(orc.create_dynamic_map())
 w13 = pkg.NF4ExpertWeights.quantize((torch.randn(E, 2 * I, H, generator=g, device=dev) * 0.02).half(), code2)
 w2 = pkg.NF4ExpertWeights.quantize((torch.randn(E, H, I, generator=g, device=dev) * 0.02).half(), code2)
 nested = a.absmax == "nested"
+REG = pkg.REGIME_GEMM_FAST if a.regime == "gemm_fast" else pkg.REGIME_GEMM
 for T in a.tokens:
     x = torch.randn(T, H, generator=g, device=dev).half()
     lg = torch.randn(T, E, generator=g, device=dev).half()
@@ -40,8 +42,8 @@ for T in a.tokens:
         ids, wts = pkg.ops.route_topk(lg, k); ev[1].record()
         b = pkg.ops.bucket(ids, E); ev[2].record()
         xs = pkg.ops.permute_rows(x, b, k); ev[3].record()
-        h = pkg.ops.expert_w13(xs, w13, b, T, k, nested=nested, regime=pkg.REGIME_GEMM); ev[4].record()
-        y = pkg.ops.expert_w2(h, w2, b, T, k, nested=nested, regime=pkg.REGIME_GEMM); ev[5].record()
+        h = pkg.ops.expert_w13(xs, w13, b, T, k, nested=nested, regime=REG); ev[4].record()
+        y = pkg.ops.expert_w2(h, w2, b, T, k, nested=nested, regime=REG); ev[5].record()
         out = pkg.ops.combine(y, wts, ids, E); ev[6].record()
         torch.cuda.synchronize()
         if rep:
@@ -49,7 +51,7 @@ for T in a.tokens:
                 acc[n].append(ev[i].elapsed_time(ev[i + 1]) * 1e3)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        out2 = pkg.ops.moe_forward(x, w13, w2, k, router_logits=lg, regime=pkg.REGIME_GEMM, nested=nested)
+        out2 = pkg.ops.moe_forward(x, w13, w2, k, router_logits=lg, regime=REG, nested=nested)
         e1.record()
         torch.cuda.synchronize()
         if rep:
@@ -57,7 +59,7 @@ for T in a.tokens:
     flops = 2.0 * T * k * (2 * I * H + H * I)
     t13, t2 = min(acc["w13"]), min(acc["w2"])
     layer = min(tot)
-    print(f"T={T} {a.absmax}: " + " ".join(f"{n}={min(v):.1f}us" for n, v in acc.items()) + f" | layer {layer:.1f} us "
+    print(f"T={T} {a.regime} {a.absmax}: " + " ".join(f"{n}={min(v):.1f}us" for n, v in acc.items()) + f" | layer {layer:.1f} us "
           f"{T / layer:.3f} Mtok/s | gemms {flops / (t13 + t2) / 1e6:.1f} TFLOP/s ({flops / (t13 + t2) / 1e6 / 2250 * 100:.1f}% of 2250) "
           f"| layer {flops / layer / 1e6:.1f} TFLOP/s", flush=True)
     assert torch.equal(out, out2)

@@ -12,11 +12,13 @@ pytestmark = pytest.mark.gpu
 ATOL, RTOL = 1e-2, 2e-3   # north_star tolerance for MoE outputs
 
 
-def assert_moe_close(got: np.ndarray, ref: np.ndarray):
+def assert_moe_close(got: np.ndarray, ref: np.ndarray, intermediate: bool = False):
+    """north-star bar for MoE outputs.  `intermediate`: the activation output h can reach tens in magnitude, where one fp16
+    ulp already exceeds the absolute bar, so only the relative-L2 and the mixed per-element bounds apply to it."""
     got32, ref32 = got.astype(np.float32), ref.astype(np.float32)
     diff = np.abs(got32 - ref32)
     assert np.isfinite(got32).all()
-    assert diff.max() <= ATOL, f"max-abs {diff.max()}"
+    assert intermediate or diff.max() <= ATOL, f"max-abs {diff.max()}"
     rel = np.linalg.norm(got32 - ref32) / max(np.linalg.norm(ref32), 1e-12)
     assert rel <= RTOL, f"rel {rel}"
     assert np.all(diff <= ATOL + RTOL * np.abs(ref32))
@@ -198,7 +200,7 @@ def test_gemv_stages_vs_oracle(pkg, cuda_device, T, nested):
             continue
         xe = x[rows // k]
         h_ref = orc.swiglu_oai(orc._mm_f16_f32acc(xe, d13[e]).astype(np.float16).astype(np.float32)).astype(np.float16)
-        assert_moe_close(h[off[e]:off[e + 1]], h_ref)
+        assert_moe_close(h[off[e]:off[e + 1]], h_ref, intermediate=True)
         y_ref = orc._mm_f16_f32acc(h[off[e]:off[e + 1]], d2[e]).astype(np.float16)
         assert_moe_close(y[rows], y_ref)
 
@@ -398,16 +400,17 @@ def test_errors_are_loud(pkg, cuda_device):
 
 
 # ------------------------------------------------------------------------------------------------- prefill regime (tcgen05)
-def _gemm_stage_check(pkg, dev, T, E, H, I, k, nested, seed):
-    st13, st2, w13, w2 = make_layer(pkg, dev, seed, E, H, I)
+def _gemm_stage_check(pkg, dev, T, E, H, I, k, nested, seed, regime=None, std=0.05):
+    regime = pkg.REGIME_GEMM if regime is None else regime
+    st13, st2, w13, w2 = make_layer(pkg, dev, seed, E, H, I, std)
     rng = np.random.default_rng(200 + T)
     x = rng.standard_normal((T, H)).astype(np.float16)
     ids = np.stack([rng.choice(E, size=k, replace=False) for _ in range(T)]).astype(np.int32)
     b = pkg.ops.bucket(torch.from_numpy(ids).to(dev), E)
     xd = torch.from_numpy(x).to(dev)
     xs = pkg.ops.permute_rows(xd, b, k)
-    h = pkg.ops.expert_w13(xs, w13, b, T, k, nested=nested, regime=pkg.REGIME_GEMM)
-    y = pkg.ops.expert_w2(h, w2, b, T, k, nested=nested, regime=pkg.REGIME_GEMM).cpu().numpy()
+    h = pkg.ops.expert_w13(xs, w13, b, T, k, nested=nested, regime=regime)
+    y = pkg.ops.expert_w2(h, w2, b, T, k, nested=nested, regime=regime).cpu().numpy()
     h = h.cpu().numpy()
     sp = b["sorted_pairs"].cpu().numpy()[:T * k]
     off = b["expert_offsets"].cpu().numpy()
@@ -419,7 +422,7 @@ def _gemm_stage_check(pkg, dev, T, E, H, I, k, nested, seed):
             continue
         xe = x[rows // k]
         h_ref = orc.swiglu_oai(orc._mm_f16_f32acc(xe, d13[e]).astype(np.float16).astype(np.float32)).astype(np.float16)
-        assert_moe_close(h[off[e]:off[e + 1]], h_ref)
+        assert_moe_close(h[off[e]:off[e + 1]], h_ref, intermediate=True)
         y_ref = orc._mm_f16_f32acc(h[off[e]:off[e + 1]], d2[e]).astype(np.float16)
         assert_moe_close(y[rows], y_ref)
 
@@ -427,10 +430,21 @@ def _gemm_stage_check(pkg, dev, T, E, H, I, k, nested, seed):
 @pytest.mark.parametrize("T,E,H,I,k", [(3, 8, 64, 64, 2), (40, 8, 256, 192, 4), (300, 8, 256, 192, 4), (700, 4, 192, 320, 2),
                                        (1100, 4, 128, 64, 1)])
 @pytest.mark.parametrize("nested", [False, True])
-def test_gemm_stages_vs_oracle(pkg, cuda_device, T, E, H, I, k, nested):
+@pytest.mark.parametrize("fast", [False, True])
+def test_gemm_stages_vs_oracle(pkg, cuda_device, T, E, H, I, k, nested, fast):
     """tcgen05 grouped GEMMs (w13+SwiGLU, w2) against the oracle's per-expert fp16 matmul: ragged token tiles, row tiles
-    that end inside the next expert (rows % 128 != 0), K tails that are not a multiple of the 4-block raw stage."""
-    _gemm_stage_check(pkg, cuda_device, T, E, H, I, k, nested, 51)
+    that end inside the next expert (rows % 128 != 0), K tails that are not a multiple of the 4-block raw stage.  Both
+    operand modes: EXACT (bit-exact dequant) and FAST (half2 arithmetic) must meet the north-star MoE tolerance."""
+    _gemm_stage_check(pkg, cuda_device, T, E, H, I, k, nested, 51, pkg.REGIME_GEMM_FAST if fast else pkg.REGIME_GEMM)
+
+
+@pytest.mark.parametrize("T", [16, 64, 8192])
+def test_gemm_full_size_k_2880(pkg, cuda_device, T):
+    """the real K = 2880 (45 k-blocks: 11 raw stages + a 1-block tail, A-stage ring wrapping inside an item) on a few
+    experts, decode-sized and prefill-sized token tiles, both operand modes."""
+    E, H, I, k = 4, 2880, 256, 2
+    for fast in (False, True):
+        _gemm_stage_check(pkg, cuda_device, T, E, H, I, k, True, 59, pkg.REGIME_GEMM_FAST if fast else pkg.REGIME_GEMM, std=0.02)
 
 
 @pytest.mark.parametrize("T,E,H,I,k", [(65, 32, 128, 128, 4), (333, 8, 192, 128, 4), (1024, 32, 256, 128, 4)])
@@ -450,6 +464,9 @@ def test_moe_forward_gemm_regime_vs_oracle(pkg, cuda_device, T, E, H, I, k):
     assert_moe_close(out.cpu().numpy(), out_v.cpu().numpy())
     out_a = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_AUTO)
     assert torch.equal(out_a, out)
+    # FAST operand mode: same layer, half2-arithmetic dequant, still inside the north-star tolerance of the oracle
+    out_f = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_GEMM_FAST)
+    assert_moe_close(out_f.cpu().numpy(), ref)
 
 
 def test_gemm_operand_is_bit_exact_dequant(pkg, cuda_device):
