@@ -44,6 +44,8 @@ def parse():
     p.add_argument("--experts", type=int, default=32)
     p.add_argument("--absmax", default="nested", choices=["nested", "flat"])
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-prefill", action="store_true", help="skip the extra 8192-token prefill measurement")
+    p.add_argument("--prefill-tokens", type=int, default=8192)
     p.add_argument("--cpu-tokens", type=int, default=16)
     return p.parse_args()
 
@@ -172,6 +174,53 @@ def make_stack(pkg, dev, layers, E, code2):
         stack.append((w13, w2))
     torch.cuda.synchronize(dev)
     return stack
+
+
+def prefill_section(pkg, dev, layer, E, nested, T=8192, reps=5):
+    """BASELINE.json configs[2] beside the headline: ONE gpt-oss-20b MoE layer, 8192 tokens, tcgen05 grouped-GEMM regime, both
+    operand modes; CUDA events around the whole layer call and around the two GEMM kernels alone."""
+    import torch
+    w13, w2 = layer
+    g = torch.Generator(device=dev).manual_seed(SEED + 2)
+    x = torch.randn(T, H, generator=g, device=dev).half()
+    lg = torch.randn(T, E, generator=g, device=dev).half()
+    flops = 2.0 * T * TOP_K * (2 * I * H + H * I)
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            mp = json.load(f)
+        burst, sust = float(mp["bf16_tflops"]), float(mp.get("bf16_tflops_sustained", mp["bf16_tflops"]))
+    except Exception:
+        burst, sust = 1590.0, 1400.0
+    out = {"workload": f"one gpt-oss-20b NF4 MoE layer, T={T} tokens prefill (BASELINE.json configs[2])", "flops_per_layer": flops,
+           "peak_tflops": {"nominal_dense_fp16": 2250.0, "measured_bf16_burst": burst, "measured_bf16_sustained": sust}}
+    ws = pkg.ops.get_workspace(dev, T, E, H, I, TOP_K)
+    for name, regime in (("exact", pkg.REGIME_GEMM), ("fast", pkg.REGIME_GEMM_FAST)):
+        o = torch.empty(T, H, dtype=torch.float16, device=dev)
+        tl, tg = [], []
+        for rep in range(reps + 2):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            pkg.ops.moe_forward(x, w13, w2, TOP_K, router_logits=lg, out=o, workspace=ws, nested=nested, regime=regime)
+            e1.record()
+            torch.cuda.synchronize()
+            ids, wts = pkg.ops.route_topk(lg, TOP_K)
+            b = pkg.ops.bucket(ids, E)
+            xs = pkg.ops.permute_rows(x, b, TOP_K)
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            hbuf = pkg.ops.expert_w13(xs, w13, b, T, TOP_K, nested=nested, regime=regime)
+            pkg.ops.expert_w2(hbuf, w2, b, T, TOP_K, nested=nested, regime=regime)
+            a1.record()
+            torch.cuda.synchronize()
+            if rep >= 2:
+                tl.append(e0.elapsed_time(e1))
+                tg.append(a0.elapsed_time(a1))
+        ml, mg = statistics.mean(tl), statistics.mean(tg)
+        out[name] = {"layer_ms": ml, "tokens_per_s": T / (ml * 1e-3), "layer_tflops": flops / (ml * 1e-3) / 1e12,
+                     "gemm_kernels_ms": mg, "gemm_tflops": flops / (mg * 1e-3) / 1e12,
+                     "gemm_frac_of_nominal": flops / (mg * 1e-3) / 1e12 / 2250.0, "gemm_frac_of_measured_sustained": flops / (mg * 1e-3) / 1e12 / sust}
+    out["operand_modes"] = "exact = fp16_rn(fp32 code x fp32 absmax), bit-identical to bnb dequantize_4bit; fast = half2 arithmetic"
+    return out
 
 
 def state_to_cpu(w, e):
@@ -305,8 +354,16 @@ def run_ours(args):
     b2 = ea * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2
     d13, d2 = statistics.mean(t13) * 1e-3, statistics.mean(t2) * 1e-3
     layer_bytes = b13 + b2
+    traffic, traffic_src = None, None
+    try:   # dram bytes of this kernel at this configuration from the committed `ncu --set full` capture (never measured under ncu here)
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            tj = json.load(f)
+        if T == 64 and E == 32 and nested:
+            traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
+    except Exception:
+        pass
     roof = {"bound": "hbm", "kernel": "gemv_kernel<NT=2,W13> (w13 NF4 GEMV + SwiGLU)", "achieved": b13 / d13 / 1e9, "peak": peak,
-            "unit": "GB/s", "frac": b13 / d13 / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+            "unit": "GB/s", "frac": b13 / d13 / 1e9 / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": b13, "avg_launch_us": d13 * 1e6, "frac_of_nominal_8TBs": b13 / d13 / 8e12,
             "w2_kernel": {"achieved": b2 / d2 / 1e9, "frac": b2 / d2 / 1e9 / peak, "avg_launch_us": d2 * 1e6,
                           "algorithmic_bytes_per_launch": b2},
@@ -326,6 +383,9 @@ def run_ours(args):
                     "api": "B200NF4MoEMethod.apply_legacy(layer, x, router_logits, top_k) x 24, pinned host buffers"},
             "gpu_launches": launches_per_layer * L * K, "launches_per_layer": launches_per_layer,
             "roofline": roof, "step_ms_min_max": [min(step_ms), max(step_ms)]}
+
+    if not args.no_prefill:
+        line["prefill"] = prefill_section(pkg, dev, stack[0], E, nested)
 
     if not args.no_cpu_baseline:
         st13 = [state_to_cpu(stack[0][0], e) for e in range(E)]

@@ -42,7 +42,7 @@ constexpr int kGemmBoxRows = 32;        // token rows per activation TMA box (a 
 constexpr int kMaxAStages = 12;         // A (dequantised weights) stages in TMEM, 32 columns each: (512 - 2*tile) / 32
 constexpr int kMaxBStages = 12;         // activation stages in shared memory (own ring, own empty barriers)
 constexpr int kGemmWPrefetch = 6;       // raw-weight stages requested into L2 ahead of the shared-memory ring
-constexpr int kMaxWStages = 4;
+constexpr int kMaxWStages = 6;
 constexpr uint32_t kWStageBytes = 128 * 128;   // raw NF4: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kGemmSmemBytes = 232448 - 1024;  // dynamic part; the kernel's static __shared__ control block takes the rest
 constexpr uint32_t kGemmLutBytes = 65536;
@@ -494,7 +494,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           if (lane == 0) mbar_arrive(bar(kBarWEmpty + sw));
           if (++sw == n_wst) { sw = 0; phw ^= 1u; }
           ++ws;
-          mbar_wait(bar(kBarWFull + sw), phw);
+          if (!(a.exp & 8)) mbar_wait(bar(kBarWFull + sw), phw);
           wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
         }
         GEMM_DBG_ADD(1);
