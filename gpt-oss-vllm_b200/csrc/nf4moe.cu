@@ -260,7 +260,7 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
   if (tile_rows < 16 || tile_rows > 256 || tile_rows % 16)
     return fail(NF4MOE_EINVAL, "bucket: tile_rows must be a multiple of 16 in 16..256 (or 0 = automatic)");
   const long long n = (long long)T * k;
-  const size_t smem = (size_t)((n + 31) & ~31ll);
+  const size_t smem = (size_t)((n + 127) & ~127ll);
   if (smem > 200 * 1024) return fail(NF4MOE_EINVAL, "bucket: T*k = %lld exceeds the single-CTA limit of 204800 pairs", n);
   static thread_local bool attr_set = false;
   if (!attr_set) {

@@ -81,16 +81,26 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
   __shared__ int s_count[256];
   __shared__ int s_off[257];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int n_pad = (n_pairs + 31) & ~31;
+  const int n_pad = (n_pairs + 127) & ~127;
   for (int i = tid; i < n_pad; i += kBucketThreads) {
     int e = i < n_pairs ? ids[i] : -1;
     s_ids[i] = (e >= 0 && e < E) ? (uint8_t)e : (uint8_t)0xFF;
   }
   if (tid < 256) s_count[tid] = 0;
   __syncthreads();
+  // ids are read four at a time (one 32-bit shared-memory load per lane = 128 pairs per warp iteration); n_pad128 rounds
+  // the scan up to whole iterations, the tail is 0xFF (never matches)
+  const int n_pad128 = (n_pairs + 127) & ~127;
   for (int e = warp; e < E; e += 32) {
+    const uint32_t pat = 0x01010101u * (uint32_t)e;
     int c = 0;
-    for (int i = lane; i < n_pad; i += 32) c += __popc(__ballot_sync(0xffffffffu, s_ids[i] == e));
+    for (int i = lane * 4; i < n_pad128; i += 128) {
+      const uint32_t x = *reinterpret_cast<const uint32_t*>(s_ids + i) ^ pat;   // a zero byte = a match
+      const uint32_t z = __vcmpeq4(x, 0u);                                        // 0xFF in matching bytes
+      c += __popc(z) >> 3;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
     if (lane == 0) s_count[e] = c;
   }
   __syncthreads();
@@ -134,12 +144,22 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
     meta[0] = na; meta[1] = s_off[E]; meta[2] = nt; meta[3] = mx;
   }
   for (int e = warp; e < E; e += 32) {
+    const uint32_t pat = 0x01010101u * (uint32_t)e;
     int run = s_off[e];
-    for (int i = lane; i < n_pad; i += 32) {
-      const bool hit = s_ids[i] == e;
-      const unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (hit) sorted_pairs[run + __popc(m & ((1u << lane) - 1u))] = i;
-      run += __popc(m);
+    for (int i = lane * 4; i < n_pad128; i += 128) {
+      const uint32_t z = __vcmpeq4(*reinterpret_cast<const uint32_t*>(s_ids + i) ^ pat, 0u);
+      const int mine = __popc(z) >> 3;                      // matches among this lane's four pairs
+      int inc = mine;                                        // inclusive prefix over the lanes (pair order = lane-major)
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int nb = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += nb;
+      }
+      int pos = run + inc - mine;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if ((z >> (8 * j)) & 1u) sorted_pairs[pos++] = i + j;
+      run += __shfl_sync(0xffffffffu, inc, 31);
     }
   }
 }

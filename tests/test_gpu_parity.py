@@ -485,3 +485,23 @@ def test_gemm_operand_is_bit_exact_dequant(pkg, cuda_device):
     for t in range(T):
         e = 0 if t < T // 2 else 1
         assert np.array_equal(raw[t].view(np.uint16), d13[e][:, t].view(np.uint16))
+
+
+# ------------------------------------------------------------------------------------------------- loader
+def test_loader_to_gpu_forward(pkg, cuda_device, tmp_path):
+    """synthetic checkpoint in the reference's on-disk key set -> loader -> kernels: dequant bit-exact, layer within tolerance."""
+    import importlib
+    import os
+    ld = importlib.import_module("gpt-oss-vllm_b200.loader")
+    E, H, I, k, T = 8, 128, 64, 2, 9
+    rng = np.random.default_rng(77)
+    st13, st2 = make_states(rng, E, 2 * I, H, 0.05), make_states(rng, E, H, I, 0.05)
+    path = os.path.join(tmp_path, "ckpt.safetensors")
+    ld.save_layer_experts(path, 3, st13, st2)
+    w13, w2 = ld.load_layer_experts([path], 3, E, H, I, device=cuda_device)
+    got = w13.dequantize(nested=True).cpu().numpy()
+    assert np.array_equal(got.view(np.uint16), np.stack([orc.dequant_state(s) for s in st13]).view(np.uint16))
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    out = pkg.ops.moe_forward(torch.from_numpy(x).to(cuda_device), w13, w2, k, router_logits=torch.from_numpy(lg).to(cuda_device))
+    assert_moe_close(out.cpu().numpy(), orc.moe_forward_from_states(x, lg, st13, st2, k=k))
