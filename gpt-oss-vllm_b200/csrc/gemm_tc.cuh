@@ -219,7 +219,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   __shared__ uint32_t s_tmem;
   __shared__ uint32_t s_wst[kMaxWStages], s_mst[2];
   __shared__ int s_nw, s_nb;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // Role index: the control warps take the HIGHEST hardware warp ids (16-19).  The sub-partition arbiter serves the highest
+  // warp id first, so as warps 0-3 the single-thread roles were starved of issue slots by the twelve dequant warps (every
+  // mbarrier / tcgen05 / TMA instruction of theirs took 100-300 cycles); `warp` below is the ROLE index (0-3 control, 4-15
+  // dequant, 16-19 epilogue), `warp & 3` is still the hardware TMEM lane quarter.  (a.exp & 16: old placement, for A/B timing.)
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int hw_warp = tid >> 5;
+  const int warp = (a.exp & 16) ? hw_warp : (hw_warp + 4) % (kGemmThreads / 32);
   const int nkb = a.w.nkb;
   const int n_a = a.n_a, kps = a.kps;
   const int nslot = (nkb + kps - 1) / kps;                  // slots per item (the last one may be partly padding)

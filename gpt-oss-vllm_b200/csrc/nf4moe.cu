@@ -9,6 +9,7 @@
 #include "ep.cuh"
 #include "gemm_tc.cuh"
 #include "gemv.cuh"
+#include "gemm_dec.cuh"
 #include "route.cuh"
 
 using namespace nf4moe;
@@ -356,6 +357,9 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
                            const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, int mode,
                            void* h_sorted, void* stream) {
+  if (dec_serves(T, k, E, mode))
+    return dec_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, h_sorted, stream, g_err, sizeof(g_err),
+                            &g_launches);
   return gemm_w13_entry(x_sorted, w13, expert_offsets, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err,
                         sizeof(g_err), &g_launches);
 }
@@ -363,6 +367,9 @@ int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, cons
 int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
                    const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
                    int mode, void* y, void* stream) {
+  if (dec_serves(T, k, E, mode))
+    return dec_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, y, stream, g_err, sizeof(g_err),
+                             &g_launches);
   return gemm_w2_entry(h_sorted, w2, expert_offsets, sorted_pairs, meta, tile_list, T, k, E, mode, y, stream, g_err,
                        sizeof(g_err), &g_launches);
 }
