@@ -23,11 +23,32 @@ namespace nf4moe {
 
 constexpr int kDecDqWarps = 16;
 constexpr int kDecThreads = (kDecDqWarps + 4 + 4) * 32;   // 768: dequant, epilogue warpgroup, control warpgroup
-constexpr int kDecMaxStages = 6;
-constexpr int kDecSlots = 3;                               // A-operand slots in TMEM (one stage = 4 k-blocks = 128 columns each)
+constexpr int kDecMaxRaw = 8;                              // raw-NF4 stages (16 KB each) in the shared-memory ring
+constexpr int kDecMaxB = 6;                                // activation stages (their own ring: they live until the MMAs retire)
+constexpr int kDecSlots = 3;                               // A-operand slots in TMEM: one stage = 4 k-blocks = 128 columns each
 constexpr int kDecAccCols = 32;                            // per accumulator (two of them)
-constexpr uint32_t kDecRawBytes = 128 * 128;               // raw NF4 of one stage
+constexpr uint32_t kDecRawBytes = 128 * 128;               // raw NF4 of one stage: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kDecSmemBytes = 232448 - 1024;
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+      : "memory");
+}
+
+// Activations [rows, cols] fp16 viewed as a 3-D tensor (64 inner, rows, cols / 64 k-blocks) so ONE box [64, box_rows, 4] lands the
+// four K-major 128B-swizzled UMMA tiles of a stage back to back (k-blocks past the end read as zero).
+inline bool make_map_x3d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_t rows, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return false;
+  const cuuint64_t dims[3] = {(cuuint64_t)kBlock, rows, cols / kBlock};
+  const cuuint64_t strides[2] = {cols * 2, (cuuint64_t)kBlock * 2};
+  const cuuint32_t box[3] = {(cuuint32_t)kBlock, box_rows, 4};
+  const cuuint32_t es[3] = {1, 1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 
 struct DecArgs {
   QW w;
@@ -37,34 +58,46 @@ struct DecArgs {
   const int32_t* tile_list;
   int act;
   long long* dbg;
+  int max_raw, max_b;   // ring caps (tuning knobs NF4MOE_DEC_RAW / NF4MOE_DEC_B)
+  int b3d;              // the activation maps are the 3-D form (one TMA per stage) rather than 2-D (one per k-block)
+  int exp;              // timing experiments (NF4MOE_DEC_EXP; results are wrong when non-zero)
 };
 
 // barrier slots
-constexpr int kDbWFull = 0, kDbWEmpty = kDbWFull + kDecMaxStages, kDbAFull = kDbWEmpty + kDecMaxStages,
-              kDbAEmpty = kDbAFull + kDecSlots, kDbDFull = kDbAEmpty + kDecSlots, kDbDEmpty = kDbDFull + 2,
+//   RFull[i]  <- TMA bytes of raw stage i AND of the matching activation stage (one expect_tx): waited on by the 8 dequant warps
+//                that own the stage; the MMA thread never waits on it (its wait on AFull is causally after all 8 of theirs)
+//   REmpty[i] <- the 8 dequant warps, as soon as their 4 LDS.128 are done (the stage refills while they decode)
+//   AFull[s]  <- the 8 dequant warps, A operand of the stage written to TMEM slot s
+//   Done[c]   <- ONE tcgen05.commit per stage (ring of n_b = 3 or 6): frees A slot c % 3 for the dequant warps of stage + 3
+//                and activation stage c for the producer of stage + n_b
+constexpr int kDbRFull = 0, kDbREmpty = kDbRFull + kDecMaxRaw, kDbDone = kDbREmpty + kDecMaxRaw,
+              kDbAFull = kDbDone + kDecMaxB, kDbDFull = kDbAFull + kDecSlots, kDbDEmpty = kDbDFull + 2,
               kDbMFull = kDbDEmpty + 2, kDbMEmpty = kDbMFull + 2, kNumDecBars = kDbMEmpty + 2;
 
-// Warp roles (768 threads, one persistent CTA per SM):
+// Warp roles (768 threads, one persistent CTA per SM).  cs = the CTA's running stage counter (12 per item for K = 2880); the
+// rings follow it: raw stage cs % n_raw, activation stage cs % n_b, A slot cs % 3.
 //   warps 0-15   dequant: q = warp & 3 (TMEM lane quarter = weight rows 32q..32q+31), hh = (warp >> 2) & 1 (k-blocks 2hh, 2hh+1
-//                of a stage), pp = warp >> 3 (stages with running index cs = pp mod 2)
+//                of a stage), pp = warp >> 3 (stages cs = pp mod 2).  Per owned stage: wait RFull, 4 x LDS.128, arrive REmpty at
+//                once, decode, wait Done of stage cs - 3, 2 x tcgen05.st, arrive AFull
 //   warps 16-19  epilogue
-//   warp 20      TMA producer (absmax per item, raw NF4 + activations per stage)
-//   warp 21      TMEM allocator and the MMA-issuing thread
-template <bool W13>
+//   warp 20      TMA producer: absmax per item; raw NF4 + activations per stage
+//   warp 21      TMEM allocator and the MMA-issuing thread: per stage ONE wait, <= 16 tcgen05.mma, ONE commit
+template <bool W13, bool DBG>
 __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, const __grid_constant__ CUtensorMap map_w,
                                                             const __grid_constant__ CUtensorMap map_x16,
                                                             const __grid_constant__ CUtensorMap map_x32) {
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumDecBars];
   __shared__ uint32_t s_tmem;
-  __shared__ uint32_t s_st[kDecMaxStages], s_mst[2];
-  __shared__ int s_nst;
+  __shared__ uint32_t s_raw[kDecMaxRaw], s_b0, s_mst[2];
+  __shared__ int s_nraw;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nkb = a.w.nkb;
   const int nst = (nkb + 3) >> 2;                       // stages per item (the last one may be partly padding)
   const bool nested = a.w.absmax_f32 == nullptr;
   const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
-  const uint32_t stage_bytes = kDecRawBytes + 4u * (uint32_t)bmax * 128u;
+  const uint32_t b_stage = 4u * (uint32_t)bmax * 128u;  // activations of one stage: 4 k-blocks x N x 128 B
+  const int n_b = bmax == 16 ? 6 : 3;                   // activation stages (48 KB either way, ONE contiguous block); multiple of 3
   const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
   const uint32_t m_code2 = (m_tile + 15u) & ~15u;
   const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
@@ -89,12 +122,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       cur[best] += bytes;
       return at;
     };
-    int im = 0, is = 0;
+    int im = 0, ir = 0;
     for (int i = 0; i < 2; ++i) { const uint32_t at = place(m_bytes); if (at) s_mst[im++] = at; }
-    for (int i = 0; i < kDecMaxStages; ++i) { const uint32_t at = place(stage_bytes); if (at) s_st[is++] = at; else break; }
-    s_nst = (im == 2 && is >= 2) ? is : 0;
-    for (int i = 0; i < kDecMaxStages; ++i) { mbar_init(bar(kDbWFull + i), 1); mbar_init(bar(kDbWEmpty + i), kDecDqWarps / 2 + 1); }
-    for (int i = 0; i < kDecSlots; ++i) { mbar_init(bar(kDbAFull + i), kDecDqWarps / 2); mbar_init(bar(kDbAEmpty + i), 1); }
+    const uint32_t b_at = place((uint32_t)n_b * b_stage);
+    s_b0 = b_at;
+    for (int i = 0; i < min(kDecMaxRaw, a.max_raw); ++i) { const uint32_t at = place(kDecRawBytes); if (at) s_raw[ir++] = at; else break; }
+    s_nraw = (im == 2 && b_at != 0u && ir >= 2) ? ir : 0;
+    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecDqWarps / 2); }
+    for (int i = 0; i < kDecMaxB; ++i) mbar_init(bar(kDbDone + i), 1);
+    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecDqWarps / 2);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kDbDFull + i), 1); mbar_init(bar(kDbDEmpty + i), 4);
       mbar_init(bar(kDbMFull + i), 1); mbar_init(bar(kDbMEmpty + i), kDecDqWarps);
@@ -113,22 +149,30 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const int n_st = s_nst;
+  const int n_raw = s_nraw;
+  const uint32_t b_ring = s_b0;
   const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
-  const int n_items = n_st > 0 ? a.meta[2] * n_row_tiles : 0;
+  const int n_items = n_raw > 0 ? a.meta[2] * n_row_tiles : 0;
   const uint32_t acol0 = 2u * kDecAccCols;   // TMEM: accumulators at columns 0 and 32, A slots after them
+  const bool dbg_on = DBG && a.dbg != nullptr && blockIdx.x == 0 && lane == 0;   // DBG = false: every counter below folds away
+  long long dbg_acc[6] = {0, 0, 0, 0, 0, 0};
 
   if (warp < kDecDqWarps) {
     // =============================== dequant: NF4 -> fp16 A operand in TMEM ===============================
     const int q = warp & 3, hh = (warp >> 2) & 1, pp = warp >> 3;
     const int r = q * 32 + lane;
     const uint32_t lut_lane = pin(lut | ((uint32_t)lane << 2));
-    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0 + (uint32_t)hh * 64u;
-    const uint32_t swz = (uint32_t)(r & 7);
-    const uint32_t wfull0 = bar(kDbWFull), wempty0 = bar(kDbWEmpty), afull0 = bar(kDbAFull), aempty0 = bar(kDbAEmpty);
-    // running stage counter cs = it * nst + st; this warp owns cs = pp (mod 2); (sw, phw) / (slot, pha) follow cs
-    int sw = pp, slot = pp, st = pp, it = 0;
-    uint32_t phw = 0, pha = 0;
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0;
+    const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), afull0 = bar(kDbAFull), done0 = bar(kDbDone);
+    // this lane's four 16-byte chunks of a raw stage row (128B swizzle: chunk c of row r sits at chunk c ^ (r & 7))
+    const uint32_t row_off = (uint32_t)r * 128u, swz = (uint32_t)(r & 7);
+    const uint32_t ch0 = row_off + (((uint32_t)(hh * 4) ^ swz) << 4), ch1 = row_off + (((uint32_t)(hh * 4 + 1) ^ swz) << 4);
+    const uint32_t ch2 = row_off + (((uint32_t)(hh * 4 + 2) ^ swz) << 4), ch3 = row_off + (((uint32_t)(hh * 4 + 3) ^ swz) << 4);
+    // this warp owns stages cs = pp (mod 2).  Running ring positions of its NEXT stage: raw stage sw, A slot `slot`, and the Done
+    // barrier of stage cs - 3 (index dn, parity pdn; "stage -3 .. -1" = the phase before the first one, which a fresh barrier
+    // reports complete)
+    int sw = pp, slot = pp, dn = pp + n_b - 3, st = pp, it = 0;
+    uint32_t phw = 0, pdn = 1;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
       const int e = a.tile_list[4 * tile];
@@ -145,53 +189,61 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         off_e = __ldg(a.w.offset + e);
         blk_hi = ((i2 + 1) << 8) - blk0;
       }
+      GEMM_DBG_T0();
       mbar_wait(bar(kDbMFull + mb), (uint32_t)(it >> 1) & 1u);
+      GEMM_DBG_ADD(0);
       const uint32_t m_st = pin(s_mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       for (; st < nst; st += 2) {
-        mbar_wait(wfull0 + 8u * (uint32_t)sw, phw);
-        const uint32_t wrow = pin(s_st[sw]) + (uint32_t)r * 128u;
-        const uint32_t t_slot = t_lane + (uint32_t)slot * 128u;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          const int kb = st * 4 + hh * 2 + j;
-          const bool real = kb < nkb;
-          uint32_t regs[32];
-          if (real) {
-            float am;
-            if (nested) {
-              const float c = lds_f32(m_st + m_code2 + 4u * lds_u8(m_row + (uint32_t)kb));
-              am = __fadd_rn(__fmul_rn(c, kb < blk_hi ? a2_lo : a2_hi), off_e);
-            } else {
-              am = lds_f32(m_row + 4u * (uint32_t)kb);
-            }
-            const uint32_t c2 = (uint32_t)(hh * 2 + j) * 2u;
-            const uint4 v0 = lds128(wrow + ((c2 ^ swz) << 4));
-            const uint4 v1 = lds128(wrow + (((c2 + 1u) ^ swz) << 4));
-            decode_block<true>(v0, v1, lut_lane, am, regs);
-          }
-          if (j == 0) {
-            mbar_wait(aempty0 + 8u * (uint32_t)slot, pha ^ 1u);   // the MMAs that read this slot three stages ago are done
-            tc_fence_after();
-          }
-          if (real) tmem_st32(t_slot + (uint32_t)j * 32u, regs);
+        mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
+        GEMM_DBG_ADD(1);
+        const uint32_t wst = pin(s_raw[sw]);
+        const int kb0 = st * 4 + hh * 2;
+        const bool real0 = kb0 < nkb && !(a.exp & 16), real1 = kb0 + 1 < nkb && !(a.exp & 24);
+        uint4 v0 = lds128(wst + ch0), v1 = lds128(wst + ch1), v2 = lds128(wst + ch2), v3 = lds128(wst + ch3);
+        float am0 = 0.f, am1 = 0.f;
+        if (nested) {
+          const uint32_t c0 = lds_u8(m_row + (uint32_t)min(kb0, nkb - 1)), c1 = lds_u8(m_row + (uint32_t)min(kb0 + 1, nkb - 1));
+          am0 = __fadd_rn(__fmul_rn(lds_f32(m_st + m_code2 + 4u * c0), kb0 < blk_hi ? a2_lo : a2_hi), off_e);
+          am1 = __fadd_rn(__fmul_rn(lds_f32(m_st + m_code2 + 4u * c1), kb0 + 1 < blk_hi ? a2_lo : a2_hi), off_e);
+        } else {
+          am0 = lds_f32(m_row + 4u * (uint32_t)min(kb0, nkb - 1));
+          am1 = lds_f32(m_row + 4u * (uint32_t)min(kb0 + 1, nkb - 1));
         }
+        // the raw bytes are in registers: hand the stage back now (mbarrier.arrive has release semantics: the loads above
+        // are performed before the arrival is visible), so its refill overlaps the decode
+        __syncwarp();
+        if (lane == 0) mbar_arrive(rempty0 + 8u * (uint32_t)sw);
+        const uint32_t t_half = t_lane + (uint32_t)slot * 128u + (uint32_t)hh * 64u;
+        uint32_t regs[32];
+        if (real0) decode_block<true>(v0, v1, lut_lane, am0, regs, (a.exp & 2) != 0);
+        GEMM_DBG_ADD(2);
+        mbar_wait(done0 + 8u * (uint32_t)dn, pdn);          // the MMAs of stage cs - 3, which read this A slot, are done
+        tc_fence_after();
+        GEMM_DBG_ADD(3);
+        if (real0) tmem_st32(t_half, regs);
+        if (real1) {
+          decode_block<true>(v2, v3, lut_lane, am1, regs, (a.exp & 2) != 0);
+          tmem_st32(t_half + 32u, regs);
+        }
+        GEMM_DBG_ADD(4);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(afull0 + 8u * (uint32_t)slot);
-          mbar_arrive(wempty0 + 8u * (uint32_t)sw);
-        }
+        if (lane == 0) mbar_arrive(afull0 + 8u * (uint32_t)slot);
+        GEMM_DBG_ADD(5);
         sw += 2;
-        if (sw >= n_st) { sw -= n_st; phw ^= 1u; }
+        if (sw >= n_raw) { sw -= n_raw; phw ^= 1u; }
         slot += 2;
-        if (slot >= kDecSlots) { slot -= kDecSlots; pha ^= 1u; }
+        if (slot >= kDecSlots) slot -= kDecSlots;
+        dn += 2;
+        if (dn >= n_b) { dn -= n_b; pdn ^= 1u; }
       }
       st -= nst;
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kDbMEmpty + mb));
     }
+    if (dbg_on && (warp == 0 || warp == 13)) for (int i = 0; i < 6; ++i) a.dbg[(warp ? 8 : 0) + i] = dbg_acc[i];
   } else if (warp < kDecDqWarps + 4) {
     // =============================== epilogue: TMEM -> registers -> global, overlapped with the next item ===============
     const int q = warp & 3;
@@ -252,19 +304,31 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       }
     }
   } else if (warp == 20) {
-    // =============================== TMA producer ===============================
+    // =============================== TMA producer: absmax per item, raw NF4 per stage ===============================
     const uint64_t pol = l2_policy_evict_first();   // weights are read exactly once per step
     const uint32_t am_elt = nested ? 1u : 4u;
     const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
-    const uint32_t wfull0 = bar(kDbWFull), wempty0 = bar(kDbWEmpty);
+    const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty);
     int sw = 0, it = 0;
     uint32_t phw = 0;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+    // Experiment (NF4MOE_DEC_EXP & 4; measured SLOWER, 92 -> 98 us, so off): pull each item's packed bytes (one contiguous
+    // 184 KB span) into L2 front to back one item ahead, so the strided stage boxes hit L2.
+    auto prefetch_item = [&](int item) {
       const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-      const int e = a.tile_list[4 * tile], row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
-      const int nb = n_tok <= 16 ? 16 : 32;
-      const uint32_t b_tile = (uint32_t)nb * 128u;
-      const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
+      const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
+      const uint8_t* src = a.w.packed + (long long)a.tile_list[4 * tile] * a.w.packed_stride + (long long)rt * kGemmRowTile * (nkb * 32);
+      const uint32_t bytes = (uint32_t)(rows_here * nkb * 32);
+      if (elect_one())
+        for (uint32_t off = 0; off < bytes; off += 16384u)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + off), "r"(min(16384u, bytes - off)) : "memory");
+      __syncwarp();
+    };
+    if ((a.exp & 4) && (int)blockIdx.x < n_items) prefetch_item(blockIdx.x);
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+      GEMM_DBG_T0();
+      if ((a.exp & 4) && item + (int)gridDim.x < n_items) prefetch_item(item + gridDim.x);
+      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+      const int e = a.tile_list[4 * tile];
       const int c1 = e * a.w.rows + rt * kGemmRowTile;
       {
         const int mb = it & 1;
@@ -279,26 +343,84 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         }
         __syncwarp();
       }
+      GEMM_DBG_ADD(0);
+      const int n_tok = a.tile_list[4 * tile + 2];
+      const uint32_t b_tile = n_tok <= 16 ? 2048u : 4096u;
       for (int st = 0; st < nst; ++st) {
-        mbar_wait(wempty0 + 8u * (uint32_t)sw, phw ^ 1u);
+        mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);          // the 8 dequant warps of the stage n_raw back have read it
+        GEMM_DBG_ADD(1);
         const int nreal = min(4, nkb - st * 4);
         if (elect_one()) {
-          const uint32_t full = wfull0 + 8u * (uint32_t)sw, dst = s_st[sw];
-          mbar_expect_tx(full, kDecRawBytes + (uint32_t)nreal * b_tile);
-          tma_load_2d(dst, &map_w, st * 128, c1, full);
-          for (int u = 0; u < nreal; ++u)
-            tma_load_2d(dst + kDecRawBytes + (uint32_t)u * b_tile, map_x, (st * 4 + u) * kBlock, row0, full);
+          const uint32_t full = rfull0 + 8u * (uint32_t)sw;
+          // the activation producer (warp 22) adds its bytes to the same barrier; a 3-D box always delivers 4 tiles (zero-filled)
+          mbar_expect_tx(full, kDecRawBytes + (uint32_t)(a.b3d ? 4 : nreal) * b_tile);
+          if (a.exp & 32) {   // experiment: the same byte count as ONE contiguous 16 KB bulk copy (wrong data layout)
+            const long long span = (long long)kGemmRowTile * nkb * 32;
+            bulk_g2s(s_raw[sw], a.w.packed + (long long)c1 * (nkb * 32) + min((long long)st * 16384, span - 16384), kDecRawBytes, full, pol);
+          } else {
+            tma_load_2d(s_raw[sw], &map_w, st * 128, c1, full);
+          }
         }
         __syncwarp();
-        if (++sw == n_st) { sw = 0; phw ^= 1u; }
+        GEMM_DBG_ADD(2);
+        if (++sw == n_raw) { sw = 0; phw ^= 1u; }
+      }
+    }
+    if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[24 + i] = dbg_acc[i];
+  } else if (warp == 22) {
+    // =============================== TMA producer: activations per stage ===============================
+    // Its bytes complete on the SAME barrier as the stage's raw NF4 (the raw producer's expect_tx covers both), so the dequant
+    // warps' one wait covers both and the MMA thread waits on nothing but AFull.  It waits for REmpty too: the barrier's
+    // previous phase (stage cs - n_raw) must be over before bytes of stage cs may be counted on it.
+    const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), done0 = bar(kDbDone);
+    int sw = 0, sb = 0;
+    uint32_t phw = 0, phb = 0;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+      const int tile = item / n_row_tiles;
+      const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
+      const int nb = n_tok <= 16 ? 16 : 32;
+      const uint32_t b_tile = (uint32_t)nb * 128u;
+      const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
+      for (int st = 0; st < nst; ++st) {
+        mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);
+        mbar_wait(done0 + 8u * (uint32_t)sb, phb ^ 1u);            // the MMAs of the stage n_b back have read its activations
+        const int nreal = min(4, nkb - st * 4);
+        if (elect_one()) {
+          const uint32_t full = rfull0 + 8u * (uint32_t)sw, dst = b_ring + (uint32_t)sb * b_stage;
+          if (a.b3d) {
+            tma_load_3d(dst, map_x, 0, row0, st * 4, full);
+          } else {
+            for (int u = 0; u < nreal; ++u) tma_load_2d(dst + (uint32_t)u * b_tile, map_x, (st * 4 + u) * kBlock, row0, full);
+          }
+        }
+        __syncwarp();
+        if (++sw == n_raw) { sw = 0; phw ^= 1u; }
+        if (++sb == n_b) { sb = 0; phb ^= 1u; }
       }
     }
   } else if (warp == 21) {
     // =============================== MMA issuer (one thread) ===============================
-    const uint32_t wfull0 = bar(kDbWFull), wempty0 = bar(kDbWEmpty), afull0 = bar(kDbAFull), aempty0 = bar(kDbAEmpty);
+    // A lone warp runs at one dependent instruction per ~6 cycles and every mbarrier / tcgen05 instruction costs it 60-100, so
+    // this loop is kept to one wait, the MMAs (running addresses, constant accumulate flag except in an item's first stage)
+    // and one commit per stage.
+    const uint32_t afull0 = bar(kDbAFull), done0 = bar(kDbDone);
     const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version 1, SWIZZLE_128B
-    int sw = 0, slot = 0, it = 0;
-    uint32_t phw = 0, pha = 0;
+    const uint32_t blo0 = (b_ring & 0x3FFFFu) >> 4, bstep = b_stage >> 4;
+    const uint32_t a_t0 = tmem + acol0;
+    int sb = 0, slot = 0, it = 0;
+    uint32_t pha = 0;
+    auto issue = [&](const uint32_t d_t, const uint32_t a_t, const uint32_t b_lo, const uint32_t blo_step, const uint32_t idesc,
+                     const int nreal, const bool first) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (u < nreal) {
+          const uint64_t desc = ((uint64_t)desc_hi << 32) | (uint64_t)(b_lo + (uint32_t)u * blo_step);
+#pragma unroll
+          for (int kk = 0; kk < ((a.exp & 1) ? 1 : 4); ++kk)
+            tc_mma_ts(d_t, a_t + (uint32_t)(u * 32 + 8 * kk), desc + (uint64_t)(2 * kk), idesc, first ? (uint32_t)(u | kk) : 1u);
+        }
+      }
+    };
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const int tile = item / n_row_tiles;
       const int n_tok = a.tile_list[4 * tile + 2];
@@ -307,34 +429,28 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const uint32_t blo_step = ((uint32_t)nb * 128u) >> 4;
       const int db = it & 1;
       const uint32_t d_t = tmem + (uint32_t)(db * kDecAccCols);
+      GEMM_DBG_T0();
       mbar_wait(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
-      tc_fence_after();
+      GEMM_DBG_ADD(0);
       for (int st = 0; st < nst; ++st) {
-        mbar_wait(wfull0 + 8u * (uint32_t)sw, phw);      // activations landed (TMA)
-        mbar_wait(afull0 + 8u * (uint32_t)slot, pha);    // A operand written (8 dequant warps)
+        mbar_wait(afull0 + 8u * (uint32_t)slot, pha);     // A operand written by the stage's 8 dequant warps (who saw its TMA land)
         tc_fence_after();
+        GEMM_DBG_ADD(2);
         const int nreal = min(4, nkb - st * 4);
         if (elect_one()) {
-          const uint32_t b_lo = ((s_st[sw] + kDecRawBytes) & 0x3FFFFu) >> 4;
-          const uint32_t a_t = tmem + acol0 + (uint32_t)slot * 128u;
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            if (u < nreal) {
-              const uint64_t desc = ((uint64_t)desc_hi << 32) | (uint64_t)(b_lo + (uint32_t)u * blo_step);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                tc_mma_ts(d_t, a_t + (uint32_t)(u * 32 + 8 * kk), desc + (uint64_t)(2 * kk), idesc, (uint32_t)(st | u | kk));
-            }
-          }
-          tc_commit(wempty0 + 8u * (uint32_t)sw);        // the stage's activations are consumed
-          tc_commit(aempty0 + 8u * (uint32_t)slot);      // ... and so is the A slot
+          const uint32_t a_t = a_t0 + (uint32_t)slot * 128u, b_lo = blo0 + (uint32_t)sb * bstep;
+          if (st == 0) issue(d_t, a_t, b_lo, blo_step, idesc, nreal, true);
+          else issue(d_t, a_t, b_lo, blo_step, idesc, nreal, false);
+          tc_commit(done0 + 8u * (uint32_t)sb);            // frees the A slot and the activation stage
           if (st == nst - 1) tc_commit(bar(kDbDFull + db));
         }
         __syncwarp();
-        if (++sw == n_st) { sw = 0; phw ^= 1u; }
+        GEMM_DBG_ADD(3);
         if (++slot == kDecSlots) { slot = 0; pha ^= 1u; }
+        if (++sb == n_b) sb = 0;
       }
     }
+    if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[16 + i] = dbg_acc[i];
   }
 
   // ---- teardown ----
@@ -380,19 +496,29 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   a.meta = meta;
   a.tile_list = tile_list;
   a.act = act;
-  a.dbg = nullptr;
+  a.dbg = gemm_debug_buffer();
+  static const int raw_env = getenv("NF4MOE_DEC_RAW") ? atoi(getenv("NF4MOE_DEC_RAW")) : kDecMaxRaw;
+  static const int b_env = getenv("NF4MOE_DEC_B") ? atoi(getenv("NF4MOE_DEC_B")) : 4;
+  static const int exp_env = getenv("NF4MOE_DEC_EXP") ? atoi(getenv("NF4MOE_DEC_EXP")) : 0;
+  a.exp = exp_env;
+  a.max_raw = std::max(2, raw_env);
+  a.max_b = std::max(2, b_env);
   CUtensorMap map_w, map_x16, map_x32;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
-  if (!make_map_2d(&map_x16, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 16) ||
-      !make_map_2d(&map_x32, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32))
+  static const bool no3d = getenv("NF4MOE_DEC_NO3D") != nullptr;
+  a.b3d = !no3d && make_map_x3d(&map_x16, act_in, (uint64_t)w->cols, (uint64_t)T * k, 16) &&
+          make_map_x3d(&map_x32, act_in, (uint64_t)w->cols, (uint64_t)T * k, 32);
+  if (!a.b3d && (!make_map_2d(&map_x16, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 16) ||
+                 !make_map_2d(&map_x32, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32)))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
-  auto kern = dec_kernel<W13>;
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
+  const bool dbg = W13 && a.dbg != nullptr;   // the cycle-counter build exists for w13 only (scripts/dec_roles.py)
+  auto kern = dbg ? dec_kernel<W13, W13> : dec_kernel<W13, false>;
+  static thread_local bool attr_set[2] = {false, false};
+  if (!attr_set[dbg]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDecSmemBytes);
     if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
-    attr_set = true;
+    attr_set[dbg] = true;
   }
   kern<<<sms, kDecThreads, kDecSmemBytes, (cudaStream_t)stream>>>(a, map_w, map_x16, map_x32);
   ++*launches;
