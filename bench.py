@@ -43,6 +43,8 @@ def parse():
     p.add_argument("--layers", type=int, default=24)
     p.add_argument("--experts", type=int, default=32)
     p.add_argument("--absmax", default="nested", choices=["nested", "flat"])
+    p.add_argument("--regime", default="auto", choices=["auto", "gemv", "gemm", "gemm_fast"],
+                   help="auto = what the drop-in apply() uses: GEMV up to 8 tokens, decode tcgen05 kernel above")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-prefill", action="store_true", help="skip the extra 8192-token prefill measurement")
     p.add_argument("--prefill-tokens", type=int, default=8192)
@@ -254,6 +256,11 @@ def run_ours(args):
         ep = importlib.import_module("gpt-oss-vllm_b200.ep")
         return ep.bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, METRIC)
 
+    regime = {"auto": pkg.REGIME_AUTO, "gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "gemm_fast": pkg.REGIME_GEMM_FAST}[args.regime]
+    eff = pkg.ops.auto_regime(T, TOP_K, E) if regime == pkg.REGIME_AUTO else regime     # what AUTO resolves to
+    eff_name = {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "gemm_exact", pkg.REGIME_GEMM_FAST: "gemm_fast"}[eff]
+    use_tc = eff != pkg.REGIME_GEMV
+    dec_kernel = use_tc and T * TOP_K <= 32 * E
     stack = make_stack(pkg, dev, L, E, code2)
     g = torch.Generator(device=dev).manual_seed(SEED + 1)
     x = torch.randn(T, H, generator=g, device=dev).half()
@@ -264,7 +271,7 @@ def run_ours(args):
     def stack_forward():
         for l, (w13, w2) in enumerate(stack):
             pkg.ops.moe_forward(x, w13, w2, TOP_K, router_logits=logits[l], out=outs[l], workspace=ws, nested=nested,
-                                regime=pkg.REGIME_GEMV)
+                                regime=regime)
 
     stack_forward()
     launches_per_layer = pkg.ops.last_launch_count()
@@ -300,7 +307,7 @@ def run_ours(args):
     value = T / (ms_per_step * 1e-3)
 
     # ---- e2e: public API, host buffers, H2D + D2H inside the timed region ----
-    method = pkg.B200NF4MoEMethod(top_k=TOP_K, nested=nested, regime=pkg.REGIME_GEMV)
+    method = pkg.B200NF4MoEMethod(top_k=TOP_K, nested=nested, regime=regime)
     layers_mod = []
     for w13, w2 in stack:
         m = torch.nn.Module()
@@ -337,12 +344,13 @@ def run_ours(args):
     for rep in range(3):
         for l, (w13, w2) in enumerate(stack):
             ids, wts = pkg.ops.route_topk(logits[l], TOP_K)
-            b = pkg.ops.bucket(ids, E, want_tiles=False)
+            b = pkg.ops.bucket(ids, E, want_tiles=use_tc)
+            xin = pkg.ops.permute_rows(x, b, TOP_K) if use_tc else x
             a0, a1, a2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
             a0.record()
-            hbuf = pkg.ops.expert_w13(x, w13, b, T, TOP_K, nested=nested)
+            hbuf = pkg.ops.expert_w13(xin, w13, b, T, TOP_K, nested=nested, regime=eff)
             a1.record()
-            pkg.ops.expert_w2(hbuf, w2, b, T, TOP_K, nested=nested)
+            pkg.ops.expert_w2(hbuf, w2, b, T, TOP_K, nested=nested, regime=eff)
             a2.record()
             torch.cuda.synchronize()
             if rep > 0:
@@ -358,11 +366,14 @@ def run_ours(args):
     try:   # dram bytes of this kernel at this configuration from the committed `ncu --set full` capture (never measured under ncu here)
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
             tj = json.load(f)
-        if T == 64 and E == 32 and nested:
-            traffic, traffic_src = tj["traffic_bytes_per_launch"], tj["source"]
+        key = "dec" if dec_kernel else eff_name
+        if T == 64 and E == 32 and nested and key in tj:
+            traffic, traffic_src = tj[key]["traffic_bytes_per_launch"], tj[key]["source"]
     except Exception:
         pass
-    roof = {"bound": "hbm", "kernel": "gemv_kernel<NT=2,W13> (w13 NF4 GEMV + SwiGLU)", "achieved": b13 / d13 / 1e9, "peak": peak,
+    kname = ("dec_kernel<W13> (decode-regime tcgen05 kernel: NF4 -> TMEM A operand, w13 + SwiGLU)" if dec_kernel else
+             "gemm_kernel<W13> (tcgen05 grouped GEMM, w13 + SwiGLU)" if use_tc else "gemv_kernel<NT=2,W13> (w13 NF4 GEMV + SwiGLU)")
+    roof = {"bound": "hbm", "kernel": kname, "achieved": b13 / d13 / 1e9, "peak": peak,
             "unit": "GB/s", "frac": b13 / d13 / 1e9 / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": b13, "avg_launch_us": d13 * 1e6, "frac_of_nominal_8TBs": b13 / d13 / 8e12,
             "w2_kernel": {"achieved": b2 / d2 / 1e9, "frac": b2 / d2 / 1e9 / peak, "avg_launch_us": d2 * 1e6,
@@ -375,7 +386,7 @@ def run_ours(args):
             "dtype": "nf4 weights -> f16 mma operands, f32 accumulate, f16 activations", "data": "synthetic (seeded N(0,0.02^2) weights quantised on device, N(0,1) tokens and logits)",
             "config": {"workload": f"gpt-oss-20b {L}-layer NF4 MoE stack decode, T={T} (BASELINE.json configs[1])", "hidden": H,
                        "intermediate": I, "experts": E, "top_k": TOP_K, "layers": L, "tokens": T, "absmax": args.absmax,
-                       "regime": "gemv", "l2": "9.6 GB of weights streamed per step >> 126 MB L2 (no flush needed)",
+                       "regime": args.regime, "regime_resolved": eff_name, "l2": "9.6 GB of weights streamed per step >> 126 MB L2 (no flush needed)",
                        "cuda_graph": True, "per_layer_us": ms_per_step * 1e3 / L},
             "clocks": clocks,
             "e2e": {"value": T / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2 + hlg.numel() * 2,

@@ -127,15 +127,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
-// Wait for roles whose waits are LONG (an epilogue warp waits a whole item, a producer a whole stage): one probe, then
-// plain NANOSLEEP between probes.  try_wait's suspend hint compiles to NANOSLEEP.SYNCS, which wakes on every mbarrier
-// event of the CTA (there are thousands per item), so such a loop re-polls every ~36 cycles: measured 19 M of the decode
-// kernel's 75 M issued warp-instructions (ncu source page, profiles/r1c_*), all stolen from the dequant warps' schedulers.
-__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t ns) {
-  if (ns == 0u) { mbar_wait(bar, parity); return; }
-  if (mbar_test_wait(bar, parity)) return;
-  do { __nanosleep(ns); } while (!mbar_test_wait(bar, parity));
-}
 
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
   uint64_t p;

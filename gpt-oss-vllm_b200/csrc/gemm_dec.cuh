@@ -61,7 +61,6 @@ struct DecArgs {
   int max_raw, max_b;   // ring caps (tuning knobs NF4MOE_DEC_RAW / NF4MOE_DEC_B)
   int b3d;              // the activation maps are the 3-D form (one TMA per stage) rather than 2-D (one per k-block)
   int exp;              // timing experiments (NF4MOE_DEC_EXP; results are wrong when non-zero)
-  int ns_epi, ns_prod, ns_mma, ns_dq;   // NANOSLEEP between barrier probes per role (NF4MOE_DEC_SLEEP; 0 = try_wait spin)
 };
 
 // barrier slots
@@ -98,7 +97,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   const bool nested = a.w.absmax_f32 == nullptr;
   const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
   const uint32_t b_stage = 4u * (uint32_t)bmax * 128u;  // activations of one stage: 4 k-blocks x N x 128 B
-  const int n_b = bmax == 16 ? 6 : 3;                   // activation stages (48 KB either way, ONE contiguous block); multiple of 3
+  // activation stages in ONE contiguous block: 6 x 8 KB at N = 16; at N = 32 (16 KB each) a.max_b of them (default 5): with
+  // 3, stage cs's activations could only be requested once the MMAs of stage cs - 3 had retired, and that round trip
+  // (TMA latency + dequant + MMA per 3 stages) set the pace (measured ~10 % slower than the N = 16 launches)
+  const int n_b = bmax == 16 ? 6 : min(kDecMaxB, max(3, a.max_b));
   const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
   const uint32_t m_code2 = (m_tile + 15u) & ~15u;
   const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
@@ -166,9 +168,9 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0;
     const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), afull0 = bar(kDbAFull), done0 = bar(kDbDone);
     // this lane's four 16-byte chunks of a raw stage row (128B swizzle: chunk c of row r sits at chunk c ^ (r & 7))
-    // (chunks c+1..c+3 are chb ^ 0x10, 0x20, 0x30: stage bases are 1 KB aligned, so the XOR carries through the add.  chb is
-    // pinned: left alone, ptxas rebuilt all four offsets from %tid in every stage, ~35 instructions)
-    const uint32_t chb = pin((uint32_t)r * 128u + (((uint32_t)(hh * 4) ^ (uint32_t)(r & 7)) << 4));
+    const uint32_t row_off = (uint32_t)r * 128u, swz = (uint32_t)(r & 7);
+    const uint32_t ch0 = row_off + (((uint32_t)(hh * 4) ^ swz) << 4), ch1 = row_off + (((uint32_t)(hh * 4 + 1) ^ swz) << 4);
+    const uint32_t ch2 = row_off + (((uint32_t)(hh * 4 + 2) ^ swz) << 4), ch3 = row_off + (((uint32_t)(hh * 4 + 3) ^ swz) << 4);
     // this warp owns stages cs = pp (mod 2).  Running ring positions of its NEXT stage: raw stage sw, A slot `slot`, and the Done
     // barrier of stage cs - 3 (index dn, parity pdn; "stage -3 .. -1" = the phase before the first one, which a fresh barrier
     // reports complete)
@@ -181,34 +183,32 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const int mb = it & 1;
       // nested absmax: code2[u8] * absmax2[blk >> 8] + offset; this row's blocks touch at most two absmax2 entries
       float a2_lo = 0.f, a2_hi = 0.f, off_e = 0.f;
-      int blk_hi = 0;
+      long long blk_hi = 0;
       if (nested) {
         const long long blk0 = (long long)min(n, a.w.rows - 1) * nkb;
         const long long i2 = blk0 >> 8;
         a2_lo = __ldg(a.w.absmax2 + (long long)e * a.w.n2 + i2);
         a2_hi = __ldg(a.w.absmax2 + (long long)e * a.w.n2 + min(i2 + 1, a.w.n2 - 1));
         off_e = __ldg(a.w.offset + e);
-        blk_hi = (int)(((i2 + 1) << 8) - blk0);   // 1..256: k-blocks of this row below it use a2_lo
+        blk_hi = ((i2 + 1) << 8) - blk0;
       }
       GEMM_DBG_T0();
       mbar_wait(bar(kDbMFull + mb), (uint32_t)(it >> 1) & 1u);
       GEMM_DBG_ADD(0);
       const uint32_t m_st = pin(s_mst[mb]);
-      const uint32_t m_row = pin(m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u));
-      const uint32_t m_c2 = m_st + m_code2;
+      const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       for (; st < nst; st += 2) {
         mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
         GEMM_DBG_ADD(1);
         const uint32_t wst = pin(s_raw[sw]);
         const int kb0 = st * 4 + hh * 2;
         const bool real0 = kb0 < nkb && !(a.exp & 16), real1 = kb0 + 1 < nkb && !(a.exp & 24);
-        const uint32_t wch = wst + chb;
-        uint4 v0 = lds128(wch), v1 = lds128(wch ^ 16u), v2 = lds128(wch ^ 32u), v3 = lds128(wch ^ 48u);
+        uint4 v0 = lds128(wst + ch0), v1 = lds128(wst + ch1), v2 = lds128(wst + ch2), v3 = lds128(wst + ch3);
         float am0 = 0.f, am1 = 0.f;
         if (nested) {
           const uint32_t c0 = lds_u8(m_row + (uint32_t)min(kb0, nkb - 1)), c1 = lds_u8(m_row + (uint32_t)min(kb0 + 1, nkb - 1));
-          am0 = __fadd_rn(__fmul_rn(lds_f32(m_c2 + 4u * c0), kb0 < blk_hi ? a2_lo : a2_hi), off_e);
-          am1 = __fadd_rn(__fmul_rn(lds_f32(m_c2 + 4u * c1), kb0 + 1 < blk_hi ? a2_lo : a2_hi), off_e);
+          am0 = __fadd_rn(__fmul_rn(lds_f32(m_st + m_code2 + 4u * c0), kb0 < blk_hi ? a2_lo : a2_hi), off_e);
+          am1 = __fadd_rn(__fmul_rn(lds_f32(m_st + m_code2 + 4u * c1), kb0 + 1 < blk_hi ? a2_lo : a2_hi), off_e);
         } else {
           am0 = lds_f32(m_row + 4u * (uint32_t)min(kb0, nkb - 1));
           am1 = lds_f32(m_row + 4u * (uint32_t)min(kb0 + 1, nkb - 1));
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         uint32_t regs[32];
         if (real0) decode_block<true>(v0, v1, lut_lane, am0, regs, (a.exp & 2) != 0);
         GEMM_DBG_ADD(2);
-        mbar_wait_sleep(done0 + 8u * (uint32_t)dn, pdn, (uint32_t)a.ns_dq);   // the MMAs of stage cs - 3, which read this A slot, are done
+        mbar_wait(done0 + 8u * (uint32_t)dn, pdn);          // the MMAs of stage cs - 3, which read this A slot, are done
         tc_fence_after();
         GEMM_DBG_ADD(3);
         if (real0) tmem_st32(t_half, regs);
@@ -258,7 +258,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
       const int n = rt * kGemmRowTile + r;
       const int db = it & 1;
-      mbar_wait_sleep(bar(kDbDFull + db), (uint32_t)(it >> 1) & 1u, (uint32_t)a.ns_epi);
+      mbar_wait(bar(kDbDFull + db), (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
       const bool row_ok = n < a.w.rows;
       uint32_t v[32];
@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         const int mb = it & 1;
         const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
         const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
-        mbar_wait_sleep(bar(kDbMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u, (uint32_t)a.ns_prod);
+        mbar_wait(bar(kDbMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u);
         if (elect_one()) {
           mbar_expect_tx(bar(kDbMFull + mb), bytes + (nested ? 1024u : 0u));
           bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
@@ -350,7 +350,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const int n_tok = a.tile_list[4 * tile + 2];
       const uint32_t b_tile = n_tok <= 16 ? 2048u : 4096u;
       for (int st = 0; st < nst; ++st) {
-        mbar_wait_sleep(rempty0 + 8u * (uint32_t)sw, phw ^ 1u, (uint32_t)a.ns_prod);   // the 8 dequant warps of the stage n_raw back have read it
+        mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);          // the 8 dequant warps of the stage n_raw back have read it
         GEMM_DBG_ADD(1);
         const int nreal = min(4, nkb - st * 4);
         if (elect_one()) {
@@ -385,8 +385,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const uint32_t b_tile = (uint32_t)nb * 128u;
       const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
       for (int st = 0; st < nst; ++st) {
-        mbar_wait_sleep(rempty0 + 8u * (uint32_t)sw, phw ^ 1u, (uint32_t)a.ns_prod);
-        mbar_wait_sleep(done0 + 8u * (uint32_t)sb, phb ^ 1u, (uint32_t)a.ns_prod);   // the MMAs of the stage n_b back have read its activations
+        mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);
+        mbar_wait(done0 + 8u * (uint32_t)sb, phb ^ 1u);            // the MMAs of the stage n_b back have read its activations
         const int nreal = min(4, nkb - st * 4);
         if (elect_one()) {
           const uint32_t full = rfull0 + 8u * (uint32_t)sw, dst = b_ring + (uint32_t)sb * b_stage;
@@ -433,10 +433,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const int db = it & 1;
       const uint32_t d_t = tmem + (uint32_t)(db * kDecAccCols);
       GEMM_DBG_T0();
-      mbar_wait_sleep(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u, (uint32_t)a.ns_mma);   // the epilogue has drained this accumulator
+      mbar_wait(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
       GEMM_DBG_ADD(0);
       for (int st = 0; st < nst; ++st) {
-        mbar_wait_sleep(afull0 + 8u * (uint32_t)slot, pha, (uint32_t)a.ns_mma);   // A operand written by the stage's 8 dequant warps (who saw its TMA land)
+        mbar_wait(afull0 + 8u * (uint32_t)slot, pha);     // A operand written by the stage's 8 dequant warps (who saw its TMA land)
         tc_fence_after();
         GEMM_DBG_ADD(2);
         const int nreal = min(4, nkb - st * 4);
@@ -501,16 +501,9 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   a.act = act;
   a.dbg = gemm_debug_buffer();
   static const int raw_env = getenv("NF4MOE_DEC_RAW") ? atoi(getenv("NF4MOE_DEC_RAW")) : kDecMaxRaw;
-  static const int b_env = getenv("NF4MOE_DEC_B") ? atoi(getenv("NF4MOE_DEC_B")) : 4;
+  static const int b_env = getenv("NF4MOE_DEC_B") ? atoi(getenv("NF4MOE_DEC_B")) : 5;
   static const int exp_env = getenv("NF4MOE_DEC_EXP") ? atoi(getenv("NF4MOE_DEC_EXP")) : 0;
   a.exp = exp_env;
-  static int ns_env[4] = {500, 100, 40, 0};   // epilogue, producers, MMA issuer, dequant (A-slot wait)
-  static const bool ns_init = [] {
-    if (const char* s = getenv("NF4MOE_DEC_SLEEP")) sscanf(s, "%d,%d,%d,%d", &ns_env[0], &ns_env[1], &ns_env[2], &ns_env[3]);
-    return true;
-  }();
-  (void)ns_init;
-  a.ns_epi = ns_env[0]; a.ns_prod = ns_env[1]; a.ns_mma = ns_env[2]; a.ns_dq = ns_env[3];
   a.max_raw = std::max(2, raw_env);
   a.max_b = std::max(2, b_env);
   CUtensorMap map_w, map_x16, map_x32;

@@ -33,7 +33,7 @@
 
 namespace nf4moe {
 
-constexpr int kGemmAutoThreshold = 64;  // tokens; above this nf4moe_moe_forward(AUTO) uses the tcgen05 path
+constexpr int kDecAutoMinTokens = 8;    // tokens; up to this nf4moe_moe_forward(AUTO) uses the GEMV, above it a tcgen05 kernel
 constexpr int kDqGroups = 3;            // dequant warpgroups; k-block c of a CTA belongs to group c % 3
 constexpr int kGemmThreads = (4 + 4 * kDqGroups + 4) * 32;   // 640: control WG, 3 dequant WGs, epilogue WG
 constexpr int kGemmTokTile = 160;       // largest MMA N: two accumulators of 160 columns leave 192 TMEM columns = 3 slots of 2 k-blocks

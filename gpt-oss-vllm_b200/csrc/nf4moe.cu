@@ -172,6 +172,16 @@ int check_gemv_tokens(int T, int k, int E, const char* name) {
 extern "C" {
 
 int nf4moe_version(void) { return NF4MOE_VERSION; }
+
+// What NF4MOE_REGIME_AUTO resolves to (measured on B200, gpt-oss-20b shapes, profiles/r1c_kernel_times.txt):
+//   T <= 8                       mma.sync GEMV (few active experts, 3.3-3.5 TB/s; the tcgen05 pipeline's fill costs more)
+//   token tiles of <= 32 rows    decode-regime tcgen05 kernel (gemm_dec.cuh; FAST operand), 3.1-3.3 TB/s vs the GEMV's 2.4-2.9
+//   larger                       prefill tcgen05 grouped GEMM with the EXACT (bit-identical dequant) operand
+int nf4moe_auto_regime(int T, int k, int E) {
+  if (T <= kDecAutoMinTokens) return NF4MOE_REGIME_GEMV;
+  if (dec_serves(T, k, E, NF4MOE_GEMM_FAST)) return NF4MOE_REGIME_GEMM_FAST;
+  return NF4MOE_REGIME_GEMM;
+}
 // profiling hook (not part of the public header): 64 int64 cycle counters written by CTA 0 of the tcgen05 kernels
 void nf4moe_debug_set_gemm_counters(long long* dev_ptr) { gemm_debug_buffer() = dev_ptr; }
 const char* nf4moe_last_error(void) { return g_err; }
@@ -378,7 +388,12 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* y, int T,
                        int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches) {
   cudaStream_t st = (cudaStream_t)stream;
-  if (regime == NF4MOE_REGIME_AUTO) regime = gemm_available() && T > kGemmAutoThreshold ? NF4MOE_REGIME_GEMM : NF4MOE_REGIME_GEMV;
+  if (regime == NF4MOE_REGIME_AUTO) {
+    // the tcgen05 kernels need 16-row / 64-column granularity and K <= 4096; other shapes stay on the GEMV
+    const bool tc_ok = w13->rows % 16 == 0 && w2->rows % 16 == 0 && w13->cols % kBlock == 0 && w2->cols % kBlock == 0 &&
+                       w13->cols <= 4096 && w2->cols <= 4096;
+    regime = tc_ok ? nf4moe_auto_regime(T, k, E) : NF4MOE_REGIME_GEMV;
+  }
   if (regime != NF4MOE_REGIME_GEMV && regime != NF4MOE_REGIME_GEMM && regime != NF4MOE_REGIME_GEMM_FAST)
     return fail(NF4MOE_EINVAL, "unknown regime %d", regime);
   const bool gemm = regime != NF4MOE_REGIME_GEMV;

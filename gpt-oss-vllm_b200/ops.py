@@ -64,6 +64,11 @@ def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True, tile_rows: int = 
     return out
 
 
+def auto_regime(T: int, k: int, E: int) -> int:
+    """The regime REGIME_AUTO resolves to (nf4moe_auto_regime)."""
+    return int(_lib.load_library().nf4moe_auto_regime(T, k, E))
+
+
 def permute_rows(x: torch.Tensor, b: dict, k: int) -> torch.Tensor:
     T, H = x.shape
     xs = torch.empty((T * k + 255) // 256 * 256 + 256, H, dtype=torch.float16, device=x.device)

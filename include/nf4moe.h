@@ -87,6 +87,9 @@ typedef struct nf4moe_qweight {
 } nf4moe_qweight;
 
 int nf4moe_version(void);
+/* The regime NF4MOE_REGIME_AUTO resolves to for T tokens, top-k k, E experts (pure function of its arguments; replaces the
+ * reference's absence of any regime choice: its forward is a per-(token, slot) Python loop, P/unsloth_to_vllm_converter.py:298-323). */
+int nf4moe_auto_regime(int T, int k, int E);
 const char* nf4moe_last_error(void);
 
 /* Scratch the fused forward needs for T tokens (bytes).  Layout is private to the library. */

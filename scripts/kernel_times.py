@@ -49,6 +49,7 @@ for T in a.tokens:
     b = pkg.ops.bucket(ids, E, want_tiles=gemm)
     xin = pkg.ops.permute_rows(x, b, 4) if gemm else x
     ea = int(b["meta"][0].item())
+    print(f"# T={T}: active experts {ea}, largest per-expert count {int(b['meta'][3].item())}")
     for mode in a.absmax:
         nested = mode == "nested"
         # CUDA-graph replay: a Python/ctypes launch costs more CPU time than these kernels take on the GPU

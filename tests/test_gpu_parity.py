@@ -462,8 +462,13 @@ def test_moe_forward_gemm_regime_vs_oracle(pkg, cuda_device, T, E, H, I, k):
     # the two regimes differ only in fp32 summation order
     out_v = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_GEMV)
     assert_moe_close(out.cpu().numpy(), out_v.cpu().numpy())
+    # AUTO is exactly the regime nf4moe_auto_regime names: the decode tcgen05 kernel (FAST operand) while token tiles are
+    # <= 32 rows, the EXACT prefill GEMM above
+    auto = pkg.ops.auto_regime(T, k, E)
+    assert auto == (pkg.REGIME_GEMM_FAST if T * k <= 32 * E else pkg.REGIME_GEMM)
     out_a = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_AUTO)
-    assert torch.equal(out_a, out)
+    assert torch.equal(out_a, pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=auto))
+    assert_moe_close(out_a.cpu().numpy(), ref)
     # FAST operand mode: same layer, half2-arithmetic dequant, still inside the north-star tolerance of the oracle
     out_f = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_GEMM_FAST)
     assert_moe_close(out_f.cpu().numpy(), ref)
