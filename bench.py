@@ -340,23 +340,39 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel (w13 GEMV), timed live with CUDA events on the launching stream ----
     peak, peak_src = measured_peaks()
-    t13, t2, eact = [], [], []
-    for rep in range(3):
-        for l, (w13, w2) in enumerate(stack):
-            ids, wts = pkg.ops.route_topk(logits[l], TOP_K)
-            b = pkg.ops.bucket(ids, E, want_tiles=use_tc)
-            xin = pkg.ops.permute_rows(x, b, TOP_K) if use_tc else x
-            a0, a1, a2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
-            a0.record()
-            hbuf = pkg.ops.expert_w13(xin, w13, b, T, TOP_K, nested=nested, regime=eff)
-            a1.record()
+    # The kernels are launched back to back from CUDA graphs (one graph = the w13 kernel of all L layers, one = the w2 kernels,
+    # each layer with its own routing), so the event interval holds kernel time only, not ctypes/launch gaps; weights rotate
+    # over L layers (9.6 GB), so no launch finds its weights in L2.
+    prep = []
+    for l, (w13, w2) in enumerate(stack):
+        ids, wts = pkg.ops.route_topk(logits[l], TOP_K)
+        b = pkg.ops.bucket(ids, E, want_tiles=use_tc)
+        prep.append((b, pkg.ops.permute_rows(x, b, TOP_K) if use_tc else x))
+    eact = [int(b["meta"][0].item()) for b, _ in prep]
+
+    def run13():
+        return [pkg.ops.expert_w13(xin, w13, b, T, TOP_K, nested=nested, regime=eff) for (w13, _), (b, xin) in zip(stack, prep)]
+
+    def run2(hs):
+        for hbuf, (_, w2), (b, _) in zip(hs, stack, prep):
             pkg.ops.expert_w2(hbuf, w2, b, T, TOP_K, nested=nested, regime=eff)
-            a2.record()
-            torch.cuda.synchronize()
-            if rep > 0:
-                t13.append(a0.elapsed_time(a1))
-                t2.append(a1.elapsed_time(a2))
-                eact.append(int(b["meta"][0].item()))
+
+    hs = run13(); run2(hs); torch.cuda.synchronize()
+    g13, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g13, stream=side):
+            hs = run13()
+        with torch.cuda.graph(g2, stream=side):
+            run2(hs)
+    torch.cuda.synchronize()
+    t13, t2 = [], []
+    for rep in range(4):
+        a0, a1, a2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        a0.record(); g13.replay(); a1.record(); g2.replay(); a2.record()
+        torch.cuda.synchronize()
+        if rep > 0:
+            t13.append(a0.elapsed_time(a1) / L)
+            t2.append(a1.elapsed_time(a2) / L)
     ea = sum(eact) / len(eact)
     b13 = ea * stack[0][0].nbytes(nested) + T * H * 2 + T * TOP_K * I * 2
     b2 = ea * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2

@@ -3,6 +3,7 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/nf4moe.h"
 
@@ -123,6 +124,16 @@ __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Programmatic dependent launch: a kernel launched with launch_pdl() may start (be scheduled, run its prologue) while the
+// previous kernel of the stream is still draining; grid_dep_wait() blocks until that kernel has completed and its writes
+// are visible.  Every thread executes it before touching anything a previous kernel produced (and before writing anything a
+// previous kernel may still read).  Without the launch attribute it is a no-op.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Lets the NEXT kernel of the stream be scheduled as soon as every CTA of this one has started (it then blocks in its own
+// grid_dep_wait() until this grid has completed): launch latency, CTA rasterisation and the next kernel's input-independent
+// prologue overlap this kernel.  Called first thing by every kernel that is launched with launch_pdl().
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
@@ -230,5 +241,25 @@ __device__ __forceinline__ uint32_t swiglu_oai_h2(uint32_t g2, uint32_t u2) {
 }
 // the reference wrapper's own variant, P/unsloth_to_vllm_converter.py:312-315
 __device__ __forceinline__ float silu_mul(float g, float u) { return g / (1.0f + __expf(-g)) * u; }
+
+// ---- host: launch with the programmatic-stream-serialization attribute (NF4MOE_PDL=0 turns it off for A/B timing) ----------
+inline bool pdl_enabled() {
+  static const bool on = !(getenv("NF4MOE_PDL") && atoi(getenv("NF4MOE_PDL")) == 0);
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
 
 }  // namespace nf4moe

@@ -21,8 +21,16 @@
 
 namespace nf4moe {
 
-constexpr int kDecDqWarps = 16;
-constexpr int kDecThreads = (kDecDqWarps + 4 + 4) * 32;   // 768: dequant, epilogue warpgroup, control warpgroup
+#ifndef NF4MOE_DEC_GROUPS
+#define NF4MOE_DEC_GROUPS 2
+#endif
+// Dequant groups of 8 warps; stage cs of the CTA belongs to group cs % kDecGroups.  3 groups (1024 threads, 64 registers, a few
+// spills) measured 12 % SLOWER than 2 (T=64 w13 93.0 vs 82.8 us): issue slots and the shared-memory pipe are both ~60 % busy
+// with 2 groups and more resident warps only add contention, so 2 is the shipped value.
+constexpr int kDecGroups = NF4MOE_DEC_GROUPS;
+constexpr int kDecDqWarps = 8 * kDecGroups;
+constexpr int kDecThreads = (kDecDqWarps + 4 + 4) * 32;   // 768 / 1024: dequant, epilogue warpgroup, control warpgroup
+constexpr int kDecWarpProd = kDecDqWarps + 4, kDecWarpMma = kDecDqWarps + 5, kDecWarpAct = kDecDqWarps + 6;
 constexpr int kDecMaxRaw = 8;                              // raw-NF4 stages (16 KB each) in the shared-memory ring
 constexpr int kDecMaxB = 6;                                // activation stages (their own ring: they live until the MMAs retire)
 constexpr int kDecSlots = 3;                               // A-operand slots in TMEM: one stage = 4 k-blocks = 128 columns each
@@ -91,10 +99,27 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   __shared__ uint32_t s_tmem;
   __shared__ uint32_t s_raw[kDecMaxRaw], s_b0, s_mst[2];
   __shared__ int s_nraw;
+  grid_dep_launch();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nkb = a.w.nkb;
   const int nst = (nkb + 3) >> 2;                       // stages per item (the last one may be partly padding)
   const bool nested = a.w.absmax_f32 == nullptr;
+  const uint32_t base = smem_u32(dyn_smem);
+  const uint32_t lut = pin((base + kGemmLutBytes - 1u) & ~(kGemmLutBytes - 1u));
+  const uint32_t bar0 = pin(smem_u32(s_bar));
+  auto bar = [&](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
+
+  // ---- prologue that depends on nothing the previous kernel wrote: decode table, TMEM allocation.  Under programmatic
+  // dependent launch it overlaps the previous kernel's tail; everything below the wait may read bucket / GEMM outputs ----
+  for (int i = tid; i < 256 * 32; i += kDecThreads) {
+    const int b = i >> 5, l = i & 31;
+    sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
+  }
+  if (warp == kDecWarpMma) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  grid_dep_wait();
   const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
   const uint32_t b_stage = 4u * (uint32_t)bmax * 128u;  // activations of one stage: 4 k-blocks x N x 128 B
   // activation stages in ONE contiguous block: 6 x 8 KB at N = 16; at N = 32 (16 KB each) a.max_b of them (default 5): with
@@ -104,11 +129,6 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
   const uint32_t m_code2 = (m_tile + 15u) & ~15u;
   const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
-  const uint32_t base = smem_u32(dyn_smem);
-  const uint32_t lut = pin((base + kGemmLutBytes - 1u) & ~(kGemmLutBytes - 1u));
-  const uint32_t bar0 = pin(smem_u32(s_bar));
-  auto bar = [&](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
-
   // ---- one-time setup ----
   if (tid == 0) {
     uint32_t cur[2] = {(base + 1023u) & ~1023u, lut + kGemmLutBytes};
@@ -130,23 +150,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     const uint32_t b_at = place((uint32_t)n_b * b_stage);
     s_b0 = b_at;
     for (int i = 0; i < min(kDecMaxRaw, a.max_raw); ++i) { const uint32_t at = place(kDecRawBytes); if (at) s_raw[ir++] = at; else break; }
-    s_nraw = (im == 2 && b_at != 0u && ir >= 2) ? ir : 0;
-    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecDqWarps / 2); }
+    s_nraw = (im == 2 && b_at != 0u && ir >= 3) ? ir : 0;
+    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), 8); }
     for (int i = 0; i < kDecMaxB; ++i) mbar_init(bar(kDbDone + i), 1);
-    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecDqWarps / 2);
+    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), 8);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kDbDFull + i), 1); mbar_init(bar(kDbDEmpty + i), 4);
       mbar_init(bar(kDbMFull + i), 1); mbar_init(bar(kDbMEmpty + i), kDecDqWarps);
     }
     fence_barrier_init();
-  }
-  for (int i = tid; i < 256 * 32; i += kDecThreads) {
-    const int b = i >> 5, l = i & 31;
-    sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
-  }
-  if (warp == 21) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -162,7 +174,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 
   if (warp < kDecDqWarps) {
     // =============================== dequant: NF4 -> fp16 A operand in TMEM ===============================
-    const int q = warp & 3, hh = (warp >> 2) & 1, pp = warp >> 3;
+    const int q = warp & 3, hh = (warp >> 2) & 1, pp = warp >> 3;   // pp = dequant group
     const int r = q * 32 + lane;
     const uint32_t lut_lane = pin(lut | ((uint32_t)lane << 2));
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0;
@@ -197,7 +209,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       GEMM_DBG_ADD(0);
       const uint32_t m_st = pin(s_mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
-      for (; st < nst; st += 2) {
+      for (; st < nst; st += kDecGroups) {
         mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
         GEMM_DBG_ADD(1);
         const uint32_t wst = pin(s_raw[sw]);
@@ -235,11 +247,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         __syncwarp();
         if (lane == 0) mbar_arrive(afull0 + 8u * (uint32_t)slot);
         GEMM_DBG_ADD(5);
-        sw += 2;
+        sw += kDecGroups;
         if (sw >= n_raw) { sw -= n_raw; phw ^= 1u; }
-        slot += 2;
+        slot += kDecGroups;
         if (slot >= kDecSlots) slot -= kDecSlots;
-        dn += 2;
+        dn += kDecGroups;
         if (dn >= n_b) { dn -= n_b; pdn ^= 1u; }
       }
       st -= nst;
@@ -306,7 +318,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
             y[(long long)__ldg(a.sorted_pairs + row0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
       }
     }
-  } else if (warp == 20) {
+  } else if (warp == kDecWarpProd) {
     // =============================== TMA producer: absmax per item, raw NF4 per stage ===============================
     const uint64_t pol = l2_policy_evict_first();   // weights are read exactly once per step
     const uint32_t am_elt = nested ? 1u : 4u;
@@ -370,7 +382,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       }
     }
     if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[24 + i] = dbg_acc[i];
-  } else if (warp == 22) {
+  } else if (warp == kDecWarpAct) {
     // =============================== TMA producer: activations per stage ===============================
     // Its bytes complete on the SAME barrier as the stage's raw NF4 (the raw producer's expect_tx covers both), so the dequant
     // warps' one wait covers both and the MMA thread waits on nothing but AFull.  It waits for REmpty too: the barrier's
@@ -401,7 +413,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         if (++sb == n_b) { sb = 0; phb ^= 1u; }
       }
     }
-  } else if (warp == 21) {
+  } else if (warp == kDecWarpMma) {
     // =============================== MMA issuer (one thread) ===============================
     // A lone warp runs at one dependent instruction per ~6 cycles and every mbarrier / tcgen05 instruction costs it 60-100, so
     // this loop is kept to one wait, the MMAs (running addresses, constant accumulate flag except in an item's first stage)
@@ -459,7 +471,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   // ---- teardown ----
   tc_fence_before();
   __syncthreads();
-  if (warp == 21) {
+  if (warp == kDecWarpMma) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
   }
@@ -523,7 +535,7 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
     if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
     attr_set[dbg] = true;
   }
-  kern<<<sms, kDecThreads, kDecSmemBytes, (cudaStream_t)stream>>>(a, map_w, map_x16, map_x32);
+  launch_pdl(kern, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
   ++*launches;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }

@@ -253,10 +253,10 @@ int nf4moe_route_topk(const void* logits, int dtype, int T, int E, int k, int32_
   cudaStream_t st = (cudaStream_t)stream;
   const int per_lane = (E + 31) / 32;
   switch (per_lane <= 2 ? per_lane : per_lane <= 4 ? 4 : 8) {
-    case 1: route_topk_kernel<1><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
-    case 2: route_topk_kernel<2><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
-    case 4: route_topk_kernel<4><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
-    case 8: route_topk_kernel<8><<<grid, 256, 0, st>>>(logits, dtype, T, E, k, ids, weights); break;
+    case 1: launch_pdl(route_topk_kernel<1>, dim3(grid), dim3(256), 0, st, logits, dtype, T, E, k, ids, weights); break;
+    case 2: launch_pdl(route_topk_kernel<2>, dim3(grid), dim3(256), 0, st, logits, dtype, T, E, k, ids, weights); break;
+    case 4: launch_pdl(route_topk_kernel<4>, dim3(grid), dim3(256), 0, st, logits, dtype, T, E, k, ids, weights); break;
+    case 8: launch_pdl(route_topk_kernel<8>, dim3(grid), dim3(256), 0, st, logits, dtype, T, E, k, ids, weights); break;
     default: return fail(NF4MOE_EINVAL, "route_topk: unsupported E %d", E);
   }
   CHECK_LAUNCH("route_topk_kernel");
@@ -279,8 +279,8 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(bucket)");
     attr_set = true;
   }
-  bucket_kernel<<<1, kBucketThreads, smem, (cudaStream_t)stream>>>(ids, (int)n, E, expert_offsets, sorted_pairs,
-                                                                  active_experts, meta, tile_list, tile_rows);
+  launch_pdl(bucket_kernel, dim3(1), dim3(kBucketThreads), smem, (cudaStream_t)stream, ids, (int)n, E, expert_offsets, sorted_pairs,
+             active_experts, meta, tile_list, tile_rows);
   CHECK_LAUNCH("bucket_kernel");
   return 0;
 }
@@ -295,8 +295,8 @@ int nf4moe_permute_rows(const void* x, const int32_t* sorted_pairs, const int32_
   if (int rc = device_info(&di)) return rc;
   const long long rows = (long long)T * k;
   const int grid = (int)std::min<long long>((rows + 7) / 8, (long long)di.sms * 8);
-  permute_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)x, sorted_pairs, meta, (int)rows, k, H,
-                                                             (__half*)x_sorted);
+  launch_pdl(permute_rows_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __half*)x, sorted_pairs, meta, (int)rows, k, H,
+             (__half*)x_sorted);
   CHECK_LAUNCH("permute_rows_kernel");
   return 0;
 }
@@ -310,7 +310,7 @@ int nf4moe_combine(const void* y, const float* weights, const int32_t* ids, int 
   if (int rc = device_info(&di)) return rc;
   const long long total = (long long)T * (H / 8);
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 8);
-  combine_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y, weights, ids, E, T, k, H, (__half*)out);
+  launch_pdl(combine_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __half*)y, weights, ids, E, T, k, H, (__half*)out);
   CHECK_LAUNCH("combine_kernel");
   return 0;
 }

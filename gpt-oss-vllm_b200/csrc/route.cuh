@@ -14,6 +14,8 @@ namespace nf4moe {
 template <int kPerLane>
 __global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict__ logits, int dtype, int T, int E, int k,
                                                          int32_t* __restrict__ ids, float* __restrict__ weights) {
+  grid_dep_launch();
+  grid_dep_wait();   // launched with launch_pdl(): the logits (and a previous layer's readers of ids/weights) are done past here
   const int lane = threadIdx.x & 31;
   const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (t >= T) return;
@@ -81,6 +83,8 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
   __shared__ int s_count[256];
   __shared__ int s_off[257];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  grid_dep_launch();
+  grid_dep_wait();
   const int n_pad = (n_pairs + 127) & ~127;
   for (int i = tid; i < n_pad; i += kBucketThreads) {
     int e = i < n_pairs ? ids[i] : -1;
@@ -170,6 +174,8 @@ __global__ void __launch_bounds__(256) permute_rows_kernel(const __half* __restr
                                                            const int32_t* __restrict__ sorted_pairs,
                                                            const int32_t* __restrict__ meta, int n_rows, int k, int H,
                                                            __half* __restrict__ xs) {
+  grid_dep_launch();
+  grid_dep_wait();
   const int lane = threadIdx.x & 31;
   const int n_kept = meta[1];
   const int vec = H / 8;
@@ -189,6 +195,8 @@ __global__ void __launch_bounds__(256) permute_rows_kernel(const __half* __restr
 __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ y, const float* __restrict__ w,
                                                       const int32_t* __restrict__ ids, int E, int T, int k, int H,
                                                       __half* __restrict__ out) {
+  grid_dep_launch();
+  grid_dep_wait();
   const int vec = H / 8;
   const long long total = (long long)T * vec;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;

@@ -105,8 +105,12 @@ class EPMoELayer:
         W = plan.world
         self.cap = plan.capacity(max_tokens, top_k, capacity_factor)
         n = W * self.cap
-        # T_all * k pairs in flight globally; the tcgen05 regime pays off past 64 rows per layer call (see gemm_tc.cuh)
-        self.regime = regime if regime is not None else (_lib.REGIME_GEMM if max_tokens * W > 64 else _lib.REGIME_GEMV)
+        # default: the library's own choice for (W * cap rows, this rank's experts) -- GEMV for a handful of rows, the decode
+        # tcgen05 kernel while token tiles stay <= 32 rows, the prefill grouped GEMM above (nf4moe_auto_regime)
+        self.regime = regime if regime is not None else _lib.REGIME_AUTO
+        self.regime_resolved = self.regime
+        if self.regime == _lib.REGIME_AUTO and self.device.type == "cuda":
+            self.regime_resolved = int(_lib.load_library().nf4moe_auto_regime(n, 1, w13.num_experts))
         f16 = dict(dtype=torch.float16, device=self.device)
         i32 = dict(dtype=torch.int32, device=self.device)
         self.send_rows = torch.zeros(n, hidden_size, **f16)
@@ -302,7 +306,8 @@ def bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, m
                                        f"{E} experts expert-parallel over {world} GPUs ({El} per GPU), NCCL all-to-all dispatch/"
                                        f"combine (BASELINE.json configs[3] shape)", "hidden": H, "intermediate": I, "experts": E,
                            "top_k": K_TOP, "layers": L, "tokens_per_rank": T, "absmax": args.absmax, "parallelism": f"ep{world}",
-                           "regime": "gemm" if layers[0].regime == _lib.REGIME_GEMM else "gemv",
+                           "regime": {_lib.REGIME_GEMV: "gemv", _lib.REGIME_GEMM: "gemm_exact",
+                                      _lib.REGIME_GEMM_FAST: "gemm_fast (decode tcgen05 kernel)"}.get(layers[0].regime_resolved, "auto"),
                            "capacity_rows_per_peer": layers[0].cap, "cuda_graph": graph is not None,
                            "l2": f"{wbytes * L / 1e9:.2f} GB of weights streamed per rank per step >> 126 MB L2",
                            "per_layer_us": ms_per_step * 1e3 / L},
@@ -310,7 +315,7 @@ def bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, m
                 "e2e": {"value": T_all / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2 + hlg.numel() * 2,
                         "d2h_bytes_per_step": hout.numel() * 2, "ms_per_step": e2e_ms,
                         "api": "EPMoELayer.forward(x, router_logits) x layers, pinned host buffers, per rank"},
-                "gpu_launches": (5 + (2 if layers[0].regime == _lib.REGIME_GEMM else 1)) * L * K,
+                "gpu_launches": (5 + (1 if layers[0].regime_resolved == _lib.REGIME_GEMV else 2)) * L * K,
                 "collectives_per_layer": 3, "wire_bytes_per_rank_per_layer": wire,
                 "roofline": {"bound": "hbm", "kernel": "expert_rows chain (bucket + w13 + w2) on this rank's experts",
                              "achieved": wbytes / d / 1e9, "peak": peak, "unit": "GB/s", "frac": wbytes / d / 1e9 / peak,
