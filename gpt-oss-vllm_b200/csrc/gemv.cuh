@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a)
   constexpr int NRED = 4 * NT;                 // reducer warps per item (one table hole each)
   constexpr int NB = 240 / (NTEAMS * TW * NRED) >= 4 ? 4 : 240 / (NTEAMS * TW * NRED);  // partial buffers per team
   static_assert(NB >= 2 && NRED <= TW && NTEAMS * NB * 2 <= kNumPartBars, "bad team configuration");
+  grid_dep_launch();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nkb = NKB_T ? NKB_T : a.w.nkb;
   const uint32_t row_bytes = (uint32_t)nkb * 32u;
@@ -137,6 +138,9 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a)
       }
     fence_barrier_init();
   }
+  // launched with launch_pdl(): table fill and barrier setup above overlap the previous kernel's tail; everything below reads
+  // what the bucket (and, for w2, the w13) kernel wrote
+  grid_dep_wait();
   if (warp == 1) {
     // virtual experts: (expert e, chunk c) for every active expert and every 8*NT-token chunk of its routed rows
     uint32_t* virt = const_cast<uint32_t*>(s_virt);

@@ -118,7 +118,7 @@ int launch_gemv_inst(const GemvArgs& args, int sms, cudaStream_t stream) {
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemv)");
     attr_set = true;
   }
-  kern<<<sms, kGemvThreads, kGemvSmemBytes, stream>>>(args);
+  launch_pdl(kern, dim3(sms), dim3(kGemvThreads), kGemvSmemBytes, stream, args);
   CHECK_LAUNCH("gemv_kernel");
   return 0;
 }
