@@ -45,6 +45,8 @@ def parse():
     p.add_argument("--absmax", default="nested", choices=["nested", "flat"])
     p.add_argument("--regime", default="auto", choices=["auto", "gemv", "gemm", "gemm_fast"],
                    help="auto = what the drop-in apply() uses: GEMV up to 8 tokens, decode tcgen05 kernel above")
+    p.add_argument("--ep-capacity-factor", type=float, default=2.0,
+                   help="N>1: rows reserved per peer = factor x mean load (an overflow is detected and fatal); 0 = worst case")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-prefill", action="store_true", help="skip the extra 8192-token prefill measurement")
     p.add_argument("--prefill-tokens", type=int, default=8192)
@@ -260,7 +262,7 @@ def run_ours(args):
     eff = pkg.ops.auto_regime(T, TOP_K, E) if regime == pkg.REGIME_AUTO else regime     # what AUTO resolves to
     eff_name = {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "gemm_exact", pkg.REGIME_GEMM_FAST: "gemm_fast"}[eff]
     use_tc = eff != pkg.REGIME_GEMV
-    dec_kernel = use_tc and T * TOP_K <= 32 * E
+    dec_kernel = use_tc and (T * TOP_K <= 40 * E or (E <= 8 and T * TOP_K <= 128 * E))   # gemm_tile_tokens == 32
     stack = make_stack(pkg, dev, L, E, code2)
     g = torch.Generator(device=dev).manual_seed(SEED + 1)
     x = torch.randn(T, H, generator=g, device=dev).half()

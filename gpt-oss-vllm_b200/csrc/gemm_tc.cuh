@@ -33,6 +33,7 @@
 
 namespace nf4moe {
 
+constexpr int kDecMaxMeanRows = 40;     // mean routed rows per expert up to which token tiles are 32 rows (decode tcgen05 kernel)
 constexpr int kDecAutoMinTokens = 8;    // tokens; up to this nf4moe_moe_forward(AUTO) uses the GEMV, above it a tcgen05 kernel
 constexpr int kDqGroups = 3;            // dequant warpgroups; k-block c of a CTA belongs to group c % 3
 constexpr int kGemmThreads = (4 + 4 * kDqGroups + 4) * 32;   // 640: control WG, 3 dequant WGs, epilogue WG
@@ -667,7 +668,14 @@ inline long long*& gemm_debug_buffer() {
 // stages fit beside the 64 KB decode table and two 23 KB flat-absmax stages.
 inline int gemm_tile_tokens(int T, int k, int E, bool nested = false) {
   (void)nested;
-  if ((long long)T * k <= 32ll * E) return 32;
+  static const int tile_env = getenv("NF4MOE_TILE") ? atoi(getenv("NF4MOE_TILE")) : 0;   // crossover measurements only
+  if (tile_env == 32 || tile_env == 160) return tile_env;
+  // 32-row tiles (decode tcgen05 kernel; an expert with more rows gets several tiles and its weights are decoded once per tile)
+  // while the mean routed rows per expert stay <= 40 (measured crossover with the 160-row prefill pipeline: 48 rows per expert at
+  // E = 32), or <= 128 with at most 8 experts (an expert-parallel rank: few experts, so the extra tiles are what fills 148 SMs;
+  // E = 4..8 measured equal or faster up to 128 rows per expert)
+  const long long pairs = (long long)T * k;
+  if (pairs <= (long long)kDecMaxMeanRows * E || (E <= 8 && pairs <= 128ll * E)) return 32;
   return 160;
 }
 

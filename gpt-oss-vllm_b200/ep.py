@@ -192,12 +192,15 @@ def bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, m
     nested = args.absmax == "nested"
     plan = EPPlan(rank, world, E)
     El = plan.experts_per_rank
+    # fixed per-peer capacity keeps the exchange graph-capturable (no host read of counts); 2 x the mean load is > 6 sigma of the
+    # per-peer count for near-uniform routing, and check_overflow() below makes a dropped pair fatal rather than silent
+    cap_factor = getattr(args, "ep_capacity_factor", 0.0) or None
     g = torch.Generator(device=dev).manual_seed(20250805 + 17 * rank)
     layers = []
     for _ in range(L):
         w13 = NF4ExpertWeights.quantize((torch.randn(El, 2 * I, H, generator=g, device=dev) * 0.02).half(), code2)
         w2 = NF4ExpertWeights.quantize((torch.randn(El, H, I, generator=g, device=dev) * 0.02).half(), code2)
-        layers.append(EPMoELayer(w13, w2, plan, K_TOP, H, T, dev, device_ops=CudaEPOps(nested=nested)))
+        layers.append(EPMoELayer(w13, w2, plan, K_TOP, H, T, dev, device_ops=CudaEPOps(nested=nested), capacity_factor=cap_factor))
     x = torch.randn(T, H, generator=g, device=dev).half()
     logits = [torch.randn(T, E, generator=g, device=dev).half() for _ in range(L)]
     outs = [torch.empty(T, H, dtype=torch.float16, device=dev) for _ in range(L)]
@@ -308,7 +311,10 @@ def bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, m
                            "top_k": K_TOP, "layers": L, "tokens_per_rank": T, "absmax": args.absmax, "parallelism": f"ep{world}",
                            "regime": {_lib.REGIME_GEMV: "gemv", _lib.REGIME_GEMM: "gemm_exact",
                                       _lib.REGIME_GEMM_FAST: "gemm_fast (decode tcgen05 kernel)"}.get(layers[0].regime_resolved, "auto"),
-                           "capacity_rows_per_peer": layers[0].cap, "cuda_graph": graph is not None,
+                           "capacity_rows_per_peer": layers[0].cap,
+                           "capacity": ("worst case (T*k rows per peer)" if cap_factor is None else
+                                        f"{cap_factor} x mean load per peer, overflow checked after the run (none)"),
+                           "cuda_graph": graph is not None,
                            "l2": f"{wbytes * L / 1e9:.2f} GB of weights streamed per rank per step >> 126 MB L2",
                            "per_layer_us": ms_per_step * 1e3 / L},
                 "clocks": clocks,

@@ -35,6 +35,11 @@ def make_layer(pkg, dev, seed, E, H, I, std=0.05):
 
 
 # ------------------------------------------------------------------------------------------------- dequant
+
+def expected_tile_rows(T, k, E):
+    """gemm_tile_tokens (gemm_tc.cuh): 32-row token tiles while the mean rows per expert stay <= 40 (or <= 128 with <= 8 experts)."""
+    return 32 if (T * k <= 40 * E or (E <= 8 and T * k <= 128 * E)) else 160
+
 @pytest.mark.parametrize("nested", [True, False])
 def test_dequant_bit_exact_random(pkg, cuda_device, nested):
     rng = np.random.default_rng(11)
@@ -146,7 +151,7 @@ def test_bucket_stable_sort(pkg, cuda_device, T, k, E):
     active = np.nonzero(counts)[0]
     assert meta[0] == active.size and meta[1] == keep.sum() and meta[3] == counts.max()
     assert np.array_equal(b["active_experts"].cpu().numpy()[:active.size], active)
-    tile_rows = 32 if T * k <= 32 * E else 160            # what the grouped GEMM expects for this (T, k, E)
+    tile_rows = expected_tile_rows(T, k, E)               # what the grouped GEMM expects for this (T, k, E)
     tiles = b["tile_list"].cpu().numpy()[:4 * meta[2]].reshape(-1, 4)
     exp_tiles = []
     for e in active:
@@ -428,7 +433,7 @@ def _gemm_stage_check(pkg, dev, T, E, H, I, k, nested, seed, regime=None, std=0.
 
 
 @pytest.mark.parametrize("T,E,H,I,k", [(3, 8, 64, 64, 2), (40, 8, 256, 192, 4), (300, 8, 256, 192, 4), (700, 4, 192, 320, 2),
-                                       (1100, 4, 128, 64, 1)])
+                                       (1100, 4, 128, 64, 1), (100, 4, 192, 128, 2), (200, 8, 128, 192, 4)])
 @pytest.mark.parametrize("nested", [False, True])
 @pytest.mark.parametrize("fast", [False, True])
 def test_gemm_stages_vs_oracle(pkg, cuda_device, T, E, H, I, k, nested, fast):
@@ -465,7 +470,7 @@ def test_moe_forward_gemm_regime_vs_oracle(pkg, cuda_device, T, E, H, I, k):
     # AUTO is exactly the regime nf4moe_auto_regime names: the decode tcgen05 kernel (FAST operand) while token tiles are
     # <= 32 rows, the EXACT prefill GEMM above
     auto = pkg.ops.auto_regime(T, k, E)
-    assert auto == (pkg.REGIME_GEMM_FAST if T * k <= 32 * E else pkg.REGIME_GEMM)
+    assert auto == (pkg.REGIME_GEMM_FAST if expected_tile_rows(T, k, E) == 32 else pkg.REGIME_GEMM)
     out_a = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=pkg.REGIME_AUTO)
     assert torch.equal(out_a, pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=auto))
     assert_moe_close(out_a.cpu().numpy(), ref)
