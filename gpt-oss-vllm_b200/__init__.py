@@ -9,8 +9,9 @@ or through the alias module `nf4moe_b200` at the repo root.
 from . import _lib, ops  # noqa: F401
 from ._lib import (ACT_CHUNK_SILU, ACT_SWIGLU_OAI, REGIME_AUTO, REGIME_GEMM, REGIME_GEMM_FAST, REGIME_GEMV, Nf4MoeError,  # noqa: F401
                    load_library)
+from .graphed import GraphedForward  # noqa: F401
 from .moe_method import B200NF4MoEConfig, B200NF4MoEMethod, NF4MoELayer  # noqa: F401
 from .quant import BLOCKSIZE, NESTED_BLOCKSIZE, NF4ExpertWeights  # noqa: F401
 
-__all__ = ["NF4ExpertWeights", "B200NF4MoEConfig", "B200NF4MoEMethod", "NF4MoELayer", "ops", "load_library",
+__all__ = ["NF4ExpertWeights", "B200NF4MoEConfig", "B200NF4MoEMethod", "NF4MoELayer", "GraphedForward", "ops", "load_library",
            "Nf4MoeError"]

@@ -57,6 +57,36 @@ def test_virtual_ranks_bit_identical_to_single_gpu(pkg, cuda_device, world, T, E
         assert_moe_close(out.cpu().numpy(), ref)
 
 
+@pytest.mark.parametrize("world,T,E", [(2, 64, 32), (4, 48, 32), (8, 64, 32), (8, 32, 128)])
+def test_virtual_ranks_default_regime_and_capacity_factor(pkg, cuda_device, world, T, E):
+    """The configuration bench.py --gpus N runs: library-chosen regime (decode tcgen05 kernel on the padded capacity rows) and
+    2 x mean-load capacity per peer; near-uniform routing must not overflow and every rank must match the oracle."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    H, I, k = 192, 128, 4
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 300 + world + T, E, H, I)
+    rng = np.random.default_rng(11)
+    layers, xs, lgs = [], [], []
+    for r in range(world):
+        plan = ep.EPPlan(r, world, E)
+        layers.append(ep.EPMoELayer(ep.shard_experts(w13, plan), ep.shard_experts(w2, plan), plan, k, H, T, cuda_device,
+                                    capacity_factor=2.0))
+        assert layers[-1].cap <= T * k and layers[-1].regime == pkg.REGIME_AUTO
+        xs.append(torch.from_numpy(rng.standard_normal((T, H)).astype(np.float16)).to(cuda_device))
+        lgs.append(torch.from_numpy(rng.standard_normal((T, E)).astype(np.float16)).to(cuda_device))
+    for r in range(world):
+        layers[r].prepare(xs[r], router_logits=lgs[r])
+    exchange([l.send_ids for l in layers], [l.recv_ids for l in layers], world)
+    exchange([l.send_rows for l in layers], [l.recv_rows for l in layers], world)
+    for l in layers:
+        l.compute()
+    exchange([l.y_rows for l in layers], [l.back_rows for l in layers], world)
+    for r in range(world):
+        out = layers[r].finish()
+        layers[r].check_overflow()
+        ref = orc.moe_forward_from_states(xs[r].cpu().numpy(), lgs[r].cpu().numpy(), st13, st2, k=k)
+        assert_moe_close(out.cpu().numpy(), ref)
+
+
 def test_ep_pack_layout_and_overflow_flag(pkg, cuda_device):
     ep = importlib.import_module("gpt-oss-vllm_b200.ep")
     E, H, I, k, T, world = 8, 64, 64, 2, 12, 4

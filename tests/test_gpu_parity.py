@@ -515,3 +515,24 @@ def test_loader_to_gpu_forward(pkg, cuda_device, tmp_path):
     lg = rng.standard_normal((T, E)).astype(np.float16)
     out = pkg.ops.moe_forward(torch.from_numpy(x).to(cuda_device), w13, w2, k, router_logits=torch.from_numpy(lg).to(cuda_device))
     assert_moe_close(out.cpu().numpy(), orc.moe_forward_from_states(x, lg, st13, st2, k=k))
+
+
+def test_graphed_forward_matches_eager(pkg, cuda_device):
+    """GraphedForward (the serving-engine form: static buffers, one CUDA-graph replay per call, host in / host out) returns
+    exactly what the eager apply_legacy calls return, for several different inputs through the same captured graph."""
+    E, H, I, k, T = 32, 256, 128, 4, 24
+    _, _, w13, w2 = make_layer(pkg, cuda_device, 77, E, H, I)
+    method = pkg.B200NF4MoEMethod(top_k=k)
+    layer = torch.nn.Module()
+    method.bind(layer, w13, w2)
+    g = torch.Generator().manual_seed(3)
+    mk = lambda: (torch.randn(T, H, generator=g).half().pin_memory(), torch.randn(T, E, generator=g).half().pin_memory())
+    x0, lg0 = mk()
+    graphed = pkg.GraphedForward(lambda x, lg: method.apply_legacy(layer, x, lg, k), [x0.to(cuda_device), lg0.to(cuda_device)])
+    for _ in range(3):
+        x, lg = mk()
+        got = graphed(x, lg)
+        ref = method.apply_legacy(layer, x.to(cuda_device), lg.to(cuda_device), k)
+        assert torch.equal(got.to(cuda_device), ref)
+    with pytest.raises(ValueError):
+        graphed(x[:5], lg)
