@@ -247,6 +247,8 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # rank 0's stdout carries ONE JSON line: NCCL's own banner / debug lines (NCCL_DEBUG set on the box) go to a file instead
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/nf4moe_nccl_%h_%p.log")
         dist.init_process_group("nccl", device_id=dev)
     if world != args.gpus and rank == 0:
         print(f"warning: --gpus {args.gpus} but WORLD_SIZE {world}", file=sys.stderr)
