@@ -173,6 +173,8 @@ extern "C" {
 
 int nf4moe_version(void) { return NF4MOE_VERSION; }
 
+constexpr long long kBucketClusterMinPairs = 2048;   // pairs from which the 8-CTA cluster bucket kernel replaces the single CTA
+
 // What NF4MOE_REGIME_AUTO resolves to (measured on B200, gpt-oss-20b shapes, profiles/r1c_kernel_times.txt):
 //   T <= 8                       mma.sync GEMV (few active experts, 3.3-3.5 TB/s; the tcgen05 pipeline's fill costs more)
 //   token tiles of <= 32 rows    decode-regime tcgen05 kernel (gemm_dec.cuh; FAST operand), 3.1-3.3 TB/s vs the GEMV's 2.4-2.9
@@ -272,7 +274,28 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
     return fail(NF4MOE_EINVAL, "bucket: tile_rows must be a multiple of 16 in 16..256 (or 0 = automatic)");
   const long long n = (long long)T * k;
   const size_t smem = (size_t)((n + 127) & ~127ll);
-  if (smem > 200 * 1024) return fail(NF4MOE_EINVAL, "bucket: T*k = %lld exceeds the single-CTA limit of 204800 pairs", n);
+  if (smem > 200 * 1024) return fail(NF4MOE_EINVAL, "bucket: T*k = %lld exceeds the limit of 204800 pairs", n);
+  static const bool cluster_on = !(getenv("NF4MOE_BUCKET_CLUSTER") && atoi(getenv("NF4MOE_BUCKET_CLUSTER")) == 0);
+  if (cluster_on && n >= kBucketClusterMinPairs) {   // prefill-sized: one cluster of 8 CTAs, a chunk of the pair list each
+    const size_t chunk = (size_t)((((n + kBucketCluster - 1) / kBucketCluster) + 127) & ~127ll);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(kBucketCluster);
+    cfg.blockDim = dim3(kBucketThreads);
+    cfg.dynamicSmemBytes = chunk;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = kBucketCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, bucket_cluster_kernel, ids, (int)n, E, expert_offsets, sorted_pairs, active_experts, meta,
+                                       tile_list, tile_rows);
+    if (e != cudaSuccess) return cuda_fail(e, "bucket_cluster_kernel");
+    CHECK_LAUNCH("bucket_cluster_kernel");
+    return 0;
+  }
   static thread_local bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);

@@ -168,6 +168,123 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
   }
 }
 
+// Prefill-sized batches: the same stable counting sort by ONE thread-block cluster of kBucketCluster CTAs (the single CTA takes
+// 155 us for 8192 x 4 pairs, 8 % of the prefill layer).  CTA r sorts the contiguous chunk r of the pair list; the per-expert
+// counts of all CTAs are exchanged through distributed shared memory, so a pair's position is
+// offset[e] + (matches in lower chunks) + (rank inside its chunk): the order inside an expert stays ascending pair index.
+constexpr int kBucketCluster = 8;
+__global__ void __launch_bounds__(kBucketThreads) bucket_cluster_kernel(const int32_t* __restrict__ ids, int n_pairs, int E,
+                                                                        int32_t* __restrict__ expert_offsets,
+                                                                        int32_t* __restrict__ sorted_pairs,
+                                                                        int32_t* __restrict__ active_experts,
+                                                                        int32_t* __restrict__ meta,
+                                                                        int32_t* __restrict__ tile_list, int tile_rows) {
+  extern __shared__ uint8_t s_ids[];  // this CTA's chunk, padded to a multiple of 128 with 0xFF
+  __shared__ int s_count[256];        // this chunk's matches per expert (read by the other CTAs of the cluster)
+  __shared__ int s_tot[256];
+  __shared__ int s_before[256];
+  __shared__ int s_off[257];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  grid_dep_launch();
+  grid_dep_wait();
+  uint32_t rank, nc;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(nc));
+  const int chunk = (((n_pairs + (int)nc - 1) / (int)nc) + 127) & ~127;
+  const int c0 = min(n_pairs, (int)rank * chunk), c1 = min(n_pairs, c0 + chunk);
+  const int n_loc = c1 - c0, n_pad128 = (n_loc + 127) & ~127;
+  for (int i = tid; i < n_pad128; i += kBucketThreads) {
+    const int e = i < n_loc ? ids[c0 + i] : -1;
+    s_ids[i] = (e >= 0 && e < E) ? (uint8_t)e : (uint8_t)0xFF;
+  }
+  if (tid < 256) s_count[tid] = 0;
+  __syncthreads();
+  for (int e = warp; e < E; e += 32) {
+    const uint32_t pat = 0x01010101u * (uint32_t)e;
+    int c = 0;
+    for (int i = lane * 4; i < n_pad128; i += 128) c += __popc(__vcmpeq4(*reinterpret_cast<const uint32_t*>(s_ids + i) ^ pat, 0u)) >> 3;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) s_count[e] = c;
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (tid < 256) {   // totals over the cluster and the matches in lower chunks, through distributed shared memory
+    int tot = 0, before = 0;
+    const uint32_t mine = smem_u32(&s_count[tid]);
+    for (uint32_t r = 0; r < nc; ++r) {
+      uint32_t remote, v;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(mine), "r"(r));
+      asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(remote) : "memory");
+      tot += (int)v;
+      if (r < rank) before += (int)v;
+    }
+    s_tot[tid] = tot;
+    s_before[tid] = before;
+  }
+  __syncthreads();
+  if (warp == 0) {  // exclusive scan over <= 256 experts, 8 per lane
+    int loc[8], run = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { loc[j] = run; run += s_tot[lane * 8 + j]; }
+    int inc = run;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += n;
+    }
+    const int base = inc - run;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s_off[lane * 8 + j] = base + loc[j];
+    if (lane == 31) s_off[256] = inc;
+  }
+  __syncthreads();
+  if (rank == 0) {
+    for (int e = tid; e <= E; e += kBucketThreads) expert_offsets[e] = s_off[e];
+    if (tid == 0) {
+      int na = 0, nt = 0, mx = 0;
+      for (int e = 0; e < E; ++e) {
+        const int c = s_tot[e];
+        if (c > 0) {
+          active_experts[na++] = e;
+          mx = max(mx, c);
+          const int ntl = (c + tile_rows - 1) / tile_rows;
+          const int sz = (((c + ntl - 1) / ntl) + 15) & ~15;
+          if (tile_list)
+            for (int r = 0; r < c; r += sz) {
+              tile_list[4 * nt] = e; tile_list[4 * nt + 1] = s_off[e] + r; tile_list[4 * nt + 2] = min(sz, c - r); tile_list[4 * nt + 3] = 0;
+              ++nt;
+            }
+          else
+            nt += (c + sz - 1) / sz;
+        }
+      }
+      for (int i = na; i < E; ++i) active_experts[i] = -1;
+      meta[0] = na; meta[1] = s_off[E]; meta[2] = nt; meta[3] = mx;
+    }
+  }
+  for (int e = warp; e < E; e += 32) {
+    const uint32_t pat = 0x01010101u * (uint32_t)e;
+    int run = s_off[e] + s_before[e];
+    for (int i = lane * 4; i < n_pad128; i += 128) {
+      const uint32_t z = __vcmpeq4(*reinterpret_cast<const uint32_t*>(s_ids + i) ^ pat, 0u);
+      const int mine = __popc(z) >> 3;
+      int inc = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int nb = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += nb;
+      }
+      int pos = run + inc - mine;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if ((z >> (8 * j)) & 1u) sorted_pairs[pos++] = c0 + i + j;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+  }
+  // no CTA may exit while another can still read its s_count
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // x_sorted[s,:] = x[sorted_pairs[s]/k,:]; one warp per row, 16-byte accesses.  Rows past meta[1] are zeroed so the
 // grouped GEMM's last tile reads defined data.
 __global__ void __launch_bounds__(256) permute_rows_kernel(const __half* __restrict__ x,

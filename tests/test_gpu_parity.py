@@ -132,7 +132,8 @@ def test_route_topk_golden_fixture(pkg, cuda_device, golden):
     np.testing.assert_allclose(w.cpu().numpy(), arrays["route/weights"], rtol=0, atol=1e-6)
 
 
-@pytest.mark.parametrize("T,k,E", [(1, 4, 32), (7, 4, 32), (64, 4, 32), (300, 4, 128), (8192, 4, 32), (5, 1, 32)])
+@pytest.mark.parametrize("T,k,E", [(1, 4, 32), (7, 4, 32), (64, 4, 32), (300, 4, 128), (8192, 4, 32), (5, 1, 32),
+                                   (513, 4, 32), (2001, 4, 128), (4099, 2, 8)])   # >= 2048 pairs: the 8-CTA cluster kernel
 def test_bucket_stable_sort(pkg, cuda_device, T, k, E):
     rng = np.random.default_rng(22)
     ids = np.stack([rng.choice(E, size=k, replace=False) for _ in range(T)]).astype(np.int32)
