@@ -455,6 +455,12 @@ def run_ours(args):
 
 def main():
     args = parse()
+    # The driver reads ONE JSON line from stdout.  C libraries write to file descriptor 1 behind Python's back (NCCL prints its
+    # version banner there), so fd 1 is pointed at stderr and Python's own sys.stdout keeps the original descriptor.
+    sys.stdout.flush()
+    keep = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(keep, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
