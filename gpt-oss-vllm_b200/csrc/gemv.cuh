@@ -410,4 +410,32 @@ __global__ void __launch_bounds__(256) chunk_silu_kernel(const __half* __restric
   }
 }
 
+// Biased up-projection: raw [rows, 2I] (fp16 products of the w13 kernel) + w13_bias[e] -> activation -> h [rows, I].  The row's
+// expert is ids[sorted_pairs[row]].  Replaces the bias add of gpt-oss's expert MLP (V/model_executor/models/gpt_oss.py:199),
+// which neither the reference nor vLLM's bnb method has.  act: interleaved clamped SwiGLU or chunk + SiLU.
+__global__ void __launch_bounds__(256) bias_act_kernel(const __half* __restrict__ raw, const __half* __restrict__ bias,
+                                                       const int32_t* __restrict__ ids, const int32_t* __restrict__ sorted_pairs,
+                                                       const int32_t* __restrict__ meta, int I, int act, __half* __restrict__ h) {
+  grid_dep_launch();
+  grid_dep_wait();
+  const long long total = (long long)meta[1] * I;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / I, c = i - r * I;
+    const int e = ids[sorted_pairs[r]];
+    const __half* b = bias + (long long)e * 2 * I;
+    const __half* x = raw + r * 2 * I;
+    float g, u;
+    if (act == NF4MOE_ACT_SWIGLU_OAI) {
+      g = __fadd_rn(__half2float(x[2 * c]), __half2float(b[2 * c]));
+      u = __fadd_rn(__half2float(x[2 * c + 1]), __half2float(b[2 * c + 1]));
+      h[i] = __float2half_rn(swiglu_oai(g, u));
+    } else {
+      g = __fadd_rn(__half2float(x[c]), __half2float(b[c]));
+      u = __fadd_rn(__half2float(x[I + c]), __half2float(b[I + c]));
+      h[i] = __float2half_rn(silu_mul(g, u));
+    }
+  }
+}
+
 }  // namespace nf4moe

@@ -324,16 +324,26 @@ int nf4moe_permute_rows(const void* x, const int32_t* sorted_pairs, const int32_
   return 0;
 }
 
+static int combine_impl(const void* y, const float* weights, const int32_t* ids, int E, int T, int k, int H, void* out,
+                        const void* w2_bias, void* stream);
+
 int nf4moe_combine(const void* y, const float* weights, const int32_t* ids, int E, int T, int k, int H, void* out,
                    void* stream) {
+  return combine_impl(y, weights, ids, E, T, k, H, out, nullptr, stream);
+}
+
+static int combine_impl(const void* y, const float* weights, const int32_t* ids, int E, int T, int k, int H, void* out,
+                        const void* w2_bias, void* stream) {
   if (!y || !weights || !out || T < 0 || k <= 0 || H <= 0 || H % 8) return fail(NF4MOE_EINVAL, "combine: bad arguments");
+  if (w2_bias && (!ids || !aligned16(w2_bias))) return fail(NF4MOE_EINVAL, "combine: w2_bias needs topk ids and 16-byte alignment");
   if (!aligned16(y) || !aligned16(out)) return fail(NF4MOE_EALIGN, "combine: 16-byte alignment required");
   if (T == 0) return 0;
   DevInfo di;
   if (int rc = device_info(&di)) return rc;
   const long long total = (long long)T * (H / 8);
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 8);
-  launch_pdl(combine_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __half*)y, weights, ids, E, T, k, H, (__half*)out);
+  launch_pdl(combine_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __half*)y, weights, ids, E, T, k, H, (__half*)out,
+             (const __half*)w2_bias);
   CHECK_LAUNCH("combine_kernel");
   return 0;
 }
@@ -409,7 +419,8 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 
 // bucket -> (permute) -> w13 (+activation) -> w2 for the (row, slot) pairs of `ids` [T, k]; y fp16 [T*k, H] in pair order.
 static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* y, int T,
-                       int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches) {
+                       int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches,
+                       const void* w13_bias = nullptr) {
   cudaStream_t st = (cudaStream_t)stream;
   if (regime == NF4MOE_REGIME_AUTO) {
     // the tcgen05 kernels need 16-row / 64-column granularity and K <= 4096; other shapes stay on the GEMV
@@ -424,16 +435,25 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
   const int tile_rows = gemm ? gemm_tile_tokens(T, k, E, w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr) : 0;
   if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
   *launches += g_launches; g_launches = 0;
-  __half* h_dst = act == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
+  // with an up-projection bias the w13 kernels store their raw products and bias_act_kernel applies bias + activation
+  const int act_k = w13_bias ? NF4MOE_ACT_CHUNK_SILU : act;   // CHUNK_SILU = "store raw [rows, 2I]" for the w13 kernels
+  __half* h_dst = act_k == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
   if (gemm) {
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
-    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act, mode, h_dst, stream)) return rc;
+    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream)) return rc;
   } else {
-    if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act, h_dst, stream)) return rc;
+    if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act_k, h_dst, stream)) return rc;
   }
   *launches += g_launches; g_launches = 0;
-  if (act == NF4MOE_ACT_CHUNK_SILU) {
+  if (w13_bias) {
+    DevInfo di;
+    if (int rc = device_info(&di)) return rc;
+    launch_pdl(bias_act_kernel, dim3(di.sms * 4), dim3(256), 0, st, (const __half*)ws.raw, (const __half*)w13_bias, ids,
+               (const int32_t*)ws.sorted, (const int32_t*)ws.meta, I, act, ws.h);
+    CHECK_LAUNCH("bias_act_kernel");
+    *launches += g_launches; g_launches = 0;
+  } else if (act == NF4MOE_ACT_CHUNK_SILU) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
     chunk_silu_kernel<<<di.sms * 4, 256, 0, st>>>(ws.raw, ws.meta, I, ws.h);
@@ -459,7 +479,17 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
                        const float* topk_weights, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* out, int T,
                        int E, int H, int I, int k, int act, int regime, void* workspace, size_t workspace_bytes,
                        int32_t* topk_ids_out, float* topk_weights_out, void* stream) {
+  return nf4moe_moe_forward_bias(x, router_logits, logits_dtype, topk_ids, topk_weights, w13, w2, nullptr, nullptr, out, T, E, H, I, k,
+                                 act, regime, workspace, workspace_bytes, topk_ids_out, topk_weights_out, stream);
+}
+
+int nf4moe_moe_forward_bias(const void* x, const void* router_logits, int logits_dtype, const int32_t* topk_ids,
+                            const float* topk_weights, const nf4moe_qweight* w13, const nf4moe_qweight* w2, const void* w13_bias,
+                            const void* w2_bias, void* out, int T, int E, int H, int I, int k, int act, int regime, void* workspace,
+                            size_t workspace_bytes, int32_t* topk_ids_out, float* topk_weights_out, void* stream) {
   g_launches = 0;
+  if ((w13_bias && !aligned16(w13_bias)) || (w2_bias && !aligned16(w2_bias)))
+    return fail(NF4MOE_EALIGN, "moe_forward: biases must be 16-byte aligned");
   if (!x || !out || !w13 || !w2 || T < 0 || E <= 0 || H <= 0 || I <= 0 || k <= 0)
     return fail(NF4MOE_EINVAL, "moe_forward: bad arguments");
   if (!router_logits && !(topk_ids && topk_weights))
@@ -481,8 +511,8 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
     ids = ids_w;
     wts = wts_w;
   }
-  if (int rc = run_experts(x, ids, w13, w2, ws.y, T, E, H, I, k, act, regime, ws, stream, &launches)) return rc;
-  if (int rc = nf4moe_combine(ws.y, wts, ids, E, T, k, H, out, stream)) return rc;
+  if (int rc = run_experts(x, ids, w13, w2, ws.y, T, E, H, I, k, act, regime, ws, stream, &launches, w13_bias)) return rc;
+  if (int rc = combine_impl(ws.y, wts, ids, E, T, k, H, out, w2_bias, stream)) return rc;
   g_launches += launches;
   return 0;
 }

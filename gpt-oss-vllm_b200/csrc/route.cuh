@@ -311,7 +311,9 @@ __global__ void __launch_bounds__(256) permute_rows_kernel(const __half* __restr
 // (P/unsloth_to_vllm_converter.py:321-323).  One thread = 8 columns.
 __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ y, const float* __restrict__ w,
                                                       const int32_t* __restrict__ ids, int E, int T, int k, int H,
-                                                      __half* __restrict__ out) {
+                                                      __half* __restrict__ out, const __half* __restrict__ bias) {
+  // bias (optional, needs ids): fp16 [E, H], the down-projection bias of the slot's expert, added to y in fp32 before weighting
+  // (gpt-oss `w2_bias`, V/model_executor/models/gpt_oss.py:199)
   grid_dep_launch();
   grid_dep_wait();
   const int vec = H / 8;
@@ -321,16 +323,21 @@ __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__
     const int t = (int)(i / vec), c = (int)(i - (long long)t * vec);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int s = 0; s < k; ++s) {
+      int e = 0;
       if (ids) {
-        const int e = ids[(long long)t * k + s];
+        e = ids[(long long)t * k + s];
         if (e < 0 || e >= E) continue;
       }
       const float ws = w[(long long)t * k + s];
       const uint4 v = __ldg(reinterpret_cast<const uint4*>(y + ((long long)t * k + s) * H) + c);
       const __half2* h = reinterpret_cast<const __half2*>(&v);
+      uint4 bv = make_uint4(0u, 0u, 0u, 0u);
+      if (bias) bv = __ldg(reinterpret_cast<const uint4*>(bias + (long long)e * H) + c);
+      const __half2* bh = reinterpret_cast<const __half2*>(&bv);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float2 f = __half22float2(h[j]);
+        float2 f = __half22float2(h[j]);
+        if (bias) { const float2 b = __half22float2(bh[j]); f.x = __fadd_rn(f.x, b.x); f.y = __fadd_rn(f.y, b.y); }
         acc[2 * j] = __fadd_rn(acc[2 * j], __fmul_rn(ws, f.x));
         acc[2 * j + 1] = __fadd_rn(acc[2 * j + 1], __fmul_rn(ws, f.y));
       }

@@ -95,6 +95,18 @@ class B200NF4MoEMethod:
             self.process_weights_after_loading(layer)
         return layer._nf4_w13, layer._nf4_w2
 
+    @staticmethod
+    def _biases(layer) -> dict:
+        """gpt-oss expert biases under vLLM's parameter names (`w13_bias [E, 2I]`, `w2_bias [E, H]`,
+        V/model_executor/models/gpt_oss.py:199), when the layer carries them."""
+        out = {}
+        for name in ("w13_bias", "w2_bias"):
+            b = getattr(layer, name, None)
+            if b is not None:
+                b = b.data if isinstance(b, torch.nn.Parameter) else b
+                out[name] = b if (b.dtype == torch.float16 and b.is_contiguous()) else b.to(torch.float16).contiguous()
+        return out
+
     def _act(self, layer) -> int:
         a = getattr(layer, "activation", None)
         if a is None:
@@ -108,7 +120,7 @@ class B200NF4MoEMethod:
         if getattr(layer, "apply_router_weight_on_input", False):
             raise NotImplementedError("apply_router_weight_on_input is not part of the gpt-oss NF4 path")
         return ops.moe_forward(x, w13, w2, topk_ids.shape[1], topk_ids=topk_ids, topk_weights=topk_weights,
-                               act=self._act(layer), regime=self.regime, nested=self.nested)
+                               act=self._act(layer), regime=self.regime, nested=self.nested, **self._biases(layer))
 
     # -- V/.../fused_moe_method_base.py:174-181 --
     def apply_monolithic(self, layer, x: torch.Tensor, router_logits: torch.Tensor, input_ids=None) -> torch.Tensor:
@@ -124,7 +136,7 @@ class B200NF4MoEMethod:
             raise NotImplementedError("gpt-oss routes with renormalize=True (V/model_executor/models/gpt_oss.py:195)")
         w13, w2 = self._weights(layer)
         return ops.moe_forward(x, w13, w2, top_k, router_logits=router_logits.contiguous(), act=self._act(layer),
-                               regime=self.regime, nested=self.nested)
+                               regime=self.regime, nested=self.nested, **self._biases(layer))
 
 
 class NF4MoELayer(torch.nn.Module):

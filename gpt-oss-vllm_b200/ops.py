@@ -135,8 +135,10 @@ def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, to
                 router_logits: torch.Tensor | None = None, topk_ids: torch.Tensor | None = None,
                 topk_weights: torch.Tensor | None = None, act: int = _lib.ACT_SWIGLU_OAI,
                 regime: int = _lib.REGIME_AUTO, nested: bool | None = None, out: torch.Tensor | None = None,
-                workspace: torch.Tensor | None = None, return_routing: bool = False):
-    """The whole layer (nf4moe_moe_forward): x fp16 [T,H] -> fp16 [T,H]."""
+                workspace: torch.Tensor | None = None, return_routing: bool = False,
+                w13_bias: torch.Tensor | None = None, w2_bias: torch.Tensor | None = None):
+    """The whole layer (nf4moe_moe_forward[_bias]): x fp16 [T,H] -> fp16 [T,H].  w13_bias fp16 [E, 2I] / w2_bias fp16 [E, H]
+    (optional) are gpt-oss's expert biases."""
     _require_cuda(x, "hidden_states")
     if x.dtype != torch.float16:
         raise TypeError("hidden_states must be fp16 (the reference serves with --dtype float16)")
@@ -165,11 +167,17 @@ def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, to
         ids_out = torch.empty(T, top_k, dtype=torch.int32, device=dev)
         w_out = torch.empty(T, top_k, dtype=torch.float32, device=dev)
     q13, q2 = w13.c_struct(nested), w2.c_struct(nested)
+    for name, b, shape in (("w13_bias", w13_bias, (E, 2 * I)), ("w2_bias", w2_bias, (E, H))):
+        if b is not None:
+            _require_cuda(b, name)
+            if b.dtype != torch.float16 or tuple(b.shape) != shape or not b.is_contiguous():
+                raise ValueError(f"{name} must be a contiguous fp16 tensor of shape {shape}")
     with torch.cuda.device(dev):
-        _lib.check(lib.nf4moe_moe_forward(
+        _lib.check(lib.nf4moe_moe_forward_bias(
             x.data_ptr(), None if router_logits is None else router_logits.data_ptr(), ldt,
             None if topk_ids is None else topk_ids.data_ptr(), None if topk_weights is None else topk_weights.data_ptr(),
-            C.byref(q13), C.byref(q2), out.data_ptr(), T, E, H, I, top_k, act, regime, workspace.data_ptr(),
+            C.byref(q13), C.byref(q2), None if w13_bias is None else w13_bias.data_ptr(),
+            None if w2_bias is None else w2_bias.data_ptr(), out.data_ptr(), T, E, H, I, top_k, act, regime, workspace.data_ptr(),
             workspace.numel(), None if ids_out is None else ids_out.data_ptr(),
             None if w_out is None else w_out.data_ptr(), _stream_ptr(dev)))
     if return_routing:

@@ -171,6 +171,14 @@ int nf4moe_moe_forward(const void* x, const void* router_logits, int logits_dtyp
                        int E, int H, int I, int k, int act, int regime, void* workspace, size_t workspace_bytes,
                        int32_t* topk_ids_out, float* topk_weights_out, void* stream);
 
+/* The same layer with the expert biases of gpt-oss (V/model_executor/models/gpt_oss.py:199; SURVEY 8(f) row 3 -- absent from the
+ * reference wrapper and from vLLM's bnb method): w13_bias fp16 [E, 2I] is added to the up-projection before the activation,
+ * w2_bias fp16 [E, H] to the down-projection before the routing weight.  Either may be NULL. */
+int nf4moe_moe_forward_bias(const void* x, const void* router_logits, int logits_dtype, const int32_t* topk_ids,
+                            const float* topk_weights, const nf4moe_qweight* w13, const nf4moe_qweight* w2, const void* w13_bias,
+                            const void* w2_bias, void* out, int T, int E, int H, int I, int k, int act, int regime, void* workspace,
+                            size_t workspace_bytes, int32_t* topk_ids_out, float* topk_weights_out, void* stream);
+
 /* ---- expert parallelism (one process per GPU; experts [r*E/world, (r+1)*E/world) live on rank r) ------------------------
  * The reference is single-GPU (P/gpt_oss_server.py:25 pins CUDA_VISIBLE_DEVICES=0); these entry points are what the
  * per-(token,k) expert loop of P/unsloth_to_vllm_converter.py:298-323 becomes when the experts of that loop are sharded.

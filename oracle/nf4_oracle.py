@@ -258,7 +258,7 @@ def _mm_f16_f32acc(a16: np.ndarray, b16_t: np.ndarray) -> np.ndarray:
 
 def moe_forward_ref(x: np.ndarray, logits: np.ndarray, w13: np.ndarray, w2: np.ndarray, k: int = 4,
                     act: str = "swiglu_oai", topk: tuple[np.ndarray, np.ndarray] | None = None,
-                    storage=np.float16) -> np.ndarray:
+                    storage=np.float16, b13: np.ndarray | None = None, b2: np.ndarray | None = None) -> np.ndarray:
     """The MoE layer of P/unsloth_to_vllm_converter.py:282-325, grouped by expert instead of by token
     (same arithmetic per (token, k) pair): ``h = x @ W13_e^T`` (fp32 acc -> storage) -> activation in fp32 ->
     storage -> ``y = h @ W2_e^T`` (fp32 acc -> storage) -> ``out[t] += w[t,k] * y`` in fp32 (k ascending)
@@ -271,9 +271,17 @@ def moe_forward_ref(x: np.ndarray, logits: np.ndarray, w13: np.ndarray, w2: np.n
     for e in np.unique(ids):
         tt, kk = np.nonzero(ids == e)
         xe = x[tt].astype(storage)
-        h = _mm_f16_f32acc(xe, w13[e]).astype(storage)
+        # expert biases (gpt-oss, V/model_executor/models/gpt_oss.py:199; not in the reference wrapper): added to the fp32
+        # accumulator of each linear layer before its one rounding to storage, as F.linear(x, W, b) does
+        h = _mm_f16_f32acc(xe, w13[e])
+        if b13 is not None:
+            h = h + b13[e].astype(np.float32)
+        h = h.astype(storage)
         a = fn(h.astype(np.float32)).astype(storage)
-        y = _mm_f16_f32acc(a, w2[e]).astype(storage)
+        y = _mm_f16_f32acc(a, w2[e])
+        if b2 is not None:
+            y = y + b2[e].astype(np.float32)
+        y = y.astype(storage)
         y_pair[tt, kk] = y.astype(np.float32)
     out = np.zeros((T, H), dtype=np.float32)
     for j in range(k):
@@ -282,8 +290,8 @@ def moe_forward_ref(x: np.ndarray, logits: np.ndarray, w13: np.ndarray, w2: np.n
 
 
 def moe_forward_from_states(x, logits, st13: list[dict], st2: list[dict], k: int = 4, nested: bool = True,
-                            act: str = "swiglu_oai", topk=None) -> np.ndarray:
+                            act: str = "swiglu_oai", topk=None, b13=None, b2=None) -> np.ndarray:
     """The reference path end to end: bnb-semantics dequant of every expert, then `moe_forward_ref`."""
     w13 = np.stack([dequant_state(s, nested) for s in st13])
     w2 = np.stack([dequant_state(s, nested) for s in st2])
-    return moe_forward_ref(x, logits, w13, w2, k, act, topk)
+    return moe_forward_ref(x, logits, w13, w2, k, act, topk, b13=b13, b2=b2)

@@ -537,3 +537,43 @@ def test_graphed_forward_matches_eager(pkg, cuda_device):
         assert torch.equal(got.to(cuda_device), ref)
     with pytest.raises(ValueError):
         graphed(x[:5], lg)
+
+
+@pytest.mark.parametrize("T,E,H,I,k,regime", [(5, 8, 128, 128, 2, "gemv"), (40, 8, 256, 192, 4, "auto"), (300, 8, 256, 192, 4, "gemm"),
+                                              (64, 32, 320, 128, 4, "auto")])
+@pytest.mark.parametrize("act", ["swiglu_oai", "chunk_silu"])
+def test_moe_forward_with_expert_biases(pkg, cuda_device, T, E, H, I, k, regime, act):
+    """gpt-oss expert biases: w13_bias before the activation, w2_bias before the routing weight, in every
+    regime and both activation layouts, against the oracle; zero biases reproduce the unbiased layer bit for bit; the
+    quant-method picks the biases up from the layer's vLLM parameter names."""
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 91, E, H, I)
+    rng = np.random.default_rng(T + E)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    b13 = (rng.standard_normal((E, 2 * I)) * 0.5).astype(np.float16)
+    b2 = (rng.standard_normal((E, H)) * 0.5).astype(np.float16)
+    reg = {"gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "auto": pkg.REGIME_AUTO}[regime]
+    a = pkg.ACT_SWIGLU_OAI if act == "swiglu_oai" else pkg.ACT_CHUNK_SILU
+    xd, lgd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(lg).to(cuda_device)
+    b13d, b2d = torch.from_numpy(b13).to(cuda_device), torch.from_numpy(b2).to(cuda_device)
+    out = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=reg, act=a, w13_bias=b13d, w2_bias=b2d)
+    ref = orc.moe_forward_from_states(x, lg, st13, st2, k=k, act=act, b13=b13, b2=b2)
+    assert_moe_close(out.cpu().numpy(), ref)
+    plain = orc.moe_forward_from_states(x, lg, st13, st2, k=k, act=act)
+    assert np.abs(ref.astype(np.float32) - plain.astype(np.float32)).max() > 0.05          # the biases matter in this case
+    # each bias alone
+    for kw, okw in (({"w13_bias": b13d}, {"b13": b13}), ({"w2_bias": b2d}, {"b2": b2})):
+        o1 = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=reg, act=a, **kw)
+        assert_moe_close(o1.cpu().numpy(), orc.moe_forward_from_states(x, lg, st13, st2, k=k, act=act, **okw))
+    # zero w2 bias == no w2 bias, bit for bit (the w13 path differs by design: fused vs raw + bias kernel)
+    o0 = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=reg, act=a, w2_bias=torch.zeros_like(b2d))
+    assert torch.equal(o0, pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=reg, act=a))
+    if act == "swiglu_oai":
+        method = pkg.B200NF4MoEMethod(top_k=k, regime=reg)
+        layer = torch.nn.Module()
+        method.bind(layer, w13, w2)
+        layer.w13_bias = torch.nn.Parameter(b13d, requires_grad=False)
+        layer.w2_bias = torch.nn.Parameter(b2d, requires_grad=False)
+        assert torch.equal(method.apply_legacy(layer, xd, lgd, k), out)
+    with pytest.raises(ValueError):
+        pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, w2_bias=b2d[:, :-8].contiguous())
