@@ -65,6 +65,7 @@ struct DecArgs {
   const int32_t* meta;
   const int32_t* tile_list;
   int act;
+  const __half* bias;   // w13 only, optional: fp16 [E, rows] up-projection bias, added (fp16) before the fused SwiGLU
   long long* dbg;
   int max_raw, max_b;   // ring caps (tuning knobs NF4MOE_DEC_RAW / NF4MOE_DEC_B)
   int b3d;              // the activation maps are the 3-D form (one TMA per stage) rather than 2-D (one per k-block)
@@ -270,6 +271,13 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
       const int n = rt * kGemmRowTile + r;
       const int db = it & 1;
+      uint32_t bg2 = 0u, bu2 = 0u;   // this lane pair's gate / up bias, broadcast to both halves (zero = none)
+      if (W13 && a.bias != nullptr && a.act == NF4MOE_ACT_SWIGLU_OAI && n < a.w.rows) {
+        const __half* be = a.bias + (long long)a.tile_list[4 * tile] * a.w.rows + (n & ~1);
+        const uint32_t g = __half_as_ushort(__ldg(be)), u = __half_as_ushort(__ldg(be + 1));
+        bg2 = g | (g << 16);
+        bu2 = u | (u << 16);
+      }
       mbar_wait(bar(kDbDFull + db), (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
       const bool row_ok = n < a.w.rows;
@@ -294,6 +302,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
           const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? p[i] : p[8 + i], 1);
           gt[i] = odd ? got : p[i];
           up[i] = odd ? p[8 + i] : got;
+        }
+        if (a.bias != nullptr) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { gt[i] = hadd2_u32(gt[i], bg2); up[i] = hadd2_u32(up[i], bu2); }
         }
         const int t0 = odd ? 16 : 0;
         __half* dst = h + (long long)(row0 + t0) * I + (n >> 1);
@@ -484,7 +496,7 @@ inline bool dec_serves(int T, int k, int E, int mode) { return mode == NF4MOE_GE
 template <bool W13>
 int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
                const int32_t* tile_list, int T, int k, int E, int act, void* out, void* stream, char* err, size_t err_len,
-               int* launches) {
+               int* launches, const void* bias = nullptr) {
   const char* name = W13 ? "gemm_w13(decode)" : "gemm_w2(decode)";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
   if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
@@ -511,6 +523,7 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   a.meta = meta;
   a.tile_list = tile_list;
   a.act = act;
+  a.bias = W13 ? (const __half*)bias : nullptr;
   a.dbg = gemm_debug_buffer();
   static const int raw_env = getenv("NF4MOE_DEC_RAW") ? atoi(getenv("NF4MOE_DEC_RAW")) : kDecMaxRaw;
   static const int b_env = getenv("NF4MOE_DEC_B") ? atoi(getenv("NF4MOE_DEC_B")) : 5;

@@ -172,6 +172,11 @@ __device__ __forceinline__ void set_max_regs_inc() { asm volatile("setmaxnreg.in
 template <int N>
 __device__ __forceinline__ void set_max_regs_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
+__device__ __forceinline__ uint32_t hadd2_u32(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("add.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
 __device__ __forceinline__ uint32_t hmul2_u32(uint32_t a, uint32_t b) {
   uint32_t r;
   asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));

@@ -436,17 +436,23 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
   if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
   *launches += g_launches; g_launches = 0;
   // with an up-projection bias the w13 kernels store their raw products and bias_act_kernel applies bias + activation
-  const int act_k = w13_bias ? NF4MOE_ACT_CHUNK_SILU : act;   // CHUNK_SILU = "store raw [rows, 2I]" for the w13 kernels
+  // (the decode tcgen05 kernel adds the bias inside its fused SwiGLU epilogue instead)
+  const bool bias_fused = w13_bias && gemm && act == NF4MOE_ACT_SWIGLU_OAI && dec_serves(T, k, E, mode);
+  const bool bias_split = w13_bias && !bias_fused;
+  const int act_k = bias_split ? NF4MOE_ACT_CHUNK_SILU : act;   // CHUNK_SILU = "store raw [rows, 2I]" for the w13 kernels
   __half* h_dst = act_k == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
   if (gemm) {
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
-    if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream)) return rc;
+    if (bias_fused) {
+      if (int rc = dec_launch<true>(ws.xs, w13, nullptr, ws.meta, ws.tiles, T, k, E, act, h_dst, stream, g_err, sizeof(g_err),
+                                    &g_launches, w13_bias)) return rc;
+    } else if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act_k, h_dst, stream)) return rc;
   }
   *launches += g_launches; g_launches = 0;
-  if (w13_bias) {
+  if (bias_split) {
     DevInfo di;
     if (int rc = device_info(&di)) return rc;
     launch_pdl(bias_act_kernel, dim3(di.sms * 4), dim3(256), 0, st, (const __half*)ws.raw, (const __half*)w13_bias, ids,
