@@ -23,7 +23,9 @@ EXPORTED = (
     "nf4moe_quantize", "nf4moe_route_topk", "nf4moe_bucket", "nf4moe_permute_rows", "nf4moe_combine",
     "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
     "nf4moe_last_launch_count", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
+    "nf4moe_workspace_status_offset", "nf4moe_expert_rows_bias", "nf4moe_combine_indexed_bias",
 )
+STATUS_EP_OVERFLOW, STATUS_DEC_NOFIT, STATUS_GEMM_NOFIT = 1, 2, 4
 
 
 class Nf4MoeError(RuntimeError):
@@ -55,6 +57,8 @@ def _declare(lib):
     lib.nf4moe_last_launch_count.restype = i32
     lib.nf4moe_workspace_bytes.restype = sz
     lib.nf4moe_workspace_bytes.argtypes = [i32] * 5
+    lib.nf4moe_workspace_status_offset.restype = sz
+    lib.nf4moe_workspace_status_offset.argtypes = [i32] * 5
     lib.nf4moe_dequant.argtypes = [qp, i32, i32, vp, vp]
     lib.nf4moe_dequant_absmax.argtypes = [qp, i32, vp, vp]
     lib.nf4moe_quantize.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
@@ -73,23 +77,30 @@ def _declare(lib):
     lib.nf4moe_ep_pack.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp]
     lib.nf4moe_expert_rows.argtypes = [vp, vp, qp, qp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
     lib.nf4moe_combine_indexed.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
+    lib.nf4moe_expert_rows_bias.argtypes = [vp, vp, qp, qp, vp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
+    lib.nf4moe_combine_indexed_bias.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
     for name in EXPORTED:
         fn = getattr(lib, name)
-        if name not in ("nf4moe_version", "nf4moe_auto_regime", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_last_launch_count"):
+        if name not in ("nf4moe_version", "nf4moe_auto_regime", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_last_launch_count",
+                        "nf4moe_workspace_status_offset"):
             fn.restype = i32
 
 
-def load_library(build_if_missing: bool = True):
-    """Load (building with nvcc first if the .so is absent or stale) and return the ctypes handle."""
+def load_library(build_if_missing: bool = True, path: str | None = None):
+    """Load (building with nvcc first if the .so is absent or stale) and return the ctypes handle.  `path` loads a differently
+    built libnf4moe instead (scripts/ A-B runs of -DNF4MOE_EXPERIMENTS builds); it must be given before the first use -- the
+    environment is never consulted."""
     global _lib
     with _lock:
         if _lib is not None:
+            if path is not None and os.path.abspath(path) != getattr(_lib, "_nf4moe_path", None):
+                raise RuntimeError("libnf4moe is already loaded from another path")
             return _lib
         from . import build as _build
-        override = os.environ.get("NF4MOE_LIB")   # developer knob: A/B a differently built libnf4moe (scripts/, never the tests)
-        if override:
-            lib = C.CDLL(override)
+        if path is not None:
+            lib = C.CDLL(path)
             _declare(lib)
+            lib._nf4moe_path = os.path.abspath(path)
             _lib = lib
             return lib
         if build_if_missing and _build.needs_build():
@@ -104,6 +115,7 @@ def load_library(build_if_missing: bool = True):
             raise RuntimeError("libnf4moe.so is missing; run `python gpt-oss-vllm_b200/build.py` (no fallback exists)")
         lib = C.CDLL(LIB_PATH)
         _declare(lib)
+        lib._nf4moe_path = os.path.abspath(LIB_PATH)
         _lib = lib
         return lib
 

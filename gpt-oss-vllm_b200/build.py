@@ -33,12 +33,15 @@ def needs_build() -> bool:
     return any(os.path.getmtime(s) > t for s in _sources())
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, defines: list[str] | None = None, out: str | None = None) -> str:
+    """`defines` / `out` build a VARIANT library next to the shipped one (scripts/: -DNF4MOE_EXPERIMENTS, other pipeline
+    shapes); the shipped libnf4moe.so is always built without any."""
+    if out is None and not force and not needs_build():
         return LIB
+    target = out or LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
-    cmd = [nvcc, *flags, "-o", LIB + ".tmp", os.path.join(CSRC, "nf4moe.cu"), "-lcudart"]
+    flags = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")] + [f"-D{d}" for d in (defines or [])]
+    cmd = [nvcc, *flags, "-o", target + ".tmp", os.path.join(CSRC, "nf4moe.cu"), "-lcudart"]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
@@ -47,9 +50,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
     if verbose:
         sys.stderr.write(r.stderr)
-    os.replace(LIB + ".tmp", LIB)
-    return LIB
+    os.replace(target + ".tmp", target)
+    return target
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    outs = [a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--out=")]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, defines=defs or None, out=outs[0] if outs else None))

@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "../../include/nf4moe.h"
 
 #ifndef __CUDA_ARCH_FEAT_SM100_ALL
@@ -242,10 +244,37 @@ __device__ __forceinline__ uint32_t swiglu_oai_h2(uint32_t g2, uint32_t u2) {
 // the reference wrapper's own variant, P/unsloth_to_vllm_converter.py:312-315
 __device__ __forceinline__ float silu_mul(float g, float u) { return g / (1.0f + __expf(-g)) * u; }
 
-// ---- host: launch with the programmatic-stream-serialization attribute (NF4MOE_PDL=0 turns it off for A/B timing) ----------
+// ---- host: launch with the programmatic-stream-serialization attribute ----------------------------------------------------
+// Tuning / A-B switches read from the environment exist only in builds made with -DNF4MOE_EXPERIMENTS (scripts/); the shipped
+// library never consults the environment on its launch path.
 inline bool pdl_enabled() {
+#ifdef NF4MOE_EXPERIMENTS
   static const bool on = !(getenv("NF4MOE_PDL") && atoi(getenv("NF4MOE_PDL")) == 0);
   return on;
+#else
+  return true;
+#endif
+}
+inline int experiment_env(const char* name, int dflt) {
+#ifdef NF4MOE_EXPERIMENTS
+  const char* s = getenv(name);
+  return s ? atoi(s) : dflt;
+#else
+  (void)name;
+  return dflt;
+#endif
+}
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: set it once per (kernel, device ordinal).
+template <auto Kern>
+inline cudaError_t ensure_dyn_smem(int bytes) {
+  static std::atomic<unsigned long long> done{0ull};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 64 && ((done.load(std::memory_order_acquire) >> dev) & 1ull)) return cudaSuccess;
+  e = cudaFuncSetAttribute(Kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess && dev < 64) done.fetch_or(1ull << dev, std::memory_order_release);
+  return e;
 }
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {

@@ -42,10 +42,13 @@ __global__ void __launch_bounds__(256) ep_pack_kernel(const __half* __restrict__
   }
 }
 
-// out[t, :] = fp16( sum_slot w[t, slot] * y[pair_slot[t*k+slot], :] ), fp32, slot ascending: the same arithmetic and
-// order as combine_kernel, reading the rows where the return all-to-all left them.  pair_slot < 0: pair dropped.
+// out[t, :] = fp16( sum_slot w[t, slot] * (y[pair_slot[t*k+slot], :] + bias[ids[t*k+slot], :]) ), fp32, slot ascending: the same
+// arithmetic and order as combine_kernel, reading the rows where the return all-to-all left them.  pair_slot < 0: pair dropped.
+// bias (optional): the FULL down-projection bias table fp16 [E, H] (replicated on every rank: 184 KB for gpt-oss-20b), indexed by
+// the home rank's GLOBAL expert ids -- added at home, in fp32, so the expert-parallel sum equals the single-GPU one bit for bit.
 __global__ void __launch_bounds__(256) combine_indexed_kernel(const __half* __restrict__ y, const float* __restrict__ w,
-                                                              const int32_t* __restrict__ pair_slot, int T, int k, int H,
+                                                              const int32_t* __restrict__ pair_slot, const int32_t* __restrict__ ids,
+                                                              const __half* __restrict__ bias, int E, int T, int k, int H,
                                                               __half* __restrict__ out) {
   const int vec = H / 8;
   const long long total = (long long)T * vec;
@@ -59,9 +62,16 @@ __global__ void __launch_bounds__(256) combine_indexed_kernel(const __half* __re
       const float ws = w[(long long)t * k + s];
       const uint4 v = __ldg(reinterpret_cast<const uint4*>(y + (long long)row * H) + c);
       const __half2* h = reinterpret_cast<const __half2*>(&v);
+      uint4 bv = make_uint4(0u, 0u, 0u, 0u);
+      if (bias) {
+        const int e = ids[(long long)t * k + s];
+        if (e >= 0 && e < E) bv = __ldg(reinterpret_cast<const uint4*>(bias + (long long)e * H) + c);
+      }
+      const __half2* bh = reinterpret_cast<const __half2*>(&bv);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float2 f = __half22float2(h[j]);
+        float2 f = __half22float2(h[j]);
+        if (bias) { const float2 b = __half22float2(bh[j]); f.x = __fadd_rn(f.x, b.x); f.y = __fadd_rn(f.y, b.y); }
         acc[2 * j] = __fadd_rn(acc[2 * j], __fmul_rn(ws, f.x));
         acc[2 * j + 1] = __fadd_rn(acc[2 * j + 1], __fmul_rn(ws, f.y));
       }

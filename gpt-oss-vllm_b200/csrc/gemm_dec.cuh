@@ -1,20 +1,26 @@
-// Decode-regime grouped GEMM on tcgen05: the HBM-bound kernel for 8 < T <= ~200 tokens.
+// Decode-regime grouped GEMM on tcgen05: the HBM-bound kernel for 8 < T <= ~300 tokens.
 //
-// Same arithmetic as the FAST mode of gemm_tc.cuh (weights = A operand in TENSOR MEMORY, one dequant thread per weight
-// row, byte -> half2 table look-up, one HMUL2 by fp16(absmax), activations = B operand in shared memory), but the
-// pipeline is built for streaming 12.4 MB of packed NF4 per expert at HBM speed rather than for tensor throughput:
+// Weights = A operand in TENSOR MEMORY (one dequant thread per weight row, so absmax is a per-thread scalar), activations =
+// B operand in shared memory, accumulators in TMEM for the whole K.  The pipeline is built for streaming 12.4 MB of packed
+// NF4 per expert at HBM speed rather than for tensor throughput:
 //   * an item = 128 weight rows of one expert x all K, for the expert's <= 32 routed tokens (MMA N = 16 or 32);
 //   * a STAGE = 4 k-blocks: one 16 KB TMA box of raw NF4 [128 rows x 128 B, 128B swizzle] + the matching activation
 //     tiles [4 x N x 64] in the canonical K-major UMMA layout, all on one mbarrier; 3-6 stages in flight per SM;
-//   * SIXTEEN dequant warps: warp = (TMEM lane quarter q, k-block pair of the stage, stage parity).  Every warp does
-//     the same thing per stage it owns: two k-blocks of its 32 rows = 4 LDS.128 + 64 x (PRMT, LDS, HMUL2) +
-//     2 x tcgen05.st.x32, one barrier wait in, two arrivals out.  No k-split partial sums, no reductions: the fp32
-//     accumulators live in TMEM for the whole K;
-//   * one MMA-issuing thread: per stage ONE wait, <= 16 tcgen05.mma (M 128, N 16/32, K 16), TWO commits (stage + A slot);
+//   * dequant warps in kDecGroups groups; stage cs of the CTA belongs to group cs % kDecGroups.  Inside a group a warp is
+//     (TMEM lane quarter q, share hh of the stage's 4 k-blocks): with kDecSplit = 1 a warp decodes all four k-blocks of
+//     its 32 rows (8 LDS.128, 4 absmax, 128 x (PRMT, LDS, HMUL2), 4 x tcgen05.st, one wait in, two arrivals out), so
+//     the per-stage bookkeeping is paid once per 128 packed bytes per thread;
+//   * operand modes (template FAST): FAST = byte -> half2 table look-up x fp16(absmax) (one HMUL2 per packed byte);
+//     EXACT = byte -> two fp32 codes, fp32 multiply, ONE rounding to fp16: bit-identical to bnb dequantize_4bit;
+//   * nested (double-quant) absmax in FAST mode: code2[u8] comes from a per-lane copy of the 256-entry table parked in the
+//     unused upper halves of the decode table's 256-byte rows (bank-conflict-free; 1.7 M of the 13.5 M shared-memory
+//     wavefronts per launch of the round-1 kernel were bank conflicts of this look-up);
+//   * one MMA-issuing thread: per stage ONE wait, <= 16 tcgen05.mma (M 128, N 16/32, K 16), one commit (+1 per item);
 //   * four epilogue warps read the finished accumulator (double-buffered) while the next item streams: gpt-oss
-//     clamped SwiGLU on adjacent lanes for w13, scatter to (token, slot) order for w2.
-// Instruction budget: ~19 weights per issued instruction (the mma.sync GEMV of gemv.cuh: 8.3, measured), shared-memory
-// wavefronts ~27 per 512 packed bytes (16 of them the table look-ups, which bound this design at ~5.5 TB/s).
+//     clamped SwiGLU on adjacent lanes for w13 (+ optional fused up-projection bias), scatter to (token, slot) order for w2.
+// The shared-memory plan (two absmax stages, the activation ring, the raw ring around the 64 KB-aligned decode table) is
+// computed by dec_plan() -- the same function on the host (dec_launch refuses a shape that does not fit) and on the device
+// (a plan that does not fit there raises bit 1 of the status word instead of silently doing nothing).
 // Replaces bnb Linear4bit on single rows, P/unsloth_to_vllm_converter.py:309-318, for all routed pairs at once.
 #pragma once
 #include "gemm_tc.cuh"
@@ -22,14 +28,19 @@
 namespace nf4moe {
 
 #ifndef NF4MOE_DEC_GROUPS
-#define NF4MOE_DEC_GROUPS 2
+#define NF4MOE_DEC_GROUPS 4
 #endif
-// Dequant groups of 8 warps; stage cs of the CTA belongs to group cs % kDecGroups.  3 groups (1024 threads, 64 registers, a few
-// spills) measured 12 % SLOWER than 2 (T=64 w13 93.0 vs 82.8 us): issue slots and the shared-memory pipe are both ~60 % busy
-// with 2 groups and more resident warps only add contention, so 2 is the shipped value.
-constexpr int kDecGroups = NF4MOE_DEC_GROUPS;
-constexpr int kDecDqWarps = 8 * kDecGroups;
-constexpr int kDecThreads = (kDecDqWarps + 4 + 4) * 32;   // 768 / 1024: dequant, epilogue warpgroup, control warpgroup
+#ifndef NF4MOE_DEC_SPLIT
+#define NF4MOE_DEC_SPLIT 1
+#endif
+constexpr int kDecGroups = NF4MOE_DEC_GROUPS;     // dequant groups; stage cs belongs to group cs % kDecGroups
+constexpr int kDecSplit = NF4MOE_DEC_SPLIT;       // warps sharing one (stage, lane quarter): 1 or 2
+constexpr int kDecKpw = 4 / kDecSplit;            // k-blocks a warp decodes per stage
+constexpr int kDecStageWarps = 4 * kDecSplit;     // warps that consume one stage
+constexpr int kDecDqWarps = kDecStageWarps * kDecGroups;
+static_assert(kDecSplit == 1 || kDecSplit == 2, "NF4MOE_DEC_SPLIT must be 1 or 2");
+static_assert(kDecDqWarps >= 8 && kDecDqWarps <= 24, "8..24 dequant warps");
+constexpr int kDecThreads = (kDecDqWarps + 4 + 4) * 32;   // dequant, epilogue warpgroup, control warpgroup
 constexpr int kDecWarpProd = kDecDqWarps + 4, kDecWarpMma = kDecDqWarps + 5, kDecWarpAct = kDecDqWarps + 6;
 constexpr int kDecMaxRaw = 8;                              // raw-NF4 stages (16 KB each) in the shared-memory ring
 constexpr int kDecMaxB = 6;                                // activation stages (their own ring: they live until the MMAs retire)
@@ -37,6 +48,9 @@ constexpr int kDecSlots = 3;                               // A-operand slots in
 constexpr int kDecAccCols = 32;                            // per accumulator (two of them)
 constexpr uint32_t kDecRawBytes = 128 * 128;               // raw NF4 of one stage: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kDecSmemBytes = 232448 - 1024;
+// registers per thread after setmaxnreg (the launch bound gives every warp 65536 / kDecThreads, rounded down to 8)
+constexpr int kDecRegsDq = kDecDqWarps <= 8 ? 160 : kDecDqWarps <= 12 ? 120 : kDecDqWarps <= 16 ? 96 : kDecDqWarps <= 20 ? 72 : 64;
+constexpr int kDecRegsCtl = 40;
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
   asm volatile(
@@ -66,55 +80,127 @@ struct DecArgs {
   const int32_t* tile_list;
   int act;
   const __half* bias;   // w13 only, optional: fp16 [E, rows] up-projection bias, added (fp16) before the fused SwiGLU
-  long long* dbg;
-  int max_raw, max_b;   // ring caps (tuning knobs NF4MOE_DEC_RAW / NF4MOE_DEC_B)
+  int32_t* status;      // optional device word: bit 1 is raised when the shared-memory plan does not fit (nothing is computed then)
+  long long* dbg;       // NF4MOE_EXPERIMENTS builds only
   int b3d;              // the activation maps are the 3-D form (one TMA per stage) rather than 2-D (one per k-block)
-  int exp;              // timing experiments (NF4MOE_DEC_EXP; results are wrong when non-zero)
+  int hole_code2;       // FAST + nested + one code2 table for all experts: the table sits, per lane, in the decode table's holes
 };
 
+// ---- shared-memory plan -------------------------------------------------------------------------------------------------
+// Two regions around the 64 KB-aligned decode table: [align1024(base), lut) and [lut + 64 KB, base + kDecSmemBytes).  Wanted:
+// two absmax stages (the item's [128 rows x nkb] absmax: fp32, or u8 (+ the expert's 1 KB code2 table unless it lives in the
+// table's holes)), ONE contiguous activation ring of n_b stages (4 x N x 128 B each) and as many 16 KB raw stages as still fit.
+struct DecPlan {
+  uint32_t m_code2, m_bytes, b_stage;
+  int n_b, n_raw;
+  uint32_t mst[2], b0, raw[kDecMaxRaw];
+};
+
+__host__ __device__ inline uint32_t dec_absmax_stage_bytes(int nkb, bool nested, bool stage_code2, uint32_t* code2_off) {
+  const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
+  const uint32_t m_code2 = (m_tile + 15u) & ~15u;
+  if (code2_off) *code2_off = m_code2;
+  return (m_code2 + (nested && stage_code2 ? 1024u : 0u) + 1023u) & ~1023u;
+}
+
+__host__ __device__ inline bool dec_plan_try(uint32_t base, uint32_t lut, uint32_t m_bytes, uint32_t b_stage, int n_b, DecPlan* p) {
+  uint32_t cur[2] = {(base + 1023u) & ~1023u, lut + kGemmLutBytes};
+  const uint32_t hi[2] = {lut, base + kDecSmemBytes};
+  auto place = [&](uint32_t bytes) -> uint32_t {
+    int best = -1;
+    uint32_t best_room = 0;
+    for (int r = 0; r < 2; ++r) {   // best fit: the region with the least room that still takes the block
+      const uint32_t room = hi[r] > cur[r] ? hi[r] - cur[r] : 0u;
+      if (room >= bytes && (best < 0 || room < best_room)) { best = r; best_room = room; }
+    }
+    if (best < 0) return 0u;
+    const uint32_t at = cur[best];
+    cur[best] += bytes;
+    return at;
+  };
+  for (int i = 0; i < 2; ++i) { p->mst[i] = place(m_bytes); if (!p->mst[i]) return false; }
+  p->b0 = place((uint32_t)n_b * b_stage);
+  if (!p->b0) return false;
+  p->n_b = n_b;
+  p->n_raw = 0;
+  for (int i = 0; i < kDecMaxRaw; ++i) { const uint32_t at = place(kDecRawBytes); if (!at) break; p->raw[p->n_raw++] = at; }
+  return p->n_raw >= 2;
+}
+
+// bmax = largest MMA N of the launch (16 or 32).  Takes the deepest activation ring that still leaves >= 4 raw stages; failing
+// that, the plan with the most raw stages (>= 2).  Returns false when nothing fits (K too large for this pipeline).
+__host__ __device__ inline bool dec_plan(uint32_t base, uint32_t lut, int nkb, bool nested, bool stage_code2, int bmax, DecPlan* p) {
+  p->m_bytes = dec_absmax_stage_bytes(nkb, nested, stage_code2, &p->m_code2);
+  p->b_stage = 4u * (uint32_t)bmax * 128u;
+  const int want_b = bmax == 16 ? kDecMaxB : 5;
+  DecPlan best = *p;
+  best.n_raw = 0;
+  for (int n_b = want_b; n_b >= 3; --n_b) {
+    DecPlan t = *p;
+    if (!dec_plan_try(base, lut, p->m_bytes, p->b_stage, n_b, &t)) continue;
+    if (t.n_raw >= 4) { *p = t; return true; }
+    if (t.n_raw > best.n_raw) best = t;
+  }
+  if (best.n_raw >= 2) { *p = best; return true; }
+  p->n_raw = 0;
+  return false;
+}
+
 // barrier slots
-//   RFull[i]  <- TMA bytes of raw stage i AND of the matching activation stage (one expect_tx): waited on by the 8 dequant warps
-//                that own the stage; the MMA thread never waits on it (its wait on AFull is causally after all 8 of theirs)
-//   REmpty[i] <- the 8 dequant warps, as soon as their 4 LDS.128 are done (the stage refills while they decode)
-//   AFull[s]  <- the 8 dequant warps, A operand of the stage written to TMEM slot s
-//   Done[c]   <- ONE tcgen05.commit per stage (ring of n_b = 3 or 6): frees A slot c % 3 for the dequant warps of stage + 3
+//   RFull[i]  <- TMA bytes of raw stage i AND of the matching activation stage (one expect_tx): waited on by the dequant warps
+//                that own the stage; the MMA thread never waits on it (its wait on AFull is causally after all of theirs)
+//   REmpty[i] <- the stage's dequant warps, as soon as their LDS.128 are done (the stage refills while they decode)
+//   AFull[s]  <- the stage's dequant warps, A operand of the stage written to TMEM slot s
+//   Done[c]   <- ONE tcgen05.commit per stage (ring of n_b): frees A slot c % 3 for the dequant warps of stage + 3
 //                and activation stage c for the producer of stage + n_b
 constexpr int kDbRFull = 0, kDbREmpty = kDbRFull + kDecMaxRaw, kDbDone = kDbREmpty + kDecMaxRaw,
               kDbAFull = kDbDone + kDecMaxB, kDbDFull = kDbAFull + kDecSlots, kDbDEmpty = kDbDFull + 2,
               kDbMFull = kDbDEmpty + 2, kDbMEmpty = kDbMFull + 2, kNumDecBars = kDbMEmpty + 2;
 
-// Warp roles (768 threads, one persistent CTA per SM).  cs = the CTA's running stage counter (12 per item for K = 2880); the
-// rings follow it: raw stage cs % n_raw, activation stage cs % n_b, A slot cs % 3.
-//   warps 0-15   dequant: q = warp & 3 (TMEM lane quarter = weight rows 32q..32q+31), hh = (warp >> 2) & 1 (k-blocks 2hh, 2hh+1
-//                of a stage), pp = warp >> 3 (stages cs = pp mod 2).  Per owned stage: wait RFull, 4 x LDS.128, arrive REmpty at
-//                once, decode, wait Done of stage cs - 3, 2 x tcgen05.st, arrive AFull
-//   warps 16-19  epilogue
-//   warp 20      TMA producer: absmax per item; raw NF4 + activations per stage
-//   warp 21      TMEM allocator and the MMA-issuing thread: per stage ONE wait, <= 16 tcgen05.mma, ONE commit
-template <bool W13, bool DBG>
+__device__ __forceinline__ void ring_advance(int& idx, uint32_t& phase, int step, int n) {
+  idx += step;
+  while (idx >= n) { idx -= n; phase ^= 1u; }
+}
+
+// Warp roles (one persistent CTA per SM).  cs = the CTA's running stage counter (12 per item for K = 2880); the rings follow
+// it: raw stage cs % n_raw, activation stage cs % n_b, A slot cs % 3.
+//   warps 0..kDecDqWarps-1   dequant: q = warp & 3 (TMEM lane quarter = weight rows 32q..32q+31), hh = share of the stage's
+//                            k-blocks, pp = group (stages cs = pp mod kDecGroups)
+//   next 4 warps             epilogue
+//   then                     TMA producer (absmax per item; raw NF4 per stage), MMA issuer (+ TMEM allocator), TMA producer
+//                            of the activation stages, one idle warp
+template <bool W13, bool FAST, bool DBG>
 __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, const __grid_constant__ CUtensorMap map_w,
                                                             const __grid_constant__ CUtensorMap map_x16,
                                                             const __grid_constant__ CUtensorMap map_x32) {
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumDecBars];
   __shared__ uint32_t s_tmem;
-  __shared__ uint32_t s_raw[kDecMaxRaw], s_b0, s_mst[2];
-  __shared__ int s_nraw;
+  __shared__ DecPlan s_plan;
   grid_dep_launch();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nkb = a.w.nkb;
   const int nst = (nkb + 3) >> 2;                       // stages per item (the last one may be partly padding)
   const bool nested = a.w.absmax_f32 == nullptr;
+  const bool hole = FAST && a.hole_code2 != 0;
   const uint32_t base = smem_u32(dyn_smem);
   const uint32_t lut = pin((base + kGemmLutBytes - 1u) & ~(kGemmLutBytes - 1u));
   const uint32_t bar0 = pin(smem_u32(s_bar));
   auto bar = [&](int i) -> uint32_t { return bar0 + 8u * (uint32_t)i; };
 
-  // ---- prologue that depends on nothing the previous kernel wrote: decode table, TMEM allocation.  Under programmatic
-  // dependent launch it overlaps the previous kernel's tail; everything below the wait may read bucket / GEMM outputs ----
+  // ---- prologue that depends on nothing the previous kernel wrote: decode table (weights are constants), TMEM allocation.
+  // Under programmatic dependent launch it overlaps the previous kernel's tail; everything below the wait may read bucket /
+  // GEMM outputs ----
   for (int i = tid; i < 256 * 32; i += kDecThreads) {
     const int b = i >> 5, l = i & 31;
-    sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
+    if (FAST) {
+      sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
+      if (hole) sts32(lut + (uint32_t)b * 256u + 128u + (uint32_t)l * 4u, __float_as_uint(__ldg(a.w.code2 + b)));
+    } else {
+      const uint32_t p = lut + (uint32_t)b * 256u + (uint32_t)l * 8u;
+      sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
+      sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
+    }
   }
   if (warp == kDecWarpMma) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
@@ -122,39 +208,12 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   }
   grid_dep_wait();
   const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
-  const uint32_t b_stage = 4u * (uint32_t)bmax * 128u;  // activations of one stage: 4 k-blocks x N x 128 B
-  // activation stages in ONE contiguous block: 6 x 8 KB at N = 16; at N = 32 (16 KB each) a.max_b of them (default 5): with
-  // 3, stage cs's activations could only be requested once the MMAs of stage cs - 3 had retired, and that round trip
-  // (TMA latency + dequant + MMA per 3 stages) set the pace (measured ~10 % slower than the N = 16 launches)
-  const int n_b = bmax == 16 ? 6 : min(kDecMaxB, max(3, a.max_b));
-  const uint32_t m_tile = (uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u);
-  const uint32_t m_code2 = (m_tile + 15u) & ~15u;
-  const uint32_t m_bytes = (m_code2 + (nested ? 1024u : 0u) + 1023u) & ~1023u;
   // ---- one-time setup ----
   if (tid == 0) {
-    uint32_t cur[2] = {(base + 1023u) & ~1023u, lut + kGemmLutBytes};
-    const uint32_t hi[2] = {lut, base + kDecSmemBytes};
-    auto place = [&](uint32_t bytes) -> uint32_t {
-      int best = -1;
-      uint32_t best_room = 0;
-      for (int r = 0; r < 2; ++r) {
-        const uint32_t room = hi[r] > cur[r] ? hi[r] - cur[r] : 0u;
-        if (room >= bytes && (best < 0 || room < best_room)) { best = r; best_room = room; }
-      }
-      if (best < 0) return 0u;
-      const uint32_t at = cur[best];
-      cur[best] += bytes;
-      return at;
-    };
-    int im = 0, ir = 0;
-    for (int i = 0; i < 2; ++i) { const uint32_t at = place(m_bytes); if (at) s_mst[im++] = at; }
-    const uint32_t b_at = place((uint32_t)n_b * b_stage);
-    s_b0 = b_at;
-    for (int i = 0; i < min(kDecMaxRaw, a.max_raw); ++i) { const uint32_t at = place(kDecRawBytes); if (at) s_raw[ir++] = at; else break; }
-    s_nraw = (im == 2 && b_at != 0u && ir >= 3) ? ir : 0;
-    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), 8); }
+    if (!dec_plan(base, lut, nkb, nested, !hole, bmax, &s_plan) && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
+    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
     for (int i = 0; i < kDecMaxB; ++i) mbar_init(bar(kDbDone + i), 1);
-    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), 8);
+    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecStageWarps);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kDbDFull + i), 1); mbar_init(bar(kDbDEmpty + i), 4);
       mbar_init(bar(kDbMFull + i), 1); mbar_init(bar(kDbMEmpty + i), kDecDqWarps);
@@ -165,8 +224,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const int n_raw = s_nraw;
-  const uint32_t b_ring = s_b0;
+  const int n_raw = s_plan.n_raw, n_b = s_plan.n_b;
+  const uint32_t b_ring = s_plan.b0, b_stage = s_plan.b_stage, m_code2 = s_plan.m_code2;
   const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
   const int n_items = n_raw > 0 ? a.meta[2] * n_row_tiles : 0;
   const uint32_t acol0 = 2u * kDecAccCols;   // TMEM: accumulators at columns 0 and 32, A slots after them
@@ -175,20 +234,25 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 
   if (warp < kDecDqWarps) {
     // =============================== dequant: NF4 -> fp16 A operand in TMEM ===============================
-    const int q = warp & 3, hh = (warp >> 2) & 1, pp = warp >> 3;   // pp = dequant group
+    set_max_regs_inc<kDecRegsDq>();
+    const int q = warp & 3, hh = (warp >> 2) % kDecSplit, pp = (warp >> 2) / kDecSplit;   // pp = dequant group
     const int r = q * 32 + lane;
-    const uint32_t lut_lane = pin(lut | ((uint32_t)lane << 2));
+    const uint32_t lut_lane = pin(lut | ((uint32_t)lane << (FAST ? 2 : 3)));
+    const uint32_t hole_lane = pin(lut | 128u | ((uint32_t)lane << 2));
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0;
     const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), afull0 = bar(kDbAFull), done0 = bar(kDbDone);
-    // this lane's four 16-byte chunks of a raw stage row (128B swizzle: chunk c of row r sits at chunk c ^ (r & 7))
+    // this lane's 16-byte chunks of a raw stage row (128B swizzle: chunk c of row r sits at chunk c ^ (r & 7))
     const uint32_t row_off = (uint32_t)r * 128u, swz = (uint32_t)(r & 7);
-    const uint32_t ch0 = row_off + (((uint32_t)(hh * 4) ^ swz) << 4), ch1 = row_off + (((uint32_t)(hh * 4 + 1) ^ swz) << 4);
-    const uint32_t ch2 = row_off + (((uint32_t)(hh * 4 + 2) ^ swz) << 4), ch3 = row_off + (((uint32_t)(hh * 4 + 3) ^ swz) << 4);
-    // this warp owns stages cs = pp (mod 2).  Running ring positions of its NEXT stage: raw stage sw, A slot `slot`, and the Done
-    // barrier of stage cs - 3 (index dn, parity pdn; "stage -3 .. -1" = the phase before the first one, which a fresh barrier
-    // reports complete)
-    int sw = pp, slot = pp, dn = pp + n_b - 3, st = pp, it = 0;
+    uint32_t ch[2 * kDecKpw];
+#pragma unroll
+    for (int j = 0; j < 2 * kDecKpw; ++j) ch[j] = row_off + (((uint32_t)(hh * 2 * kDecKpw + j) ^ swz) << 4);
+    // this warp owns stages cs = pp (mod kDecGroups).  Running ring positions of its NEXT stage: raw stage sw, A slot `slot`,
+    // and the Done barrier of stage cs - 3 (index dn, parity pdn; "stage -3 .. -1" = the phase before the first one, which a
+    // fresh barrier reports complete)
+    int sw = 0, slot = pp % kDecSlots, dn = 0, st = pp, it = 0;
     uint32_t phw = 0, pdn = 1;
+    ring_advance(sw, phw, pp, max(n_raw, 1));
+    ring_advance(dn, pdn, pp + n_b - 3, max(n_b, 1));
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
       const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
       const int e = a.tile_list[4 * tile];
@@ -208,39 +272,45 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       GEMM_DBG_T0();
       mbar_wait(bar(kDbMFull + mb), (uint32_t)(it >> 1) & 1u);
       GEMM_DBG_ADD(0);
-      const uint32_t m_st = pin(s_mst[mb]);
+      const uint32_t m_st = pin(s_plan.mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       for (; st < nst; st += kDecGroups) {
         mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
         GEMM_DBG_ADD(1);
-        const uint32_t wst = pin(s_raw[sw]);
-        const int kb0 = st * 4 + hh * 2;
-        const bool real0 = kb0 < nkb && !(a.exp & 16), real1 = kb0 + 1 < nkb && !(a.exp & 24);
-        uint4 v0 = lds128(wst + ch0), v1 = lds128(wst + ch1), v2 = lds128(wst + ch2), v3 = lds128(wst + ch3);
-        float am0 = 0.f, am1 = 0.f;
-        if (nested) {
-          const uint32_t c0 = lds_u8(m_row + (uint32_t)min(kb0, nkb - 1)), c1 = lds_u8(m_row + (uint32_t)min(kb0 + 1, nkb - 1));
-          am0 = __fadd_rn(__fmul_rn(lds_f32(m_st + m_code2 + 4u * c0), kb0 < blk_hi ? a2_lo : a2_hi), off_e);
-          am1 = __fadd_rn(__fmul_rn(lds_f32(m_st + m_code2 + 4u * c1), kb0 + 1 < blk_hi ? a2_lo : a2_hi), off_e);
-        } else {
-          am0 = lds_f32(m_row + 4u * (uint32_t)min(kb0, nkb - 1));
-          am1 = lds_f32(m_row + 4u * (uint32_t)min(kb0 + 1, nkb - 1));
+        const uint32_t wst = pin(s_plan.raw[sw]);
+        const int kb0 = st * 4 + hh * kDecKpw;
+        uint4 v[2 * kDecKpw];
+#pragma unroll
+        for (int j = 0; j < 2 * kDecKpw; ++j) v[j] = lds128(wst + ch[j]);
+        float am[kDecKpw];
+#pragma unroll
+        for (int u = 0; u < kDecKpw; ++u) {
+          const int kb = min(kb0 + u, nkb - 1);
+          if (nested) {
+            const uint32_t c = lds_u8(m_row + (uint32_t)kb);
+            const float cv = hole ? lds_f32(hole_lane + (c << 8)) : lds_f32(m_st + m_code2 + 4u * c);
+            am[u] = __fadd_rn(__fmul_rn(cv, kb < blk_hi ? a2_lo : a2_hi), off_e);
+          } else {
+            am[u] = lds_f32(m_row + 4u * (uint32_t)kb);
+          }
         }
         // the raw bytes are in registers: hand the stage back now (mbarrier.arrive has release semantics: the loads above
         // are performed before the arrival is visible), so its refill overlaps the decode
         __syncwarp();
         if (lane == 0) mbar_arrive(rempty0 + 8u * (uint32_t)sw);
-        const uint32_t t_half = t_lane + (uint32_t)slot * 128u + (uint32_t)hh * 64u;
+        const uint32_t t_st = t_lane + (uint32_t)slot * 128u + (uint32_t)(hh * kDecKpw) * 32u;
         uint32_t regs[32];
-        if (real0) decode_block<true>(v0, v1, lut_lane, am0, regs, (a.exp & 2) != 0);
-        GEMM_DBG_ADD(2);
-        mbar_wait(done0 + 8u * (uint32_t)dn, pdn);          // the MMAs of stage cs - 3, which read this A slot, are done
-        tc_fence_after();
-        GEMM_DBG_ADD(3);
-        if (real0) tmem_st32(t_half, regs);
-        if (real1) {
-          decode_block<true>(v2, v3, lut_lane, am1, regs, (a.exp & 2) != 0);
-          tmem_st32(t_half + 32u, regs);
+#pragma unroll
+        for (int u = 0; u < kDecKpw; ++u) {
+          const bool real = kb0 + u < nkb;
+          if (real) decode_block<FAST>(v[2 * u], v[2 * u + 1], lut_lane, am[u], regs);
+          if (u == 0) {
+            GEMM_DBG_ADD(2);
+            mbar_wait(done0 + 8u * (uint32_t)dn, pdn);      // the MMAs of stage cs - 3, which read this A slot, are done
+            tc_fence_after();
+            GEMM_DBG_ADD(3);
+          }
+          if (real) tmem_st32(t_st + (uint32_t)u * 32u, regs);
         }
         GEMM_DBG_ADD(4);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -248,18 +318,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         __syncwarp();
         if (lane == 0) mbar_arrive(afull0 + 8u * (uint32_t)slot);
         GEMM_DBG_ADD(5);
-        sw += kDecGroups;
-        if (sw >= n_raw) { sw -= n_raw; phw ^= 1u; }
-        slot += kDecGroups;
-        if (slot >= kDecSlots) slot -= kDecSlots;
-        dn += kDecGroups;
-        if (dn >= n_b) { dn -= n_b; pdn ^= 1u; }
+        ring_advance(sw, phw, kDecGroups, n_raw);
+        slot = (slot + kDecGroups) % kDecSlots;
+        ring_advance(dn, pdn, kDecGroups, n_b);
       }
       st -= nst;
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kDbMEmpty + mb));
     }
-    if (dbg_on && (warp == 0 || warp == 13)) for (int i = 0; i < 6; ++i) a.dbg[(warp ? 8 : 0) + i] = dbg_acc[i];
+    if (dbg_on && (warp == 0 || warp == kDecDqWarps - 3)) for (int i = 0; i < 6; ++i) a.dbg[(warp ? 8 : 0) + i] = dbg_acc[i];
   } else if (warp < kDecDqWarps + 4) {
     // =============================== epilogue: TMEM -> registers -> global, overlapped with the next item ===============
     const int q = warp & 3;
@@ -330,154 +397,139 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
             y[(long long)__ldg(a.sorted_pairs + row0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
       }
     }
-  } else if (warp == kDecWarpProd) {
-    // =============================== TMA producer: absmax per item, raw NF4 per stage ===============================
-    const uint64_t pol = l2_policy_evict_first();   // weights are read exactly once per step
-    const uint32_t am_elt = nested ? 1u : 4u;
-    const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
-    const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty);
-    int sw = 0, it = 0;
-    uint32_t phw = 0;
-    // Experiment (NF4MOE_DEC_EXP & 4; measured SLOWER, 92 -> 98 us, so off): pull each item's packed bytes (one contiguous
-    // 184 KB span) into L2 front to back one item ahead, so the strided stage boxes hit L2.
-    auto prefetch_item = [&](int item) {
-      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-      const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
-      const uint8_t* src = a.w.packed + (long long)a.tile_list[4 * tile] * a.w.packed_stride + (long long)rt * kGemmRowTile * (nkb * 32);
-      const uint32_t bytes = (uint32_t)(rows_here * nkb * 32);
-      if (elect_one())
-        for (uint32_t off = 0; off < bytes; off += 16384u)
-          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src + off), "r"(min(16384u, bytes - off)) : "memory");
-      __syncwarp();
-    };
-    if ((a.exp & 4) && (int)blockIdx.x < n_items) prefetch_item(blockIdx.x);
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      GEMM_DBG_T0();
-      if ((a.exp & 4) && item + (int)gridDim.x < n_items) prefetch_item(item + gridDim.x);
-      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
-      const int e = a.tile_list[4 * tile];
-      const int c1 = e * a.w.rows + rt * kGemmRowTile;
-      {
-        const int mb = it & 1;
-        const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
-        const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
-        mbar_wait(bar(kDbMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u);
-        if (elect_one()) {
-          mbar_expect_tx(bar(kDbMFull + mb), bytes + (nested ? 1024u : 0u));
-          bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
-                   bar(kDbMFull + mb), pol);
-          if (nested) bulk_g2s(s_mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kDbMFull + mb), pol);
+  } else {
+    set_max_regs_dec<kDecRegsCtl>();
+    if (warp == kDecWarpProd) {
+      // =============================== TMA producer: absmax per item, raw NF4 per stage ===============================
+      const uint64_t pol = l2_policy_evict_first();   // weights are read exactly once per step
+      const uint32_t am_elt = nested ? 1u : 4u;
+      const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
+      const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty);
+      const bool stage_code2 = nested && !hole;
+      int sw = 0, it = 0;
+      uint32_t phw = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        GEMM_DBG_T0();
+        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+        const int e = a.tile_list[4 * tile];
+        const int c1 = e * a.w.rows + rt * kGemmRowTile;
+        {
+          const int mb = it & 1;
+          const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
+          const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
+          mbar_wait(bar(kDbMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(bar(kDbMFull + mb), bytes + (stage_code2 ? 1024u : 0u));
+            bulk_g2s(s_plan.mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
+                     bar(kDbMFull + mb), pol);
+            if (stage_code2) bulk_g2s(s_plan.mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kDbMFull + mb), pol);
+          }
+          __syncwarp();
         }
-        __syncwarp();
+        GEMM_DBG_ADD(0);
+        const int n_tok = a.tile_list[4 * tile + 2];
+        const uint32_t b_tile = n_tok <= 16 ? 2048u : 4096u;
+        for (int st = 0; st < nst; ++st) {
+          mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);          // the dequant warps of the stage n_raw back have read it
+          GEMM_DBG_ADD(1);
+          const int nreal = min(4, nkb - st * 4);
+          if (elect_one()) {
+            const uint32_t full = rfull0 + 8u * (uint32_t)sw;
+            // the activation producer adds its bytes to the same barrier; a 3-D box always delivers 4 tiles (zero-filled)
+            mbar_expect_tx(full, kDecRawBytes + (uint32_t)(a.b3d ? 4 : nreal) * b_tile);
+            tma_load_2d(s_plan.raw[sw], &map_w, st * 128, c1, full);
+          }
+          __syncwarp();
+          GEMM_DBG_ADD(2);
+          if (++sw == n_raw) { sw = 0; phw ^= 1u; }
+        }
       }
-      GEMM_DBG_ADD(0);
-      const int n_tok = a.tile_list[4 * tile + 2];
-      const uint32_t b_tile = n_tok <= 16 ? 2048u : 4096u;
-      for (int st = 0; st < nst; ++st) {
-        mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);          // the 8 dequant warps of the stage n_raw back have read it
-        GEMM_DBG_ADD(1);
-        const int nreal = min(4, nkb - st * 4);
-        if (elect_one()) {
-          const uint32_t full = rfull0 + 8u * (uint32_t)sw;
-          // the activation producer (warp 22) adds its bytes to the same barrier; a 3-D box always delivers 4 tiles (zero-filled)
-          mbar_expect_tx(full, kDecRawBytes + (uint32_t)(a.b3d ? 4 : nreal) * b_tile);
-          if (a.exp & 32) {   // experiment: the same byte count as ONE contiguous 16 KB bulk copy (wrong data layout)
-            const long long span = (long long)kGemmRowTile * nkb * 32;
-            bulk_g2s(s_raw[sw], a.w.packed + (long long)c1 * (nkb * 32) + min((long long)st * 16384, span - 16384), kDecRawBytes, full, pol);
-          } else {
-            tma_load_2d(s_raw[sw], &map_w, st * 128, c1, full);
+      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[24 + i] = dbg_acc[i];
+    } else if (warp == kDecWarpAct) {
+      // =============================== TMA producer: activations per stage ===============================
+      // Its bytes complete on the SAME barrier as the stage's raw NF4 (the raw producer's expect_tx covers both), so the dequant
+      // warps' one wait covers both and the MMA thread waits on nothing but AFull.  It waits for REmpty too: the barrier's
+      // previous phase (stage cs - n_raw) must be over before bytes of stage cs may be counted on it.
+      const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), done0 = bar(kDbDone);
+      int sw = 0, sb = 0;
+      uint32_t phw = 0, phb = 0;
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int tile = item / n_row_tiles;
+        const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
+        const int nb = n_tok <= 16 ? 16 : 32;
+        const uint32_t b_tile = (uint32_t)nb * 128u;
+        const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
+        for (int st = 0; st < nst; ++st) {
+          mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);
+          mbar_wait(done0 + 8u * (uint32_t)sb, phb ^ 1u);            // the MMAs of the stage n_b back have read its activations
+          const int nreal = min(4, nkb - st * 4);
+          if (elect_one()) {
+            const uint32_t full = rfull0 + 8u * (uint32_t)sw, dst = b_ring + (uint32_t)sb * b_stage;
+            if (a.b3d) {
+              tma_load_3d(dst, map_x, 0, row0, st * 4, full);
+            } else {
+              for (int u = 0; u < nreal; ++u) tma_load_2d(dst + (uint32_t)u * b_tile, map_x, (st * 4 + u) * kBlock, row0, full);
+            }
+          }
+          __syncwarp();
+          if (++sw == n_raw) { sw = 0; phw ^= 1u; }
+          if (++sb == n_b) { sb = 0; phb ^= 1u; }
+        }
+      }
+    } else if (warp == kDecWarpMma) {
+      // =============================== MMA issuer (one thread) ===============================
+      // A lone warp runs at one dependent instruction per ~6 cycles and every mbarrier / tcgen05 instruction costs it 60-100, so
+      // this loop is kept to one wait, the MMAs (running addresses, constant accumulate flag except in an item's first stage)
+      // and one commit per stage.
+      const uint32_t afull0 = bar(kDbAFull), done0 = bar(kDbDone);
+      const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version 1, SWIZZLE_128B
+      const uint32_t blo0 = (b_ring & 0x3FFFFu) >> 4, bstep = b_stage >> 4;
+      const uint32_t a_t0 = tmem + acol0;
+      int sb = 0, slot = 0, it = 0;
+      uint32_t pha = 0;
+      auto issue = [&](const uint32_t d_t, const uint32_t a_t, const uint32_t b_lo, const uint32_t blo_step, const uint32_t idesc,
+                       const int nreal, const bool first) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (u < nreal) {
+            const uint64_t desc = ((uint64_t)desc_hi << 32) | (uint64_t)(b_lo + (uint32_t)u * blo_step);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              tc_mma_ts(d_t, a_t + (uint32_t)(u * 32 + 8 * kk), desc + (uint64_t)(2 * kk), idesc, first ? (uint32_t)(u | kk) : 1u);
           }
         }
-        __syncwarp();
-        GEMM_DBG_ADD(2);
-        if (++sw == n_raw) { sw = 0; phw ^= 1u; }
-      }
-    }
-    if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[24 + i] = dbg_acc[i];
-  } else if (warp == kDecWarpAct) {
-    // =============================== TMA producer: activations per stage ===============================
-    // Its bytes complete on the SAME barrier as the stage's raw NF4 (the raw producer's expect_tx covers both), so the dequant
-    // warps' one wait covers both and the MMA thread waits on nothing but AFull.  It waits for REmpty too: the barrier's
-    // previous phase (stage cs - n_raw) must be over before bytes of stage cs may be counted on it.
-    const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), done0 = bar(kDbDone);
-    int sw = 0, sb = 0;
-    uint32_t phw = 0, phb = 0;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-      const int tile = item / n_row_tiles;
-      const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
-      const int nb = n_tok <= 16 ? 16 : 32;
-      const uint32_t b_tile = (uint32_t)nb * 128u;
-      const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
-      for (int st = 0; st < nst; ++st) {
-        mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);
-        mbar_wait(done0 + 8u * (uint32_t)sb, phb ^ 1u);            // the MMAs of the stage n_b back have read its activations
-        const int nreal = min(4, nkb - st * 4);
-        if (elect_one()) {
-          const uint32_t full = rfull0 + 8u * (uint32_t)sw, dst = b_ring + (uint32_t)sb * b_stage;
-          if (a.b3d) {
-            tma_load_3d(dst, map_x, 0, row0, st * 4, full);
-          } else {
-            for (int u = 0; u < nreal; ++u) tma_load_2d(dst + (uint32_t)u * b_tile, map_x, (st * 4 + u) * kBlock, row0, full);
+      };
+      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
+        const int tile = item / n_row_tiles;
+        const int n_tok = a.tile_list[4 * tile + 2];
+        const int nb = n_tok <= 16 ? 16 : 32;
+        const uint32_t idesc = make_idesc(nb);
+        const uint32_t blo_step = ((uint32_t)nb * 128u) >> 4;
+        const int db = it & 1;
+        const uint32_t d_t = tmem + (uint32_t)(db * kDecAccCols);
+        GEMM_DBG_T0();
+        mbar_wait(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
+        GEMM_DBG_ADD(0);
+        for (int st = 0; st < nst; ++st) {
+          mbar_wait(afull0 + 8u * (uint32_t)slot, pha);     // A operand written by the stage's dequant warps (who saw its TMA land)
+          tc_fence_after();
+          GEMM_DBG_ADD(2);
+          const int nreal = min(4, nkb - st * 4);
+          if (elect_one()) {
+            const uint32_t a_t = a_t0 + (uint32_t)slot * 128u, b_lo = blo0 + (uint32_t)sb * bstep;
+            if (st == 0) issue(d_t, a_t, b_lo, blo_step, idesc, nreal, true);
+            else issue(d_t, a_t, b_lo, blo_step, idesc, nreal, false);
+            tc_commit(done0 + 8u * (uint32_t)sb);            // frees the A slot and the activation stage
+            if (st == nst - 1) tc_commit(bar(kDbDFull + db));
           }
+          __syncwarp();
+          GEMM_DBG_ADD(3);
+          if (++slot == kDecSlots) { slot = 0; pha ^= 1u; }
+          if (++sb == n_b) sb = 0;
         }
-        __syncwarp();
-        if (++sw == n_raw) { sw = 0; phw ^= 1u; }
-        if (++sb == n_b) { sb = 0; phb ^= 1u; }
       }
+      if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[16 + i] = dbg_acc[i];
     }
-  } else if (warp == kDecWarpMma) {
-    // =============================== MMA issuer (one thread) ===============================
-    // A lone warp runs at one dependent instruction per ~6 cycles and every mbarrier / tcgen05 instruction costs it 60-100, so
-    // this loop is kept to one wait, the MMAs (running addresses, constant accumulate flag except in an item's first stage)
-    // and one commit per stage.
-    const uint32_t afull0 = bar(kDbAFull), done0 = bar(kDbDone);
-    const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version 1, SWIZZLE_128B
-    const uint32_t blo0 = (b_ring & 0x3FFFFu) >> 4, bstep = b_stage >> 4;
-    const uint32_t a_t0 = tmem + acol0;
-    int sb = 0, slot = 0, it = 0;
-    uint32_t pha = 0;
-    auto issue = [&](const uint32_t d_t, const uint32_t a_t, const uint32_t b_lo, const uint32_t blo_step, const uint32_t idesc,
-                     const int nreal, const bool first) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (u < nreal) {
-          const uint64_t desc = ((uint64_t)desc_hi << 32) | (uint64_t)(b_lo + (uint32_t)u * blo_step);
-#pragma unroll
-          for (int kk = 0; kk < ((a.exp & 1) ? 1 : 4); ++kk)
-            tc_mma_ts(d_t, a_t + (uint32_t)(u * 32 + 8 * kk), desc + (uint64_t)(2 * kk), idesc, first ? (uint32_t)(u | kk) : 1u);
-        }
-      }
-    };
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const int tile = item / n_row_tiles;
-      const int n_tok = a.tile_list[4 * tile + 2];
-      const int nb = n_tok <= 16 ? 16 : 32;
-      const uint32_t idesc = make_idesc(nb);
-      const uint32_t blo_step = ((uint32_t)nb * 128u) >> 4;
-      const int db = it & 1;
-      const uint32_t d_t = tmem + (uint32_t)(db * kDecAccCols);
-      GEMM_DBG_T0();
-      mbar_wait(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
-      GEMM_DBG_ADD(0);
-      for (int st = 0; st < nst; ++st) {
-        mbar_wait(afull0 + 8u * (uint32_t)slot, pha);     // A operand written by the stage's 8 dequant warps (who saw its TMA land)
-        tc_fence_after();
-        GEMM_DBG_ADD(2);
-        const int nreal = min(4, nkb - st * 4);
-        if (elect_one()) {
-          const uint32_t a_t = a_t0 + (uint32_t)slot * 128u, b_lo = blo0 + (uint32_t)sb * bstep;
-          if (st == 0) issue(d_t, a_t, b_lo, blo_step, idesc, nreal, true);
-          else issue(d_t, a_t, b_lo, blo_step, idesc, nreal, false);
-          tc_commit(done0 + 8u * (uint32_t)sb);            // frees the A slot and the activation stage
-          if (st == nst - 1) tc_commit(bar(kDbDFull + db));
-        }
-        __syncwarp();
-        GEMM_DBG_ADD(3);
-        if (++slot == kDecSlots) { slot = 0; pha ^= 1u; }
-        if (++sb == n_b) sb = 0;
-      }
-    }
-    if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[16 + i] = dbg_acc[i];
   }
 
   // ---- teardown ----
@@ -490,17 +542,30 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 }
 
 // ---- host side ------------------------------------------------------------------------------------------------------
-// True when the decode-regime tcgen05 kernel serves this call: FAST operand mode and token tiles of at most 32 rows.
-inline bool dec_serves(int T, int k, int E, int mode) { return mode == NF4MOE_GEMM_FAST && gemm_tile_tokens(T, k, E) <= 32; }
+// True when the decode-regime tcgen05 kernel serves this call: token tiles of at most 32 rows (either operand mode).
+inline bool dec_serves(int T, int k, int E, int mode) {
+  return (mode == NF4MOE_GEMM_FAST || mode == NF4MOE_GEMM_EXACT) && gemm_tile_tokens(T, k, E) <= 32;
+}
+
+// Does the pipeline fit in shared memory for this K / absmax form, whatever the largest token tile turns out to be?  The
+// dynamic shared memory starts 1 KB (static control block) or 2 KB (+ the 1 KB the driver reserves) into the CTA's window.
+inline bool dec_shape_fits(int nkb, bool nested, bool stage_code2) {
+  DecPlan p;
+  for (uint32_t base : {1024u, 2048u})
+    for (int bmax : {16, 32})
+      if (!dec_plan(base, kGemmLutBytes, nkb, nested, stage_code2, bmax, &p)) return false;
+  return true;
+}
 
 template <bool W13>
 int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
-               const int32_t* tile_list, int T, int k, int E, int act, void* out, void* stream, char* err, size_t err_len,
-               int* launches, const void* bias = nullptr) {
+               const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err, size_t err_len,
+               int* launches, const void* bias = nullptr, int32_t* status = nullptr) {
   const char* name = W13 ? "gemm_w13(decode)" : "gemm_w2(decode)";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
   if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
   if (!W13 && !sorted_pairs) return fail(NF4MOE_EINVAL, "sorted_pairs required");
+  if (mode != NF4MOE_GEMM_EXACT && mode != NF4MOE_GEMM_FAST) return fail(NF4MOE_EINVAL, "mode must be NF4MOE_GEMM_EXACT or NF4MOE_GEMM_FAST");
   if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "cols must be a multiple of 64");
   if (W13 && (w->rows & 1)) return fail(NF4MOE_EINVAL, "w13 rows must be even");
   if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "absmax missing");
@@ -516,6 +581,8 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaDeviceGetAttribute(&cc, cudaDevAttrComputeCapabilityMajor, dev);
   if (cc != 10) return fail(NF4MOE_EARCH, "needs an sm_100 device");
+  const bool fast = mode == NF4MOE_GEMM_FAST;
+  const bool nested = w->absmax_f32 == nullptr;
   DecArgs a;
   a.w = make_qw(*w);
   a.out = out;
@@ -524,33 +591,35 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   a.tile_list = tile_list;
   a.act = act;
   a.bias = W13 ? (const __half*)bias : nullptr;
+  a.status = status ? status : const_cast<int32_t*>(meta) + 4;
   a.dbg = gemm_debug_buffer();
-  static const int raw_env = getenv("NF4MOE_DEC_RAW") ? atoi(getenv("NF4MOE_DEC_RAW")) : kDecMaxRaw;
-  static const int b_env = getenv("NF4MOE_DEC_B") ? atoi(getenv("NF4MOE_DEC_B")) : 5;
-  static const int exp_env = getenv("NF4MOE_DEC_EXP") ? atoi(getenv("NF4MOE_DEC_EXP")) : 0;
-  a.exp = exp_env;
-  a.max_raw = std::max(2, raw_env);
-  a.max_b = std::max(2, b_env);
+  a.hole_code2 = fast && nested && w->code2_stride == 0;
+  if (!dec_shape_fits(a.w.nkb, nested, nested && !a.hole_code2))
+    return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form");
   CUtensorMap map_w, map_x16, map_x32;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
-  static const bool no3d = getenv("NF4MOE_DEC_NO3D") != nullptr;
-  a.b3d = !no3d && make_map_x3d(&map_x16, act_in, (uint64_t)w->cols, (uint64_t)T * k, 16) &&
+  a.b3d = make_map_x3d(&map_x16, act_in, (uint64_t)w->cols, (uint64_t)T * k, 16) &&
           make_map_x3d(&map_x32, act_in, (uint64_t)w->cols, (uint64_t)T * k, 32);
   if (!a.b3d && (!make_map_2d(&map_x16, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 16) ||
                  !make_map_2d(&map_x32, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32)))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
-  const bool dbg = W13 && a.dbg != nullptr;   // the cycle-counter build exists for w13 only (scripts/dec_roles.py)
-  auto kern = dbg ? dec_kernel<W13, W13> : dec_kernel<W13, false>;
-  static thread_local bool attr_set[2] = {false, false};
-  if (!attr_set[dbg]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDecSmemBytes);
-    if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
-    attr_set[dbg] = true;
+  cudaError_t e;
+#ifdef NF4MOE_EXPERIMENTS
+  if (W13 && fast && a.dbg != nullptr) {   // the cycle-counter build exists for FAST w13 only (scripts/dec_roles.py)
+    e = ensure_dyn_smem<dec_kernel<W13, true, W13>>((int)kDecSmemBytes);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<W13, true, W13>, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
+  } else
+#endif
+  if (fast) {
+    e = ensure_dyn_smem<dec_kernel<W13, true, false>>((int)kDecSmemBytes);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<W13, true, false>, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
+  } else {
+    e = ensure_dyn_smem<dec_kernel<W13, false, false>>((int)kDecSmemBytes);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<W13, false, false>, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
   }
-  launch_pdl(kern, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
   ++*launches;
-  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }
   return 0;
 }

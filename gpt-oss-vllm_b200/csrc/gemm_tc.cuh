@@ -12,15 +12,17 @@
 // weight therefore feeds up to 192 tokens, 1.5x fewer dequants than the usual "tokens = M = 128" arrangement, and no
 // dequantised weight ever touches shared or global memory.
 //
-// Roles (512 threads, one persistent CTA per SM, registers re-balanced per warpgroup with setmaxnreg):
-//   warp 0       TMA producer: activation tiles [<=192 tokens x 64] per k-block, as 32-row boxes matching the ragged tile
-//   warp 1       TMEM allocator and the single MMA-issuing thread (tcgen05.mma kind::f16, A in TMEM, B in smem)
-//   warp 2       TMA producer: the tile's absmax (one bulk copy per tile, double-buffered) and raw NF4 tiles [128 rows x 128 B]
-//                per 4 k-blocks, on their own rings so they run ahead of the MMA
-//   warps 4-11   dequant: two groups of four warps (one lane quarter each) on alternate k-blocks
-//   warps 12-15  epilogue: tcgen05.ld of one of the TWO accumulators while the next tile's main loop fills the other;
-//                gpt-oss clamped SwiGLU on adjacent lanes (rows 2j / 2j+1 = gate / up) for w13, scatter to (token, slot)
-//                order for w2
+// Roles (640 threads, one persistent CTA per SM, registers re-balanced per warpgroup with setmaxnreg; the role index is the
+// hardware warp id rotated by 4 so that the single-thread roles get the HIGHEST warp ids, which the sub-partition arbiter
+// serves first):
+//   role 0        TMA producer: activation tiles [<= tile_tokens x 64] per k-block, as whole-tile or 32-row boxes, own ring
+//   role 1        TMEM allocator and the single MMA-issuing thread (tcgen05.mma kind::f16, A in TMEM, B in smem)
+//   role 2        TMA producer: the item's absmax (one bulk copy per item, double-buffered) and raw NF4 stages [128 rows x 128 B]
+//                 per 4 k-blocks, L2-prefetched kGemmWPrefetch stages ahead
+//   roles 4-15    dequant: THREE warpgroups; k-block c of the CTA's run belongs to group c % 3
+//   roles 16-19   epilogue: tcgen05.ld of one of the TWO accumulators while the next item's main loop fills the other;
+//                 gpt-oss clamped SwiGLU on adjacent lanes (rows 2j / 2j+1 = gate / up) for w13, scatter to (token, slot)
+//                 order for w2
 // Replaces vLLM's dequantise-everything + Triton fused_experts (V/.../quantization/bitsandbytes.py:478-506, 588-603).
 #pragma once
 #include <cuda.h>
@@ -133,7 +135,7 @@ struct GemmArgs {
   int kps;                        // k-blocks per pipeline slot (2 or 4): one barrier wait and one commit serve kps k-blocks
   int n_a;                        // slots in TMEM: (512 - 2 * tile_tokens) / (32 * kps), each kps x 32 columns of A operand
   int want_b;                     // activation stages wanted (the kernel takes fewer if shared memory runs out, never below 2)
-  int exp;                        // timing experiments (NF4MOE_GEMM_EXP; results are wrong when non-zero)
+  int32_t* status;                // optional device word: bit 2 is raised when the shared-memory plan does not fit
 };
 
 // instruction descriptor: D f32, A/B f16, both K-major, M = 128, N = n
@@ -191,7 +193,7 @@ __device__ __forceinline__ uint32_t hmul2_u32(uint32_t a, uint32_t b) {
 //          3 instead of 5 instructions per byte; differs from EXACT by fp16 roundings of code and absmax (~2^-11 relative).
 template <bool FAST>
 __device__ __forceinline__ void decode_block(const uint4 v0, const uint4 v1, const uint32_t lut_lane, const float am,
-                                             uint32_t (&regs)[32], const bool skip_lut = false) {
+                                             uint32_t (&regs)[32]) {
   const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
   const uint32_t am2 = FAST ? pack_half2(am, am) : 0u;
 #pragma unroll
@@ -200,12 +202,54 @@ __device__ __forceinline__ void decode_block(const uint4 v0, const uint4 v1, con
     for (int i = 0; i < 4; ++i) {
       const uint32_t addr = prmt(wd[wi], lut_lane, 0x7604u | ((uint32_t)i << 4));
       if (FAST) {
-        regs[wi * 4 + i] = hmul2_u32(skip_lut ? addr : lds32(addr), am2);
+        regs[wi * 4 + i] = hmul2_u32(lds32(addr), am2);
       } else {
         const float2 f = lds_f32x2(addr);
         regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am), __fmul_rn(f.y, am));
       }
     }
+}
+
+// Shared-memory plan around the 64 KB-aligned decode table -- the same function on the host (gemm_launch refuses a shape that
+// does not fit) and on the device (a plan that does not fit there raises NF4MOE_STATUS_GEMM_NOFIT instead of doing nothing).
+// The activation ring is ONE contiguous block right above the table (stage addresses are then base + i * b_bytes: no table
+// look-up on the single-thread roles); raw-weight stages fill the rest above; the two absmax stages and more raw-weight stages
+// go below.
+struct GemmPlan {
+  int n_b, n_w;
+  uint32_t wst[6], mst[2];
+};
+__host__ __device__ inline bool gemm_plan(uint32_t base, uint32_t lut, uint32_t smem_bytes, int nkb, bool nested, int tile_tokens,
+                                          int kps, int n_a, int want_b, GemmPlan* p) {
+  const uint32_t b_bytes = (uint32_t)tile_tokens * 128u;
+  const uint32_t m_tile = (uint32_t)(128 * nkb) * (nested ? 1u : 4u);
+  const uint32_t m_bytes = (((m_tile + 15u) & ~15u) + (nested ? 1024u : 0u) + 1023u) & ~1023u;
+  const uint32_t above0 = lut + 65536u, above1 = base + smem_bytes;
+  int nb = want_b < 12 ? want_b : 12;
+  if (nb > n_a * kps) nb = n_a * kps;                        // n_b / kps <= n_a keeps the shared slots in phase
+  if (above1 <= above0) return false;
+  if (nb > (int)((above1 - above0) / b_bytes)) nb = (int)((above1 - above0) / b_bytes);
+  nb -= nb % kps;                                            // whole slots only
+  uint32_t cur[2] = {(base + 1023u) & ~1023u, above0 + (uint32_t)nb * b_bytes};
+  const uint32_t hi[2] = {lut, above1};
+  auto place = [&](uint32_t bytes) -> uint32_t {
+    int best = -1;
+    uint32_t best_room = 0;
+    for (int r = 0; r < 2; ++r) {   // best fit: the region with the least room that still takes the block
+      const uint32_t room = hi[r] > cur[r] ? hi[r] - cur[r] : 0u;
+      if (room >= bytes && (best < 0 || room < best_room)) { best = r; best_room = room; }
+    }
+    if (best < 0) return 0u;
+    const uint32_t at = cur[best];
+    cur[best] += bytes;
+    return at;
+  };
+  int iw = 0, im = 0;
+  for (int i = 0; i < 2; ++i) { const uint32_t at = place(m_bytes); if (at) p->mst[im++] = at; }
+  for (int i = 0; i < 6; ++i) { const uint32_t at = place(128u * 128u); if (at) p->wst[iw++] = at; else break; }
+  p->n_w = iw;
+  p->n_b = (im == 2 && iw >= 2 && nb >= kps) ? nb : 0;
+  return p->n_b > 0;
 }
 
 // Warp roles (640 threads, one persistent CTA per SM, registers re-balanced per warpgroup with setmaxnreg):
@@ -223,15 +267,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumGemmBars];
   __shared__ uint32_t s_tmem;
-  __shared__ uint32_t s_wst[kMaxWStages], s_mst[2];
-  __shared__ int s_nw, s_nb;
+  __shared__ GemmPlan s_plan;
   // Role index: the control warps take the HIGHEST hardware warp ids (16-19).  The sub-partition arbiter serves the highest
   // warp id first, so as warps 0-3 the single-thread roles were starved of issue slots by the twelve dequant warps (every
   // mbarrier / tcgen05 / TMA instruction of theirs took 100-300 cycles); `warp` below is the ROLE index (0-3 control, 4-15
-  // dequant, 16-19 epilogue), `warp & 3` is still the hardware TMEM lane quarter.  (a.exp & 16: old placement, for A/B timing.)
+  // dequant, 16-19 epilogue), `warp & 3` is still the hardware TMEM lane quarter.
+  grid_dep_launch();
   const int tid = threadIdx.x, lane = tid & 31;
   const int hw_warp = tid >> 5;
-  const int warp = (a.exp & 16) ? hw_warp : (hw_warp + 4) % (kGemmThreads / 32);
+  const int warp = (hw_warp + 4) % (kGemmThreads / 32);
   const int nkb = a.w.nkb;
   const int n_a = a.n_a, kps = a.kps;
   const int nslot = (nkb + kps - 1) / kps;                  // slots per item (the last one may be partly padding)
@@ -252,32 +296,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
 
   // ---- one-time setup ----
   if (tid == 0) {
-    // Shared memory around the 64 KB-aligned table: the activation ring is ONE contiguous block right above it (stage
-    // addresses are then base + i * b_bytes: no table look-up on the single-thread roles); raw-weight stages fill the rest
-    // above; the two absmax stages and more raw-weight stages go below.
-    const uint32_t above0 = lut + kGemmLutBytes, above1 = base + kGemmSmemBytes;
-    int nb = min(min(a.want_b, kMaxBStages), n_a * a.kps);     // n_b / kps <= n_a keeps the shared slots in phase
-    nb = min(nb, (int)((above1 - above0) / b_bytes));
-    nb -= nb % a.kps;                                          // whole slots only
-    uint32_t cur[2] = {(base + 1023u) & ~1023u, above0 + (uint32_t)nb * b_bytes};
-    const uint32_t hi[2] = {lut, above1};
-    int iw = 0, im = 0;
-    auto place = [&](uint32_t bytes) -> uint32_t {
-      int best = -1;
-      uint32_t best_room = 0;
-      for (int r = 0; r < 2; ++r) {   // best fit: the region with the least room that still takes the block
-        const uint32_t room = hi[r] > cur[r] ? hi[r] - cur[r] : 0u;
-        if (room >= bytes && (best < 0 || room < best_room)) { best = r; best_room = room; }
-      }
-      if (best < 0) return 0u;
-      const uint32_t at = cur[best];
-      cur[best] += bytes;
-      return at;
-    };
-    for (int i = 0; i < 2; ++i) { const uint32_t at = place(m_bytes); if (at) s_mst[im++] = at; }
-    for (int i = 0; i < kMaxWStages; ++i) { const uint32_t at = place(kWStageBytes); if (at) s_wst[iw++] = at; else break; }
-    s_nb = (im == 2 && iw >= 2 && nb >= a.kps) ? nb : 0;
-    s_nw = iw;
+    gemm_plan(base, lut, kGemmSmemBytes, nkb, nested, a.tile_tokens, a.kps, n_a, a.want_b, &s_plan);
     for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 4 * kDqGroups); }
     for (int i = 0; i < kMaxAStages; ++i) { mbar_init(bar(kBarFull + i), 4 * a.kps + 1); mbar_init(bar(kBarEmpty + i), 1); }
     for (int i = 0; i < 2; ++i) {
@@ -300,16 +319,20 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  // launched with launch_pdl(): everything above (decode table, barriers, TMEM allocation) overlaps the previous kernel's tail;
+  // everything below reads what the bucket / permute (and, for w2, the w13) kernel wrote
+  grid_dep_wait();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s_tmem;
-  const int n_bst = s_nb, n_wst = s_nw;
+  const int n_bst = s_plan.n_b, n_wst = s_plan.n_w;
+  if (tid == 0 && n_bst == 0 && a.status != nullptr && a.meta[2] > 0) atomicOr(a.status, 4);
 
   const bool dbg_on = a.dbg != nullptr && blockIdx.x == 0 && lane == 0;
   long long dbg_acc[6] = {0, 0, 0, 0, 0, 0};
   const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
-  const int n_items = n_bst > 0 ? a.meta[2] * n_row_tiles : 0;   // (n_bst == 0: K too large for the stage budget; host rejects it)
+  const int n_items = n_bst > 0 ? a.meta[2] * n_row_tiles : 0;   // (n_bst == 0: K too large for the stage budget: status bit 2)
 
   if (warp < 4) {
     set_max_regs_dec<48>();
@@ -384,9 +407,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           mbar_wait(bar(kBarMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(bar(kBarMFull + mb), bytes + (nested ? 1024u : 0u));
-            bulk_g2s(s_mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
+            bulk_g2s(s_plan.mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
                      bar(kBarMFull + mb), pol);
-            if (nested) bulk_g2s(s_mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kBarMFull + mb), pol);
+            if (nested) bulk_g2s(s_plan.mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kBarMFull + mb), pol);
           }
           __syncwarp();
         }
@@ -405,7 +428,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           mbar_wait(wempty0 + 8u * (uint32_t)sw, phw ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(wfull0 + 8u * (uint32_t)sw, kWStageBytes);
-            tma_load_2d(s_wst[sw], &map_w, st * 128, c1, wfull0 + 8u * (uint32_t)sw);
+            tma_load_2d(s_plan.wst[sw], &map_w, st * 128, c1, wfull0 + 8u * (uint32_t)sw);
           }
           __syncwarp();
           if (++sw == n_wst) { sw = 0; phw ^= 1u; }
@@ -493,11 +516,11 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       GEMM_DBG_T0();
       mbar_wait(bar(kBarMFull + mb), (uint32_t)(it >> 1) & 1u);
       GEMM_DBG_ADD(0);
-      const uint32_t m_st = pin(s_mst[mb]);
+      const uint32_t m_st = pin(s_plan.mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       int ws = 0;                                // raw-weight stage of the item this warp has reached (not yet released)
       mbar_wait(bar(kBarWFull + sw), phw);
-      uint32_t wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
+      uint32_t wrow = pin(s_plan.wst[sw]) + (uint32_t)r * 128u;
       for (; v < vkb; v += kDqGroups) {
         const bool real = v < nkb;
         const int ws_need = real ? (v >> 2) : spi - 1;
@@ -506,8 +529,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           if (lane == 0) mbar_arrive(bar(kBarWEmpty + sw));
           if (++sw == n_wst) { sw = 0; phw ^= 1u; }
           ++ws;
-          if (!(a.exp & 8)) mbar_wait(bar(kBarWFull + sw), phw);
-          wrow = pin(s_wst[sw]) + (uint32_t)r * 128u;
+          mbar_wait(bar(kBarWFull + sw), phw);
+          wrow = pin(s_plan.wst[sw]) + (uint32_t)r * 128u;
         }
         GEMM_DBG_ADD(1);
         uint32_t regs[32];
@@ -522,7 +545,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           const uint32_t j2 = (uint32_t)(v & 3) * 2u;
           const uint4 v0 = lds128(wrow + ((j2 ^ swz) << 4));
           const uint4 v1 = lds128(wrow + (((j2 + 1u) ^ swz) << 4));
-          decode_block<FAST>(v0, v1, lut_lane, am, regs, (a.exp & 1) != 0);
+          decode_block<FAST>(v0, v1, lut_lane, am, regs);
         }
         GEMM_DBG_ADD(2);
         mbar_wait(empty0 + 8u * (uint32_t)sl, pha ^ 1u);   // the MMAs that read this slot last time are done
@@ -673,7 +696,7 @@ inline long long*& gemm_debug_buffer() {
 // stages fit beside the 64 KB decode table and two 23 KB flat-absmax stages.
 inline int gemm_tile_tokens(int T, int k, int E, bool nested = false) {
   (void)nested;
-  static const int tile_env = getenv("NF4MOE_TILE") ? atoi(getenv("NF4MOE_TILE")) : 0;   // crossover measurements only
+  const int tile_env = experiment_env("NF4MOE_TILE", 0);   // crossover measurements (NF4MOE_EXPERIMENTS builds only)
   if (tile_env == 32 || tile_env == 160) return tile_env;
   // 32-row tiles (decode tcgen05 kernel; an expert with more rows gets several tiles and its weights are decoded once per tile)
   // while the mean routed rows per expert stay <= 40 (measured crossover with the 160-row prefill pipeline: 48 rows per expert at
@@ -687,7 +710,7 @@ inline int gemm_tile_tokens(int T, int k, int E, bool nested = false) {
 template <bool W13>
 int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
                 const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err,
-                size_t err_len, int* launches) {
+                size_t err_len, int* launches, int32_t* status = nullptr) {
   const char* name = W13 ? "gemm_w13" : "gemm_w2";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
   if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
@@ -720,8 +743,13 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.n_a = std::min(kMaxAStages, (512 - 2 * a.tile_tokens) / (32 * a.kps));
   a.want_b = a.tile_tokens <= 32 ? 12 : 4;
   a.dbg = gemm_debug_buffer();
-  static const int exp_env = getenv("NF4MOE_GEMM_EXP") ? atoi(getenv("NF4MOE_GEMM_EXP")) : 0;
-  a.exp = exp_env;
+  a.status = status ? status : const_cast<int32_t*>(meta) + 4;
+  {   // the dynamic shared memory starts 1 KB (static control block) or 2 KB (+ the driver's reserved 1 KB) into the window
+    GemmPlan plan;
+    for (uint32_t base : {1024u, 2048u})
+      if (!gemm_plan(base, kGemmLutBytes, kGemmSmemBytes, a.w.nkb, w->absmax_f32 == nullptr, a.tile_tokens, a.kps, a.n_a, a.want_b, &plan))
+        return fail(NF4MOE_EINVAL, "K is too large for the grouped GEMM's shared-memory plan with this absmax form");
+  }
   CUtensorMap map_w, map_x;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
@@ -731,29 +759,14 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   if (!make_map_2d(&map_xw, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, (uint32_t)a.tile_tokens))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activation tiles");
   const bool fast = mode == NF4MOE_GEMM_FAST;
-  auto kern = fast ? gemm_kernel<W13, true> : gemm_kernel<W13, false>;
-  static thread_local bool attr_set[2] = {false, false};
-  if (!attr_set[fast]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmemBytes);
-    if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
-    attr_set[fast] = true;
-  }
-  kern<<<sms, kGemmThreads, kGemmSmemBytes, (cudaStream_t)stream>>>(a, map_w, map_x, map_xw);
+  cudaError_t e = fast ? ensure_dyn_smem<gemm_kernel<W13, true>>((int)kGemmSmemBytes) : ensure_dyn_smem<gemm_kernel<W13, false>>((int)kGemmSmemBytes);
+  if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
+  if (fast) e = launch_pdl(gemm_kernel<W13, true>, dim3(sms), dim3(kGemmThreads), kGemmSmemBytes, (cudaStream_t)stream, a, map_w, map_x, map_xw);
+  else e = launch_pdl(gemm_kernel<W13, false>, dim3(sms), dim3(kGemmThreads), kGemmSmemBytes, (cudaStream_t)stream, a, map_w, map_x, map_xw);
   ++*launches;
-  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }
   return 0;
-}
-
-inline int gemm_w13_entry(const void* x_sorted, const nf4moe_qweight* w13, const int32_t*, const int32_t* meta,
-                          const int32_t* tile_list, int T, int k, int E, int act, int mode, void* h_sorted, void* stream,
-                          char* err, size_t err_len, int* launches) {
-  return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, err, err_len, launches);
-}
-inline int gemm_w2_entry(const void* h_sorted, const nf4moe_qweight* w2, const int32_t*, const int32_t* sorted_pairs,
-                         const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int mode, void* y, void* stream,
-                         char* err, size_t err_len, int* launches) {
-  return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, err, err_len, launches);
 }
 
 }  // namespace nf4moe

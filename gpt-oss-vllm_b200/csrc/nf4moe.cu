@@ -77,7 +77,7 @@ int check_qw(const nf4moe_qweight* w, const char* name) {
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct Workspace {
-  int32_t *ids, *offsets, *sorted, *active, *meta, *tiles;
+  int32_t *status, *ids, *offsets, *sorted, *active, *meta, *tiles;
   float* weights;
   __half *h, *raw, *xs, *y;
   size_t total;
@@ -94,6 +94,7 @@ Workspace carve(void* base, int T, int E, int H, int I, int k) {
     off += align_up(bytes, 256);
     return r;
   };
+  w.status = (int32_t*)take(256);   // first word: NF4MOE_STATUS_* bits (nf4moe_workspace_status_offset() == 0)
   w.ids = (int32_t*)take(n * 4);
   w.weights = (float*)take(n * 4);
   w.offsets = (int32_t*)take((size_t)(E + 1) * 4);
@@ -111,14 +112,10 @@ Workspace carve(void* base, int T, int E, int H, int I, int k) {
 
 template <int NT, int KBW, bool W13, bool NESTED, int NKB_T>
 int launch_gemv_inst(const GemvArgs& args, int sms, cudaStream_t stream) {
-  static thread_local bool attr_set = false;
-  auto kern = gemv_kernel<NT, KBW, W13, NESTED, NKB_T>;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemvSmemBytes);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemv)");
-    attr_set = true;
-  }
-  launch_pdl(kern, dim3(sms), dim3(kGemvThreads), kGemvSmemBytes, stream, args);
+  cudaError_t e = ensure_dyn_smem<gemv_kernel<NT, KBW, W13, NESTED, NKB_T>>((int)kGemvSmemBytes);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemv)");
+  e = launch_pdl(gemv_kernel<NT, KBW, W13, NESTED, NKB_T>, dim3(sms), dim3(kGemvThreads), kGemvSmemBytes, stream, args);
+  if (e != cudaSuccess) return cuda_fail(e, "gemv_kernel");
   CHECK_LAUNCH("gemv_kernel");
   return 0;
 }
@@ -131,14 +128,8 @@ int launch_gemv_k(const GemvArgs& args, int sms, cudaStream_t stream) {
 }
 
 // 0 = automatic; 19 = one token tile, 9 k-blocks/warp (three 5-warp teams); 13 / 23 = one / two tiles, 3 k-blocks/warp
-int gemv_config_override() {
-  static int v = -1;
-  if (v < 0) {
-    const char* s = getenv("NF4MOE_GEMV_CFG");
-    v = s ? atoi(s) : 0;
-  }
-  return v;
-}
+// (the override exists in NF4MOE_EXPERIMENTS builds only)
+int gemv_config_override() { return experiment_env("NF4MOE_GEMV_CFG", 0); }
 
 template <bool W13>
 int launch_gemv(const GemvArgs& args, int T, bool nested, int sms, cudaStream_t stream) {
@@ -192,6 +183,11 @@ int nf4moe_last_launch_count(void) { return g_launches; }
 size_t nf4moe_workspace_bytes(int T, int E, int H, int I, int k) {
   if (T < 0 || E <= 0 || H <= 0 || I <= 0 || k <= 0) return 0;
   return carve(nullptr, T, E, H, I, k).total;
+}
+
+size_t nf4moe_workspace_status_offset(int T, int E, int H, int I, int k) {
+  if (T < 0 || E <= 0 || H <= 0 || I <= 0 || k <= 0) return 0;
+  return 0;   // the status word is the first word of the workspace for every geometry
 }
 
 int nf4moe_dequant(const nf4moe_qweight* w, int e0, int ne, void* out_f16, void* stream) {
@@ -275,7 +271,7 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
   const long long n = (long long)T * k;
   const size_t smem = (size_t)((n + 127) & ~127ll);
   if (smem > 200 * 1024) return fail(NF4MOE_EINVAL, "bucket: T*k = %lld exceeds the limit of 204800 pairs", n);
-  static const bool cluster_on = !(getenv("NF4MOE_BUCKET_CLUSTER") && atoi(getenv("NF4MOE_BUCKET_CLUSTER")) == 0);
+  const bool cluster_on = experiment_env("NF4MOE_BUCKET_CLUSTER", 1) != 0;
   if (cluster_on && n >= kBucketClusterMinPairs) {   // prefill-sized: one cluster of 8 CTAs, a chunk of the pair list each
     const size_t chunk = (size_t)((((n + kBucketCluster - 1) / kBucketCluster) + 127) & ~127ll);
     cudaLaunchConfig_t cfg = {};
@@ -296,12 +292,8 @@ int nf4moe_bucket(const int32_t* ids, int T, int k, int E, int32_t* expert_offse
     CHECK_LAUNCH("bucket_cluster_kernel");
     return 0;
   }
-  static thread_local bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(bucket)");
-    attr_set = true;
-  }
+  cudaError_t e = ensure_dyn_smem<bucket_kernel>(200 * 1024);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(bucket)");
   launch_pdl(bucket_kernel, dim3(1), dim3(kBucketThreads), smem, (cudaStream_t)stream, ids, (int)n, E, expert_offsets, sorted_pairs,
              active_experts, meta, tile_list, tile_rows);
   CHECK_LAUNCH("bucket_kernel");
@@ -397,24 +389,37 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
   return launch_gemv<false>(a, T, w2->absmax_f32 == nullptr, di.sms, (cudaStream_t)stream);
 }
 
+static int gemm_w13_any(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* meta, const int32_t* tile_list, int T,
+                        int k, int E, int act, int mode, void* h_sorted, void* stream, const void* bias, int32_t* status) {
+  if (dec_serves(T, k, E, mode))
+    return dec_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err, sizeof(g_err),
+                            &g_launches, bias, status);
+  if (bias) return fail(NF4MOE_EINVAL, "gemm_w13: the fused bias exists in the decode-regime kernel only");
+  return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err, sizeof(g_err),
+                           &g_launches, status);
+}
+
+static int gemm_w2_any(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* sorted_pairs, const int32_t* meta,
+                       const int32_t* tile_list, int T, int k, int E, int mode, void* y, void* stream, int32_t* status) {
+  if (dec_serves(T, k, E, mode))
+    return dec_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, g_err, sizeof(g_err),
+                             &g_launches, nullptr, status);
+  return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, g_err, sizeof(g_err),
+                            &g_launches, status);
+}
+
 int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
                            const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act, int mode,
                            void* h_sorted, void* stream) {
-  if (dec_serves(T, k, E, mode))
-    return dec_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, h_sorted, stream, g_err, sizeof(g_err),
-                            &g_launches);
-  return gemm_w13_entry(x_sorted, w13, expert_offsets, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err,
-                        sizeof(g_err), &g_launches);
+  (void)expert_offsets;
+  return gemm_w13_any(x_sorted, w13, meta, tile_list, T, k, E, act, mode, h_sorted, stream, nullptr, nullptr);
 }
 
 int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* expert_offsets,
                    const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
                    int mode, void* y, void* stream) {
-  if (dec_serves(T, k, E, mode))
-    return dec_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, y, stream, g_err, sizeof(g_err),
-                             &g_launches);
-  return gemm_w2_entry(h_sorted, w2, expert_offsets, sorted_pairs, meta, tile_list, T, k, E, mode, y, stream, g_err,
-                       sizeof(g_err), &g_launches);
+  (void)expert_offsets;
+  return gemm_w2_any(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, mode, y, stream, nullptr);
 }
 
 // bucket -> (permute) -> w13 (+activation) -> w2 for the (row, slot) pairs of `ids` [T, k]; y fp16 [T*k, H] in pair order.
@@ -444,10 +449,8 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
   if (gemm) {
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
-    if (bias_fused) {
-      if (int rc = dec_launch<true>(ws.xs, w13, nullptr, ws.meta, ws.tiles, T, k, E, act, h_dst, stream, g_err, sizeof(g_err),
-                                    &g_launches, w13_bias)) return rc;
-    } else if (int rc = nf4moe_gemm_w13_swiglu(ws.xs, w13, ws.offsets, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream)) return rc;
+    if (int rc = gemm_w13_any(ws.xs, w13, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream, bias_fused ? w13_bias : nullptr,
+                              ws.status)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act_k, h_dst, stream)) return rc;
   }
@@ -467,7 +470,7 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     *launches += g_launches; g_launches = 0;
   }
   if (gemm) {
-    if (int rc = nf4moe_gemm_w2(ws.h, w2, ws.offsets, ws.sorted, ws.meta, ws.tiles, T, k, E, mode, y, stream)) return rc;
+    if (int rc = gemm_w2_any(ws.h, w2, ws.sorted, ws.meta, ws.tiles, T, k, E, mode, y, stream, ws.status)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w2(ws.h, w2, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, y, stream)) return rc;
   }
@@ -526,7 +529,15 @@ int nf4moe_moe_forward_bias(const void* x, const void* router_logits, int logits
 int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
                        void* y_rows, int n_rows, int E, int H, int I, int act, int regime, void* workspace,
                        size_t workspace_bytes, void* stream) {
+  return nf4moe_expert_rows_bias(rows, row_expert, w13, w2, nullptr, y_rows, n_rows, E, H, I, act, regime, workspace, workspace_bytes,
+                                 stream);
+}
+
+int nf4moe_expert_rows_bias(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
+                            const void* w13_bias, void* y_rows, int n_rows, int E, int H, int I, int act, int regime,
+                            void* workspace, size_t workspace_bytes, void* stream) {
   g_launches = 0;
+  if (w13_bias && !aligned16(w13_bias)) return fail(NF4MOE_EALIGN, "expert_rows: w13_bias must be 16-byte aligned");
   if (!rows || !row_expert || !y_rows || !w13 || !w2 || n_rows < 0 || E <= 0 || H <= 0 || I <= 0)
     return fail(NF4MOE_EINVAL, "expert_rows: bad arguments");
   if (int rc = check_layer_shapes("expert_rows", w13, w2, H, I)) return rc;
@@ -537,7 +548,7 @@ int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe
   if (!aligned16(workspace) || !aligned16(rows) || !aligned16(y_rows))
     return fail(NF4MOE_EALIGN, "expert_rows: rows, y_rows and workspace must be 16-byte aligned");
   int launches = 0;
-  if (int rc = run_experts(rows, row_expert, w13, w2, y_rows, n_rows, E, H, I, 1, act, regime, ws, stream, &launches)) return rc;
+  if (int rc = run_experts(rows, row_expert, w13, w2, y_rows, n_rows, E, H, I, 1, act, regime, ws, stream, &launches, w13_bias)) return rc;
   g_launches += launches;
   return 0;
 }
@@ -564,15 +575,23 @@ int nf4moe_ep_pack(const void* x, const int32_t* ids, const int32_t* expert_offs
 
 int nf4moe_combine_indexed(const void* y, const float* weights, const int32_t* pair_slot, int T, int k, int H, void* out,
                            void* stream) {
+  return nf4moe_combine_indexed_bias(y, weights, pair_slot, nullptr, nullptr, 0, T, k, H, out, stream);
+}
+
+int nf4moe_combine_indexed_bias(const void* y, const float* weights, const int32_t* pair_slot, const int32_t* ids,
+                                const void* w2_bias, int E, int T, int k, int H, void* out, void* stream) {
   if (!y || !weights || !pair_slot || !out || T < 0 || k <= 0 || H <= 0 || H % 8)
     return fail(NF4MOE_EINVAL, "combine_indexed: bad arguments");
+  if (w2_bias && (!ids || E <= 0 || !aligned16(w2_bias)))
+    return fail(NF4MOE_EINVAL, "combine_indexed: w2_bias needs the GLOBAL topk ids, E and 16-byte alignment");
   if (!aligned16(y) || !aligned16(out)) return fail(NF4MOE_EALIGN, "combine_indexed: 16-byte alignment required");
   if (T == 0) return 0;
   DevInfo di;
   if (int rc = device_info(&di)) return rc;
   const long long total = (long long)T * (H / 8);
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)di.sms * 8);
-  combine_indexed_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y, weights, pair_slot, T, k, H, (__half*)out);
+  combine_indexed_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y, weights, pair_slot, ids, (const __half*)w2_bias, E, T,
+                                                                 k, H, (__half*)out);
   CHECK_LAUNCH("combine_indexed_kernel");
   return 0;
 }

@@ -67,9 +67,18 @@ class B200NF4MoEMethod:
 
     # -- V/.../quantization/bitsandbytes.py:451-471, 508-575: identical parameter names, shapes and attributes --
     def create_weights(self, layer: torch.nn.Module, num_experts: int, hidden_size: int,
-                       intermediate_size_per_partition: int, params_dtype: torch.dtype, **extra_weight_attrs):
+                       intermediate_size_per_partition: int, params_dtype: torch.dtype, has_bias: bool = False,
+                       **extra_weight_attrs):
         quant_ratio = 2  # two 4-bit codes per uint8
         I = intermediate_size_per_partition
+        if has_bias:
+            # gpt-oss expert biases under vLLM's names (V/model_executor/layers/fused_moe/unquantized_fused_moe_method.py
+            # registers the same two for the unquantised path; vLLM's bnb method has none)
+            for name, width in (("w13_bias", 2 * I), ("w2_bias", hidden_size)):
+                b = torch.nn.Parameter(torch.zeros(num_experts, width, dtype=params_dtype), requires_grad=False)
+                for k, v in extra_weight_attrs.items():
+                    setattr(b, k, v)
+                layer.register_parameter(name, b)
         for name, out_dim, in_dim in (("w13_weight", 2 * I, hidden_size), ("w2_weight", hidden_size, I)):
             p = torch.nn.Parameter(torch.empty(num_experts, out_dim * in_dim // quant_ratio, 1, dtype=torch.uint8),
                                    requires_grad=False)
@@ -89,6 +98,7 @@ class B200NF4MoEMethod:
         if not hasattr(layer, "_nf4_w13"):
             self.bind(layer, NF4ExpertWeights.from_vllm_param(layer.w13_weight),
                       NF4ExpertWeights.from_vllm_param(layer.w2_weight))
+        layer._nf4_bias = None   # (re)built from the layer's bias parameters on the next call
 
     def _weights(self, layer):
         if not hasattr(layer, "_nf4_w13"):
@@ -98,13 +108,28 @@ class B200NF4MoEMethod:
     @staticmethod
     def _biases(layer) -> dict:
         """gpt-oss expert biases under vLLM's parameter names (`w13_bias [E, 2I]`, `w2_bias [E, H]`,
-        V/model_executor/models/gpt_oss.py:199), when the layer carries them."""
-        out = {}
+        V/model_executor/models/gpt_oss.py:199), when the layer carries them.  The fp16 contiguous form the
+        kernels read is made ONCE per source tensor and cached on the layer (a cast per call would allocate on the hot path and
+        break CUDA-graph capture); replacing the parameter's storage (a reload) invalidates the cache."""
+        cache = getattr(layer, "_nf4_bias", None)
+        out, key = {}, []
+        for name in ("w13_bias", "w2_bias"):
+            b = getattr(layer, name, None)
+            if b is not None:
+                b = b.data if isinstance(b, torch.nn.Parameter) else b
+                key.append((name, b.data_ptr(), b.dtype, tuple(b.shape)))
+        key = tuple(key)
+        if cache is not None and cache[0] == key:
+            return cache[1]
         for name in ("w13_bias", "w2_bias"):
             b = getattr(layer, name, None)
             if b is not None:
                 b = b.data if isinstance(b, torch.nn.Parameter) else b
                 out[name] = b if (b.dtype == torch.float16 and b.is_contiguous()) else b.to(torch.float16).contiguous()
+        try:
+            layer._nf4_bias = (key, out)
+        except Exception:   # a layer object that refuses new attributes: recompute per call
+            pass
         return out
 
     def _act(self, layer) -> int:
@@ -116,9 +141,24 @@ class B200NF4MoEMethod:
     # -- vLLM 0.22 split signature, V/.../fused_moe_method_base.py:163-172 --
     def apply(self, layer, x: torch.Tensor, topk_weights: torch.Tensor, topk_ids: torch.Tensor, shared_experts=None,
               shared_experts_input=None) -> torch.Tensor:
+        """Routing pre-computed.  Honours the pass-through arguments vLLM's bnb method forwards to `fused_experts`
+        (V/model_executor/layers/quantization/bitsandbytes.py:493-505), read from the layer as vLLM does:
+          * `expert_map` / `global_num_experts` (vLLM's own expert parallelism): global ids are mapped to this rank's local
+            ids, foreign experts become -1 and are skipped by the bucket and combine kernels;
+          * `apply_router_weight_on_input`: the routing weight multiplies the token BEFORE the experts (top_k must be 1, as in
+            vLLM's fused_experts) and the combine then sums with weight 1."""
         w13, w2 = self._weights(layer)
+        expert_map = getattr(layer, "expert_map", None)
+        if expert_map is not None:
+            gne = getattr(layer, "global_num_experts", None)
+            if gne is not None and gne > 0 and expert_map.numel() != gne:
+                raise ValueError(f"expert_map has {expert_map.numel()} entries for global_num_experts={gne}")
+            topk_ids = expert_map[topk_ids.long()].to(torch.int32)
         if getattr(layer, "apply_router_weight_on_input", False):
-            raise NotImplementedError("apply_router_weight_on_input is not part of the gpt-oss NF4 path")
+            if topk_ids.shape[1] != 1:
+                raise ValueError("apply_router_weight_on_input is only defined for top_k == 1 (as in vLLM's fused_experts)")
+            x = (x * topk_weights.to(x.dtype)).contiguous()
+            topk_weights = torch.ones_like(topk_weights, dtype=torch.float32)
         return ops.moe_forward(x, w13, w2, topk_ids.shape[1], topk_ids=topk_ids, topk_weights=topk_weights,
                                act=self._act(layer), regime=self.regime, nested=self.nested, **self._biases(layer))
 

@@ -12,7 +12,45 @@ import torch
 from . import _lib
 from .quant import NF4ExpertWeights, _require_cuda, _stream_ptr
 
-_ws_cache: dict[tuple, torch.Tensor] = {}
+class WorkspacePool:
+    """Scratch buffers for `moe_forward` / `expert_rows`, one per (device, CUDA stream, layer geometry).
+
+    The C ABI's threading contract is "each caller passes its own stream and workspace" (include/nf4moe.h): two streams that ran
+    MoE layers through one shared buffer would race, so the pool is keyed by the stream a call is issued on.  A buffer is sized
+    for the next power of two of the token count (>= 64).  When a larger batch arrives a NEW buffer is allocated and the old
+    one is kept alive: a CUDA graph captured earlier has the old pointer baked in, and freeing it would let later replays
+    scribble over memory the caching allocator has handed to someone else.  Buffers are zero-filled once: their first word is
+    the status word the kernels OR error bits into (`workspace_status`)."""
+
+    def __init__(self):
+        self._live: dict[tuple, tuple[int, torch.Tensor]] = {}
+        self._retired: list[torch.Tensor] = []
+
+    def get(self, device, T: int, E: int, H: int, I: int, k: int) -> torch.Tensor:
+        device = torch.device(device)
+        key = (device.index if device.index is not None else torch.cuda.current_device(),
+               torch.cuda.current_stream(device).cuda_stream, E, H, I, k)
+        cap = 64
+        while cap < T:
+            cap *= 2
+        cur = self._live.get(key)
+        if cur is None or cur[0] < cap:
+            if cur is not None:
+                self._retired.append(cur[1])
+            buf = torch.zeros(workspace_bytes(cap, E, H, I, k), dtype=torch.uint8, device=device)
+            self._live[key] = (cap, buf)
+            return buf
+        return cur[1]
+
+    def buffers(self) -> list[torch.Tensor]:
+        return [b for _, b in self._live.values()] + list(self._retired)
+
+    def release_retired(self) -> None:
+        """Drop superseded buffers (only safe when no CUDA graph captured with them is replayed any more)."""
+        self._retired.clear()
+
+
+_pool = WorkspacePool()
 
 
 def workspace_bytes(T: int, E: int, H: int, I: int, k: int) -> int:
@@ -20,14 +58,28 @@ def workspace_bytes(T: int, E: int, H: int, I: int, k: int) -> int:
 
 
 def get_workspace(device, T: int, E: int, H: int, I: int, k: int) -> torch.Tensor:
-    """A cached scratch buffer (one per device and shape; grown, never shrunk)."""
-    key = (str(device), E, H, I, k)
-    need = workspace_bytes(T, E, H, I, k)
-    buf = _ws_cache.get(key)
-    if buf is None or buf.numel() < need:
-        buf = torch.empty(need, dtype=torch.uint8, device=device)
-        _ws_cache[key] = buf
-    return buf
+    """The calling stream's scratch buffer for this geometry (see WorkspacePool)."""
+    return _pool.get(device, T, E, H, I, k)
+
+
+def new_workspace(device, T: int, E: int, H: int, I: int, k: int) -> torch.Tensor:
+    """A private, zero-filled workspace for callers that manage their own (one per captured CUDA graph, say)."""
+    return torch.zeros(workspace_bytes(T, E, H, I, k), dtype=torch.uint8, device=device)
+
+
+def workspace_status(workspace: torch.Tensor) -> int:
+    """NF4MOE_STATUS_* bits a kernel raised in this workspace (synchronises).  0 = every kernel ran."""
+    return int(workspace[:4].view(torch.int32).item())
+
+
+def check_status(workspace: torch.Tensor | None = None) -> None:
+    """Raise if a kernel refused to run (workspace=None: every pooled buffer).  Synchronises; call it where you sync anyway."""
+    bufs = [workspace] if workspace is not None else _pool.buffers()
+    for b in bufs:
+        st = workspace_status(b)
+        if st:
+            raise _lib.Nf4MoeError(-100, f"kernel status word = {st:#x} (2: decode tcgen05 kernel could not place its pipeline in "
+                                         f"shared memory, 4: prefill tcgen05 kernel likewise); the output is not valid")
 
 
 def route_topk(logits: torch.Tensor, k: int) -> tuple[torch.Tensor, torch.Tensor]:
@@ -203,27 +255,44 @@ def ep_pack(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: int, cap
 
 def expert_rows(rows: torch.Tensor, row_expert: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights,
                 y_rows: torch.Tensor, act: int = _lib.ACT_SWIGLU_OAI, regime: int = _lib.REGIME_AUTO,
-                nested: bool | None = None, workspace: torch.Tensor | None = None) -> torch.Tensor:
-    """y_rows[r] = W2[e] act(W13[e] rows[r]) for e = row_expert[r] in [0, E_local); other rows are left untouched."""
+                nested: bool | None = None, workspace: torch.Tensor | None = None,
+                w13_bias: torch.Tensor | None = None) -> torch.Tensor:
+    """y_rows[r] = W2[e] act(W13[e] rows[r] + w13_bias[e]) for e = row_expert[r] in [0, E_local); other rows are left untouched.
+    w13_bias: fp16 [E_local, 2I] or None."""
     _require_cuda(rows, "rows")
     n, H = rows.shape
     E, I = w13.num_experts, w13.rows // 2
     if workspace is None:
         workspace = get_workspace(rows.device, n, E, H, I, 1)
+    if w13_bias is not None:
+        _require_cuda(w13_bias, "w13_bias")
+        if w13_bias.dtype != torch.float16 or tuple(w13_bias.shape) != (E, 2 * I):
+            raise ValueError(f"w13_bias must be a contiguous fp16 tensor of shape {(E, 2 * I)}")
     q13, q2 = w13.c_struct(nested), w2.c_struct(nested)
     with torch.cuda.device(rows.device):
-        _lib.check(_lib.load_library().nf4moe_expert_rows(
-            rows.data_ptr(), row_expert.data_ptr(), C.byref(q13), C.byref(q2), y_rows.data_ptr(), n, E, H, I, act, regime,
-            workspace.data_ptr(), workspace.numel(), _stream_ptr(rows.device)))
+        _lib.check(_lib.load_library().nf4moe_expert_rows_bias(
+            rows.data_ptr(), row_expert.data_ptr(), C.byref(q13), C.byref(q2), None if w13_bias is None else w13_bias.data_ptr(),
+            y_rows.data_ptr(), n, E, H, I, act, regime, workspace.data_ptr(), workspace.numel(), _stream_ptr(rows.device)))
     return y_rows
 
 
-def combine_indexed(y: torch.Tensor, weights: torch.Tensor, pair_slot: torch.Tensor, out: torch.Tensor | None = None):
+def combine_indexed(y: torch.Tensor, weights: torch.Tensor, pair_slot: torch.Tensor, out: torch.Tensor | None = None,
+                    ids: torch.Tensor | None = None, w2_bias: torch.Tensor | None = None):
+    """out[t] = fp16(sum_slot w * (y[pair_slot] + w2_bias[ids])); w2_bias is the FULL fp16 [E, H] table, ids the global topk ids."""
     T, k = weights.shape
     H = y.shape[-1]
     if out is None:
         out = torch.empty(T, H, dtype=torch.float16, device=y.device)
+    E = 0
+    if w2_bias is not None:
+        if ids is None:
+            raise ValueError("w2_bias needs the global topk ids")
+        _require_cuda(w2_bias, "w2_bias")
+        if w2_bias.dtype != torch.float16 or w2_bias.dim() != 2 or w2_bias.shape[1] != H:
+            raise ValueError("w2_bias must be fp16 [E, H]")
+        E = int(w2_bias.shape[0])
     with torch.cuda.device(y.device):
-        _lib.check(_lib.load_library().nf4moe_combine_indexed(y.data_ptr(), weights.data_ptr(), pair_slot.data_ptr(), T, k, H,
-                                                              out.data_ptr(), _stream_ptr(y.device)))
+        _lib.check(_lib.load_library().nf4moe_combine_indexed_bias(
+            y.data_ptr(), weights.data_ptr(), pair_slot.data_ptr(), None if w2_bias is None else ids.data_ptr(),
+            None if w2_bias is None else w2_bias.data_ptr(), E, T, k, H, out.data_ptr(), _stream_ptr(y.device)))
     return out

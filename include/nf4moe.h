@@ -57,9 +57,10 @@ extern "C" {
 
 /* regime selector for nf4moe_moe_forward */
 #define NF4MOE_REGIME_AUTO 0
-#define NF4MOE_REGIME_GEMV 1  /* decode: HBM-bound NF4 streaming kernel */
-#define NF4MOE_REGIME_GEMM 2  /* tcgen05 grouped GEMM, NF4MOE_GEMM_EXACT operand */
-#define NF4MOE_REGIME_GEMM_FAST 3 /* tcgen05 grouped GEMM, NF4MOE_GEMM_FAST operand */
+#define NF4MOE_REGIME_GEMV 1  /* decode: HBM-bound NF4 streaming kernel (mma.sync) */
+#define NF4MOE_REGIME_GEMM 2  /* tcgen05 kernels with the NF4MOE_GEMM_EXACT operand at every T: the decode-regime kernel while
+                                 token tiles stay <= 32 rows, the prefill grouped GEMM above */
+#define NF4MOE_REGIME_GEMM_FAST 3 /* the same two kernels with the NF4MOE_GEMM_FAST operand */
 
 /* how the tcgen05 kernels turn an NF4 block into the fp16 MMA operand */
 #define NF4MOE_GEMM_EXACT 0 /* fp16_rn(fp32(code) * fp32(absmax)): bit-identical to bnb dequantize_4bit */
@@ -95,6 +96,17 @@ const char* nf4moe_last_error(void);
 /* Scratch the fused forward needs for T tokens (bytes).  Layout is private to the library. */
 size_t nf4moe_workspace_bytes(int T, int E, int H, int I, int k);
 
+/* Byte offset, inside a workspace of that geometry, of an int32 STATUS word.  The kernels only ever OR bits into it and never
+ * clear it, so the caller zeroes it once (e.g. allocates the workspace zero-filled) and may read it whenever it synchronises
+ * anyway: a non-zero value means a kernel refused to run and the output is not valid.  Bits: NF4MOE_STATUS_*.  The host-side
+ * checks of every entry point already reject the shapes that could raise a bit; the word exists so that "a kernel did nothing"
+ * can never pass silently (the reference has no such failure mode to mirror: its per-pair Python loop raises,
+ * P/unsloth_to_vllm_converter.py:298-323).  For the stand-alone nf4moe_gemm_* entry points the word is meta[4]. */
+size_t nf4moe_workspace_status_offset(int T, int E, int H, int I, int k);
+#define NF4MOE_STATUS_EP_OVERFLOW 1  /* nf4moe_ep_pack: a peer got more rows than its capacity (written to ITS status argument) */
+#define NF4MOE_STATUS_DEC_NOFIT 2    /* decode tcgen05 kernel: shared-memory plan did not fit */
+#define NF4MOE_STATUS_GEMM_NOFIT 4   /* prefill tcgen05 kernel: shared-memory plan did not fit */
+
 /* ---- NF4 (de)quantisation ------------------------------------------------------------------------------------ */
 
 /* out_f16[e, i] = fp16_rn( fp32(NF4[q_i]) * absmax[i/64] ) for experts [e0, e0+ne): bit-exact bnb semantics. */
@@ -120,7 +132,9 @@ int nf4moe_route_topk(const void* logits, int logits_dtype, int T, int E, int k,
  *   expert_offsets[E+1]  exclusive prefix of per-expert pair counts
  *   sorted_pairs[T*k]    pair index t*k+slot, grouped by expert, ascending within an expert
  *   active_experts[E]    experts with >=1 pair, ascending;  meta[0] = how many, meta[1] = total kept pairs,
- *                        meta[2] = number of token tiles, meta[3] = largest per-expert count
+ *                        meta[2] = number of token tiles, meta[3] = largest per-expert count; meta has 16 entries:
+ *                        meta[4] is the status word the nf4moe_gemm_* kernels OR NF4MOE_STATUS_* bits into (never written
+ *                        here: zero it once), the rest is reserved
  *   tile_list[4*(T*k/16+E+2)]  (expert, first sorted row, rows, 0) per token tile of the grouped GEMM: an expert with c
  *                        rows gets ceil(c/tile_rows) near-equal tiles, each a multiple of 16 rows except the last.
  *                        tile_rows: multiple of 16 in 16..256, or 0 = what nf4moe_gemm_* expect for this (T, k, E).
@@ -199,10 +213,22 @@ int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe
                        void* y_rows, int n_rows, int E, int H, int I, int act, int regime, void* workspace,
                        size_t workspace_bytes, void* stream);
 
+/* The same with gpt-oss's up-projection bias (w13_bias fp16 [E, 2I], LOCAL expert index; NULL = none), added before the
+ * activation exactly as nf4moe_moe_forward_bias does. */
+int nf4moe_expert_rows_bias(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
+                            const void* w13_bias, void* y_rows, int n_rows, int E, int H, int I, int act, int regime,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* Combine side.  out[t, :] = fp16( sum_slot weights[t,slot] * y[pair_slot[t*k+slot], :] ) -- nf4moe_combine's arithmetic and
  * order, reading each pair's row where the return all-to-all left it. */
 int nf4moe_combine_indexed(const void* y, const float* weights, const int32_t* pair_slot, int T, int k, int H, void* out,
                            void* stream);
+
+/* The same with the down-projection bias: w2_bias is the FULL table fp16 [E, H] (every rank keeps a copy: 184 KB for
+ * gpt-oss-20b), indexed by the home rank's GLOBAL topk ids [T, k]; it is added at home in fp32 before the routing weight, so
+ * the expert-parallel result equals nf4moe_moe_forward_bias bit for bit.  w2_bias == NULL: ids / E are ignored. */
+int nf4moe_combine_indexed_bias(const void* y, const float* weights, const int32_t* pair_slot, const int32_t* ids,
+                                const void* w2_bias, int E, int T, int k, int H, void* out, void* stream);
 
 /* Number of kernels the last nf4moe_moe_forward / nf4moe_expert_rows on this thread launched (bench.py's gpu_launches). */
 int nf4moe_last_launch_count(void);

@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
-"""CUDA-event timing of the two decode GEMV kernels alone (w13+SwiGLU, w2), rotating over several layers so the
-126 MB L2 never holds the weights.  NF4MOE_GEMV_CFG (19 / 13 / 23) selects the kernel configuration."""
+"""CUDA-event timing of the two expert kernels alone (w13+SwiGLU, w2) in one regime, rotating over several layers so the
+126 MB L2 never holds the weights.  --lib PATH times a differently built libnf4moe (build.py --out=...; e.g. another dequant
+pool shape -DNF4MOE_DEC_GROUPS=3, or an -DNF4MOE_EXPERIMENTS build, where NF4MOE_GEMV_CFG = 19 / 13 / 23 picks the GEMV shape)."""
 import argparse
 import importlib
 import os
@@ -14,12 +15,16 @@ p.add_argument("--experts", type=int, default=32)
 p.add_argument("--absmax", nargs="+", default=["nested", "flat"])
 p.add_argument("--cfg", type=int, nargs="+", default=[0])
 p.add_argument("--regime", default="gemv", choices=["gemv", "gemm", "gemm_fast"])
+p.add_argument("--lib", default=None)
+p.add_argument("--tag", default="")
 a = p.parse_args()
 if len(a.cfg) > 1:   # the library reads the override once per process: fan out
     import subprocess
     for c in a.cfg:
         argv = [sys.executable, __file__, "--cfg", str(c), "--layers", str(a.layers), "--reps", str(a.reps), "--experts",
                 str(a.experts), "--regime", a.regime, "--tokens", *map(str, a.tokens), "--absmax", *a.absmax]
+        if a.lib:
+            argv += ["--lib", a.lib]
         subprocess.run(argv, check=True)
     sys.exit(0)
 os.environ["NF4MOE_GEMV_CFG"] = str(a.cfg[0])
@@ -30,6 +35,8 @@ sys.path.insert(0, ROOT)
 from oracle import nf4_oracle as orc  # code2 table (data) only
 
 pkg = importlib.import_module("gpt-oss-vllm_b200")
+if a.lib:
+    pkg.load_library(path=os.path.abspath(a.lib))
 dev = torch.device("cuda:0")
 H = I = 2880
 E = a.experts
@@ -79,5 +86,5 @@ for T in a.tokens:
         b13, b2 = ea * stack[0][0].nbytes(nested), ea * stack[0][1].nbytes(nested)
         m13, m2 = min(t13), min(t2)
         a13, a2 = sum(t13) / len(t13), sum(t2) / len(t2)
-        print(f"{a.regime} cfg={a.cfg[0]:2d} T={T:3d} E_act={ea:2d} {mode:6s} w13 {a13:7.1f} us (min {m13:6.1f}) {b13 / a13 / 1e3:7.1f} GB/s | "
+        print(f"{a.tag}{a.regime} cfg={a.cfg[0]:2d} T={T:3d} E_act={ea:2d} {mode:6s} w13 {a13:7.1f} us (min {m13:6.1f}) {b13 / a13 / 1e3:7.1f} GB/s | "
               f"w2 {a2:7.1f} us (min {m2:6.1f}) {b2 / a2 / 1e3:7.1f} GB/s | both {(b13 + b2) / (a13 + a2) / 1e3:7.1f} GB/s", flush=True)

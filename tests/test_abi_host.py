@@ -54,6 +54,40 @@ def test_workspace_bytes(pkg):
     assert ws(1, 0, 1, 1, 1) == 0
 
 
+def test_status_word_and_pool_contract(pkg):
+    lib = pkg.load_library()
+    assert lib.nf4moe_workspace_status_offset(64, 32, 2880, 2880, 4) == 0      # the first word, for every geometry
+    assert lib.nf4moe_workspace_status_offset(8192, 128, 2880, 2880, 4) == 0
+    pool = pkg.ops.WorkspacePool()
+    assert pool.buffers() == []
+    assert (pkg._lib.STATUS_EP_OVERFLOW, pkg._lib.STATUS_DEC_NOFIT, pkg._lib.STATUS_GEMM_NOFIT) == (1, 2, 4)
+    header = open(os.path.join(ROOT, "include", "nf4moe.h")).read()
+    for name, val in (("NF4MOE_STATUS_EP_OVERFLOW", 1), ("NF4MOE_STATUS_DEC_NOFIT", 2), ("NF4MOE_STATUS_GEMM_NOFIT", 4)):
+        assert re.search(rf"#define {name} {val}\b", header)
+
+
+def test_shipped_library_reads_no_environment_on_the_launch_path():
+    """Experiment switches (ring depths, tile sizes, kernel variants) exist only behind -DNF4MOE_EXPERIMENTS: a stray
+    environment variable must never change the numerics or the kernel choice of the drop-in library."""
+    csrc = os.path.join(ROOT, "gpt-oss-vllm_b200", "csrc")
+    for f in os.listdir(csrc):
+        src = open(os.path.join(csrc, f)).read()
+        # every getenv sits inside an #ifdef NF4MOE_EXPERIMENTS block
+        depth, guarded = 0, True
+        stack = []
+        for line in src.splitlines():
+            t = line.strip()
+            if t.startswith("#if"):
+                stack.append("NF4MOE_EXPERIMENTS" in t and not t.startswith("#ifndef"))
+            elif t.startswith("#else") and stack:
+                stack[-1] = False
+            elif t.startswith("#endif") and stack:
+                stack.pop()
+            elif "getenv(" in t and not t.startswith("//"):
+                assert any(stack), f"{f}: getenv outside NF4MOE_EXPERIMENTS: {t}"
+    assert "NF4MOE_LIB" not in open(os.path.join(ROOT, "gpt-oss-vllm_b200", "_lib.py")).read()
+
+
 def test_config_and_create_weights_mirror_reference(pkg):
     cfg = pkg.B200NF4MoEConfig()
     assert cfg.get_name() == "bnb_moe_4bit"                                 # P/bnb_moe_4bit.py:33

@@ -1,0 +1,374 @@
+"""GPU parity, round 2: the benchmarked shapes against the oracle (full-size 20b layer, T = 64 / 128 / 256, flat and nested
+absmax, uniform and skewed routing), the CUDA dequant pinned to the reference-held golden vectors, the EXACT operand of the
+decode-regime tcgen05 kernel, the status word, and a REAL vLLM FusedMoE driving the plugin's method.  Every call goes through
+the C ABI.  Bars (north_star): dequant bit-exact, router ids bit-exact, MoE output max-abs <= 1e-2 and rel <= 2e-3."""
+import hashlib
+import importlib
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nf4_oracle as orc
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _load(name, path):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+make_golden = _load("make_golden", os.path.join(HERE, "golden", "make_golden.py"))
+_parity = _load("_gpu_parity_helpers", os.path.join(HERE, "test_gpu_parity.py"))
+assert_moe_close, make_layer = _parity.assert_moe_close, _parity.make_layer
+
+pytestmark = pytest.mark.gpu
+
+E20, H20, I20, K20 = 32, 2880, 2880, 4
+
+
+def _state(w, e):
+    return {"packed": w.packed[e].cpu().numpy().reshape(-1), "absmax_u8": w.absmax_u8[e].cpu().numpy(),
+            "absmax2": w.absmax2[e].cpu().numpy(), "code2": w.code2.cpu().numpy(), "offset": w.offset[e].item(),
+            "shape": (w.rows, w.cols), "blocksize": 64}
+
+
+@pytest.fixture(scope="module")
+def full_layer(pkg, cuda_device):
+    """One full-size gpt-oss-20b MoE layer quantised on the device + the oracle's dequantised fp16 copy of every expert (made
+    once: ~1.6 GB of host memory, a few seconds)."""
+    g = torch.Generator(device=cuda_device).manual_seed(20250805)
+    code2 = torch.from_numpy(orc.create_dynamic_map())
+    w13 = pkg.NF4ExpertWeights.quantize((torch.randn(E20, 2 * I20, H20, generator=g, device=cuda_device) * 0.02).half(), code2)
+    w2 = pkg.NF4ExpertWeights.quantize((torch.randn(E20, H20, I20, generator=g, device=cuda_device) * 0.02).half(), code2)
+    d13 = np.stack([orc.dequant_state(_state(w13, e)) for e in range(E20)])
+    d2 = np.stack([orc.dequant_state(_state(w2, e)) for e in range(E20)])
+    return w13, w2, d13, d2
+
+
+def _inputs(dev, T, skewed, seed):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    x = torch.randn(T, H20, generator=g, device=dev).half()
+    lg = torch.randn(T, E20, generator=g, device=dev).float()
+    if skewed:   # logits += 2 * onehot(t mod 4): load imbalance, experts 0..3 get most of the rows
+        lg[torch.arange(T, device=dev), torch.arange(T, device=dev) % 4] += 2.0
+    return x, lg.half()
+
+
+@pytest.mark.parametrize("routing", ["uniform", "skewed"])
+@pytest.mark.parametrize("absmax", ["flat", "nested"])
+@pytest.mark.parametrize("T", [64, 128, 256])
+def test_full_size_decode_vs_oracle(pkg, cuda_device, full_layer, T, absmax, routing):
+    """The shapes the bench times, in the regime the drop-in apply() uses (AUTO -> decode tcgen05 kernel, FAST operand), on BOTH
+    absmax forms -- flat fp32 is what vLLM binds (V/model_executor/model_loader/bitsandbytes_loader.py:585-617) and is the form
+    on which round 1's kernel silently did nothing once an expert had more than 16 rows.  Compared with the oracle on every
+    token; the largest per-expert count is asserted to exceed 16 so the N = 32 tile path is really taken."""
+    w13, w2, d13, d2 = full_layer
+    x, lg = _inputs(cuda_device, T, routing == "skewed", 1000 + T)
+    nested = absmax == "nested"
+    ws = pkg.ops.new_workspace(cuda_device, T, E20, H20, I20, K20)
+    out, ids, wts = pkg.ops.moe_forward(x, w13, w2, K20, router_logits=lg, nested=nested, workspace=ws, return_routing=True)
+    assert pkg.ops.workspace_status(ws) == 0
+    rid, _ = orc.route_topk(lg.cpu().numpy(), K20)
+    assert np.array_equal(ids.cpu().numpy(), rid)
+    counts = np.bincount(rid.reshape(-1), minlength=E20)
+    if T >= 128 or routing == "skewed":
+        assert counts.max() > 16, counts.max()
+    ref = orc.moe_forward_ref(x.cpu().numpy(), lg.cpu().numpy(), d13, d2, k=K20)
+    assert_moe_close(out.cpu().numpy(), ref)
+    assert float(out.float().abs().max()) > 1e-3          # and it is not a buffer of zeros / stale scratch
+    # EXACT operand through the same decode-regime kernel: also inside the tolerance, and not identical to FAST
+    out_e = pkg.ops.moe_forward(x, w13, w2, K20, topk_ids=ids, topk_weights=wts, nested=nested, workspace=ws, regime=pkg.REGIME_GEMM)
+    assert pkg.ops.workspace_status(ws) == 0
+    assert_moe_close(out_e.cpu().numpy(), ref)
+
+
+def test_apply_on_vllm_bound_layer_full_size(pkg, cuda_device, full_layer):
+    """B200NF4MoEMethod.apply() on a layer whose parameters carry vLLM's fused, de-nested `bnb_quant_state` (flat fp32 absmax,
+    `NF4ExpertWeights.from_vllm_param`), T = 128, full size: the exact call path round 1 got wrong."""
+    w13, w2, d13, d2 = full_layer
+    T = 128
+    method = pkg.B200NF4MoEConfig().get_quant_method(None, "model.layers.0.mlp.experts")
+    layer = torch.nn.Module()
+    method.create_weights(layer, E20, H20, I20, torch.float16)
+    layer.to(cuda_device)
+    layer.w13_weight.data = w13.packed
+    layer.w2_weight.data = w2.packed
+
+    class QS:   # V/model_executor/model_loader/bitsandbytes_loader.py:673-692
+        def __init__(self, absmax):
+            self.absmax, self.blocksize, self.quant_type, self.nested = absmax.reshape(-1), 64, "nf4", False
+    layer.w13_weight.bnb_quant_state, layer.w2_weight.bnb_quant_state = QS(w13.absmax), QS(w2.absmax)
+    method.process_weights_after_loading(layer)
+    assert layer._nf4_w13.absmax is not None and not layer._nf4_w13.has_nested
+    x, lg = _inputs(cuda_device, T, True, 77)
+    ids, wts = pkg.ops.route_topk(lg, K20)
+    out = method.apply(layer, x, wts, ids, None, None)
+    pkg.ops.check_status()
+    ref = orc.moe_forward_ref(x.cpu().numpy(), lg.cpu().numpy(), d13, d2, k=K20)
+    assert_moe_close(out.cpu().numpy(), ref)
+    assert torch.equal(out, method.apply_legacy(layer, x, lg, K20))
+
+
+def test_prefill_8192_sample_vs_oracle(pkg, cuda_device, full_layer):
+    """BASELINE.json configs[2] at full size: T = 8192 through the prefill grouped GEMM (EXACT operand, what AUTO picks), 64
+    sampled tokens against the oracle."""
+    w13, w2, d13, d2 = full_layer
+    T = 8192
+    g = torch.Generator(device=cuda_device).manual_seed(8192)
+    x = torch.randn(T, H20, generator=g, device=cuda_device).half()
+    lg = torch.randn(T, E20, generator=g, device=cuda_device).half()
+    assert pkg.ops.auto_regime(T, K20, E20) == pkg.REGIME_GEMM
+    ws = pkg.ops.new_workspace(cuda_device, T, E20, H20, I20, K20)
+    out = pkg.ops.moe_forward(x, w13, w2, K20, router_logits=lg, nested=True, workspace=ws)
+    assert pkg.ops.workspace_status(ws) == 0
+    pick = np.linspace(0, T - 1, 64).astype(np.int64)
+    ref = orc.moe_forward_ref(x[pick].cpu().numpy(), lg[pick].cpu().numpy(), d13, d2, k=K20)
+    assert_moe_close(out[pick].cpu().numpy(), ref)
+    out_f = pkg.ops.moe_forward(x, w13, w2, K20, router_logits=lg, nested=False, workspace=ws, regime=pkg.REGIME_GEMM_FAST)
+    assert pkg.ops.workspace_status(ws) == 0
+    assert_moe_close(out_f[pick].cpu().numpy(), ref)
+
+
+# ------------------------------------------------------------------------------------------------- golden pins
+def _swap_nibbles(packed: np.ndarray) -> np.ndarray:
+    return ((packed >> 4) | ((packed & 0x0F) << 4)).astype(np.uint8)
+
+
+@pytest.mark.parametrize("name,shape,which", [("dequant_unsloth_expert_cpu/gate_up_vec", (5760, 2880), "streaming"),
+                                              ("dequant_unsloth_expert_cpu/down_scalar", (2880, 2880), "streaming"),
+                                              ("load_and_dequantize_unsloth_weight/down_vec", (2880, 2880), "direct")])
+def test_cuda_dequant_reproduces_reference_held_vectors(pkg, cuda_device, golden, name, shape, which):
+    """Direct pin of the CUDA dequant kernel to outputs of the reference's OWN Python (P/streaming_unsloth_bnb.py:109-230,
+    P/unsloth_direct_loader.py:51-142, run with bnb stubbed by tests/golden/make_golden.py): the reference unpacks low nibble
+    first and scales by its own (offset-free) absmax, so with the packed bytes nibble-swapped and that absmax handed over as
+    the flat fp32 form, `nf4moe_dequant` must reproduce the committed SHA-256 of the reference's fp16 output bit for bit --
+    the NF4 table, the block indexing, the fp32 multiply and the single rounding are thereby pinned to reference-held data,
+    independently of the oracle's bnb-semantics mode."""
+    _, meta = golden
+    m = meta[name]
+    st = make_golden.synth_state(m["seed"], m["n_weights"], m["scalar_nested"])
+    code = st["nested_quant_map"].astype(np.float32)[st["absmax_u8"].astype(np.int64)]
+    if which == "direct":
+        absmax = orc.dequantize_absmax_reference(st["absmax_u8"], st["nested_absmax"], st["nested_quant_map"])
+    elif st["nested_absmax"].size == 1:
+        absmax = (code * np.float32(st["nested_absmax"][0])).astype(np.float32)
+    else:   # shape mismatch branch of P/streaming_unsloth_bnb.py:158-171: the mean of nested_absmax (torch fp32 reduction)
+        mean = torch.from_numpy(np.ascontiguousarray(st["nested_absmax"], dtype=np.float32)).mean()
+        absmax = (torch.from_numpy(code.copy()) * mean).numpy()
+    state = {"packed": _swap_nibbles(st["packed"]), "absmax_f32": absmax.astype(np.float32), "shape": shape, "blocksize": 64}
+    w = pkg.NF4ExpertWeights.from_states([state], cuda_device)
+    out = w.dequantize(nested=False).cpu().numpy()[0]
+    flat = np.ascontiguousarray(out).reshape(-1)
+    assert list(out.shape) == m["shape"]
+    assert flat.view(np.uint16)[np.asarray(m["sample_pos"])].tolist() == m["sample_bits"]
+    assert hashlib.sha256(flat.tobytes()).hexdigest() == m["sha256"]
+
+
+def test_bitsandbytes_cross_check_or_recorded_absence(pkg, cuda_device):
+    """SURVEY 8(c) optional cross-check: if bitsandbytes imports on this box, the oracle's bnb-semantics dequant (the mode the
+    CUDA kernels are graded against) must equal bnb.functional.dequantize_4bit bit for bit; if it does not import, the absence is
+    the recorded outcome and the test passes."""
+    try:
+        import bitsandbytes as bnb   # noqa: F401
+        from bitsandbytes.functional import dequantize_4bit, quantize_4bit
+    except Exception as exc:
+        print(f"bitsandbytes unavailable on this box: {type(exc).__name__}: {exc}")
+        return
+    g = torch.Generator(device=cuda_device).manual_seed(5)
+    w = (torch.randn(256, 512, generator=g, device=cuda_device) * 0.02).half()
+    q, state = quantize_4bit(w, blocksize=64, compress_statistics=True, quant_type="nf4")
+    ref = dequantize_4bit(q, state).cpu().numpy()
+    st = {"packed": q.cpu().numpy().reshape(-1), "absmax_u8": state.absmax.cpu().numpy(),
+          "absmax2": state.state2.absmax.cpu().numpy(), "code2": state.state2.code.cpu().numpy(),
+          "offset": float(state.offset.item()), "shape": (256, 512), "blocksize": 64}
+    assert np.array_equal(orc.dequant_state(st).view(np.uint16), ref.view(np.uint16))
+    got = pkg.NF4ExpertWeights.from_states([st], cuda_device).dequantize(nested=True).cpu().numpy()[0]
+    assert np.array_equal(got.view(np.uint16), ref.view(np.uint16))
+
+
+# ------------------------------------------------------------------------------------------------- decode kernel, EXACT operand
+@pytest.mark.parametrize("nested", [False, True])
+def test_decode_kernel_exact_operand_is_bit_exact_dequant(pkg, cuda_device, nested):
+    """One-hot activations through the DECODE-regime tcgen05 kernel (token tiles <= 32 rows) in EXACT mode return the
+    dequantised weight columns themselves: the A operand must be bit-identical to bnb's dequantize_4bit; K = 320 (5 k-blocks:
+    one full 4-block stage + a padded one) and rows % 128 != 0."""
+    E, H, I, k = 2, 320, 96, 1
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 157, E, H, I)
+    T = 24                                        # 12 tokens per expert -> 32-row tiles -> dec_kernel
+    d13 = np.stack([orc.dequant_state(s) for s in st13])      # [E, 2I, H]
+    for c0 in range(0, H, T):
+        cols = np.arange(c0, min(c0 + T, H))
+        x = np.zeros((T, H), np.float16)
+        x[np.arange(cols.size), cols] = 1
+        ids = (np.arange(T) % E).astype(np.int32).reshape(T, 1)
+        b = pkg.ops.bucket(torch.from_numpy(ids).to(cuda_device), E)
+        assert int(b["meta"][3].item()) <= 32
+        xs = pkg.ops.permute_rows(torch.from_numpy(x).to(cuda_device), b, k)
+        raw = pkg.ops.expert_w13(xs, w13, b, T, k, act=pkg.ACT_CHUNK_SILU, regime=pkg.REGIME_GEMM, nested=nested).cpu().numpy()
+        assert int(b["meta"][4].item()) == 0
+        sp = b["sorted_pairs"].cpu().numpy()[:T]
+        for s, pair in enumerate(sp):
+            if pair < cols.size:
+                assert np.array_equal(raw[s].view(np.uint16), d13[ids[pair, 0]][:, cols[pair]].view(np.uint16))
+
+
+@pytest.mark.parametrize("T,E,H,I,k", [(9, 8, 128, 128, 2), (40, 8, 256, 192, 4), (100, 4, 192, 128, 2), (64, 32, 320, 128, 4)])
+def test_decode_kernel_exact_vs_fast_vs_oracle(pkg, cuda_device, T, E, H, I, k):
+    """REGIME_GEMM (EXACT operand, what vLLM `operand_mode="exact"` selects) and REGIME_GEMM_FAST through the decode-regime
+    kernel, flat and nested: all inside the north-star tolerance, and flat == nested bit for bit in each mode."""
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 163, E, H, I)
+    rng = np.random.default_rng(T * 7)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    xd, lgd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(lg).to(cuda_device)
+    ref = orc.moe_forward_from_states(x, lg, st13, st2, k=k)
+    for regime in (pkg.REGIME_GEMM, pkg.REGIME_GEMM_FAST):
+        o_f = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=regime, nested=False)
+        o_n = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, regime=regime, nested=True)
+        assert torch.equal(o_f, o_n)
+        assert_moe_close(o_f.cpu().numpy(), ref)
+    pkg.ops.check_status()
+
+
+def test_per_expert_code2_tables(pkg, cuda_device):
+    """code2_stride = 256 (one double-quant table per expert): the decode kernel then stages the expert's table per item
+    instead of using the per-lane copy in the decode table's holes; results must not change."""
+    E, H, I, k, T = 4, 256, 128, 2, 20
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 171, E, H, I)
+    x = torch.randn(T, H, generator=torch.Generator().manual_seed(1)).half().to(cuda_device)
+    lg = torch.randn(T, E, generator=torch.Generator().manual_seed(2)).half().to(cuda_device)
+    base = pkg.ops.moe_forward(x, w13, w2, k, router_logits=lg, nested=True, regime=pkg.REGIME_GEMM_FAST)
+    for w in (w13, w2):
+        w.code2 = w.code2.reshape(1, 256).repeat(E, 1).contiguous()
+    assert w13.c_struct(True).code2_stride == 256
+    per = pkg.ops.moe_forward(x, w13, w2, k, router_logits=lg, nested=True, regime=pkg.REGIME_GEMM_FAST)
+    assert torch.equal(base, per)
+
+
+# ------------------------------------------------------------------------------------------------- failure is loud
+def test_shape_the_pipeline_cannot_place_is_refused(pkg, cuda_device):
+    """K = 4096 with flat fp32 absmax does not fit the decode kernel's shared-memory plan (two 32 KB absmax stages + rings):
+    the C ABI returns an error instead of launching a kernel that would do nothing (round 1 returned 0 and garbage)."""
+    E, H, I, k, T = 2, 4096, 64, 1, 40
+    packed = torch.zeros(E, 2 * I * H // 2, 1, dtype=torch.uint8, device=cuda_device)
+    w13 = pkg.NF4ExpertWeights(packed, 2 * I, H, absmax=torch.ones(E, 2 * I * H // 64, device=cuda_device))
+    ids = torch.zeros(T, 1, dtype=torch.int32, device=cuda_device)
+    b = pkg.ops.bucket(ids, E)
+    xs = pkg.ops.permute_rows(torch.zeros(T, H, dtype=torch.float16, device=cuda_device), b, k)
+    try:
+        pkg.ops.expert_w13(xs, w13, b, T, k, regime=pkg.REGIME_GEMM_FAST, nested=False)
+    except pkg.Nf4MoeError as exc:
+        assert "shared-memory plan" in str(exc)
+    else:   # if a future plan does fit, it must really have run: no status bit, finite output
+        assert int(b["meta"][4].item()) == 0
+
+
+# ------------------------------------------------------------------------------------------------- real vLLM layer
+def test_real_vllm_fused_moe_forward(pkg, cuda_device):
+    """What P/patch_6_add_bnb_moe.py:75-107 and P/patch_9_fusedmoe_unsloth.py:19-56 were trying to reach: a REAL
+    vllm FusedMoE built with quant_config = the plugin's config, packed weights + `bnb_quant_state` bound the way vLLM's
+    bitsandbytes loader leaves them, then the layer's own quant_method.apply() (the call the MoE runner makes) and, when the
+    runner's custom-op path is usable on this box, the layer's forward."""
+    pytest.importorskip("vllm")
+    build_real_fused_moe = _load("_loader_plugin_helpers", os.path.join(HERE, "test_loader_plugin.py")).build_real_fused_moe
+    plug = importlib.import_module("gpt-oss-vllm_b200.vllm_plugin")
+    try:
+        cls = plug.register()
+        E, H, I, k, T = 8, 256, 128, 4, 48
+        layer, vc = build_real_fused_moe(cls, device="cuda", E=E, H=H, I=I, top_k=k)
+    except Exception as exc:
+        pytest.skip(f"vLLM cannot build a FusedMoE on this box: {type(exc).__name__}: {exc}")
+    from vllm.model_executor.layers.fused_moe.fused_moe_method_base import FusedMoEMethodBase
+    assert isinstance(layer.quant_method, FusedMoEMethodBase)
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 181, E, H, I)
+    layer.to(cuda_device)
+    layer.w13_weight.data.copy_(w13.packed)
+    layer.w2_weight.data.copy_(w2.packed)
+
+    class QS:
+        def __init__(self, absmax):
+            self.absmax, self.blocksize, self.quant_type, self.nested = absmax.reshape(-1), 64, "nf4", False
+    layer.w13_weight.bnb_quant_state, layer.w2_weight.bnb_quant_state = QS(w13.absmax), QS(w2.absmax)
+    rng = np.random.default_rng(5)
+    b13 = (rng.standard_normal((E, 2 * I)) * 0.3).astype(np.float16)
+    b2 = (rng.standard_normal((E, H)) * 0.3).astype(np.float16)
+    layer.w13_bias.data.copy_(torch.from_numpy(b13))
+    layer.w2_bias.data.copy_(torch.from_numpy(b2))
+    layer.quant_method.process_weights_after_loading(layer)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    xd, lgd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(lg).to(cuda_device)
+    ref = orc.moe_forward_from_states(x, lg, st13, st2, k=k, b13=b13, b2=b2)
+    ids, wts = pkg.ops.route_topk(lgd, k)
+    out = layer.quant_method.apply(layer, xd, wts, ids, None, None)
+    pkg.ops.check_status()
+    assert_moe_close(out.cpu().numpy(), ref)
+    # the whole layer through vLLM's runner (router + custom op + our apply); a vLLM-internal failure is recorded, not hidden
+    try:
+        from vllm.forward_context import set_forward_context
+        with set_forward_context(None, vc):
+            full = layer(xd.clone(), lgd)
+    except Exception as exc:
+        print(f"vLLM runner path not usable on this box ({type(exc).__name__}: {exc}); quant_method.apply() verified instead")
+        return
+    assert_moe_close(full.cpu().numpy(), ref)
+
+
+def test_apply_pass_throughs(pkg, cuda_device):
+    """`expert_map` / `global_num_experts` and `apply_router_weight_on_input`, read from the layer as vLLM's bnb method reads
+    them (V/model_executor/layers/quantization/bitsandbytes.py:493-505)."""
+    E, H, I, T = 8, 128, 128, 12
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 191, E, H, I)
+    rng = np.random.default_rng(9)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    xd = torch.from_numpy(x).to(cuda_device)
+    # (a) expert_map: 16 global experts, this rank owns global 8..15 as local 0..7
+    lg16 = rng.standard_normal((T, 16)).astype(np.float16)
+    gids, gw = orc.route_topk(lg16, 4)
+    method = pkg.B200NF4MoEMethod(top_k=4)
+    layer = torch.nn.Module()
+    method.bind(layer, w13, w2)
+    emap = torch.full((16,), -1, dtype=torch.int32, device=cuda_device)
+    emap[8:] = torch.arange(8, dtype=torch.int32, device=cuda_device)
+    layer.expert_map, layer.global_num_experts = emap, 16
+    out = method.apply(layer, xd, torch.from_numpy(gw).to(cuda_device), torch.from_numpy(gids).to(cuda_device), None, None)
+    local = gids >= 8
+    lids = np.where(local, gids - 8, 0).astype(np.int32)
+    ref = orc.moe_forward_from_states(x, lg16[:, :8], st13, st2, k=4, topk=(lids, np.where(local, gw, 0).astype(np.float32)))
+    assert_moe_close(out.cpu().numpy(), ref)
+    layer.global_num_experts = 12
+    with pytest.raises(ValueError):
+        method.apply(layer, xd, torch.from_numpy(gw).to(cuda_device), torch.from_numpy(gids).to(cuda_device), None, None)
+    # (b) apply_router_weight_on_input, top_k = 1
+    layer2 = torch.nn.Module()
+    method.bind(layer2, w13, w2)
+    layer2.apply_router_weight_on_input = True
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    ids1, w1 = orc.route_topk(lg, 1)
+    w1 = (w1 * 0.5).astype(np.float32)          # softmax over one logit is 1.0; scale it so the test can tell where it is applied
+    out1 = method.apply(layer2, xd, torch.from_numpy(w1).to(cuda_device), torch.from_numpy(ids1).to(cuda_device), None, None)
+    x_scaled = (torch.from_numpy(x) * torch.from_numpy(w1).half()).numpy()
+    ref1 = orc.moe_forward_from_states(x_scaled, lg, st13, st2, k=1, topk=(ids1, np.ones_like(w1)))
+    assert_moe_close(out1.cpu().numpy(), ref1)
+    with pytest.raises(ValueError):
+        layer2.apply_router_weight_on_input = True
+        method.apply(layer2, xd, torch.from_numpy(gw).to(cuda_device), torch.from_numpy(np.minimum(gids, 7)).to(cuda_device), None, None)
+
+
+def test_workspace_pool_is_per_stream_and_keeps_captured_buffers(pkg, cuda_device):
+    pool = pkg.ops.WorkspacePool()
+    a = pool.get(cuda_device, 16, 8, 128, 128, 2)
+    assert pool.get(cuda_device, 64, 8, 128, 128, 2) is a                  # same capacity bucket
+    s = torch.cuda.Stream(device=cuda_device)
+    with torch.cuda.stream(s):
+        b = pool.get(cuda_device, 16, 8, 128, 128, 2)
+    assert b is not a and b.data_ptr() != a.data_ptr()                     # another stream, another buffer
+    big = pool.get(cuda_device, 300, 8, 128, 128, 2)
+    assert big is not a and any(t is a for t in pool.buffers())            # the superseded buffer stays alive (captured graphs)
+    assert pkg.ops.workspace_status(big) == 0 and int(a[:4].view(torch.int32).item()) == 0

@@ -62,20 +62,75 @@ def test_loader_fails_loudly(tmp_path):
     assert ld.load_expert_matrix(good.get, "x", 64, 64, offset_override=0.25)["offset"] == 0.25
 
 
-def test_vllm_plugin_registers_config():
+def _vllm_or_skip():
     pytest.importorskip("vllm")
     plug = importlib.import_module("gpt-oss-vllm_b200.vllm_plugin")
     try:
         cls = plug.register()
-    except Exception as exc:   # vLLM import needs CUDA libs on some boxes; the shim itself is exercised below either way
-        pytest.skip(f"vLLM could not be imported here: {type(exc).__name__}")
+    except Exception as exc:   # vLLM import needs CUDA libs on some boxes
+        pytest.skip(f"vLLM could not be imported here: {type(exc).__name__}: {exc}")
+    return plug, cls
+
+
+def test_vllm_plugin_registers_config():
+    plug, cls = _vllm_or_skip()
+    from vllm.model_executor.layers.fused_moe.fused_moe_method_base import FusedMoEMethodBase
     from vllm.model_executor.layers.quantization import get_quantization_config
     assert get_quantization_config(plug.NAME) is cls and plug.register() is cls
     cfg = cls.from_config({"top_k": 4})
     assert cfg.get_name() == plug.NAME and cfg.get_min_capability() == 100 and cfg.get_supported_act_dtypes() == [torch.float16]
+    assert cfg.operand_mode == "fast" and cls.from_config({"operand_mode": "exact"}).operand_mode == "exact"
+    with pytest.raises(ValueError):
+        cls.from_config({"operand_mode": "sloppy"})
 
     class FusedMoE(torch.nn.Module):
         pass
     m = cfg.get_quant_method(FusedMoE(), "model.layers.0.mlp.experts")
-    assert isinstance(m, plug.VllmNF4MoEMethod) and m.top_k == 4
+    assert isinstance(m, FusedMoEMethodBase)            # what V/model_executor/layers/fused_moe/layer.py:363 asserts
+    assert isinstance(m, plug.build_method_class()) and m.inner.top_k == 4 and m.is_monolithic is False
+    lib = importlib.import_module("gpt-oss-vllm_b200._lib")
+    assert m.inner.regime == lib.REGIME_AUTO                                           # operand_mode is honoured, not ignored:
+    m2 = cls.from_config({"operand_mode": "exact"}).get_quant_method(FusedMoE(), "model.layers.0.mlp.experts")
+    assert m2.inner.regime == lib.REGIME_GEMM                                          # "exact" -> the bit-exact tcgen05 operand
     assert cfg.get_quant_method(torch.nn.Linear(2, 2), "model.layers.0.self_attn.qkv_proj") is None
+
+
+def build_real_fused_moe(cls, device="cpu", E=4, H=128, I=64, top_k=2, has_bias=True, operand_mode="fast", prefix=None,
+                         apply_router_weight_on_input=False):
+    """A REAL vllm FusedMoE layer whose quant_config is the plugin's config (what P/patch_6_add_bnb_moe.py:75-107 tried to
+    reach with `FusedMoE(quant_config=moe_quant_config)`).  Returns (layer, vllm_config)."""
+    from vllm.config import DeviceConfig, VllmConfig, set_current_vllm_config
+    from vllm.distributed import init_distributed_environment, initialize_model_parallel
+    from vllm.distributed.parallel_state import model_parallel_is_initialized
+    from vllm.model_executor.layers.fused_moe import FusedMoE
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    vc = VllmConfig(device_config=DeviceConfig(device=device))
+    with set_current_vllm_config(vc):
+        if not model_parallel_is_initialized():
+            init_distributed_environment(world_size=1, rank=0, local_rank=0, distributed_init_method="tcp://127.0.0.1:29655",
+                                         backend="gloo" if device == "cpu" else "nccl")
+            initialize_model_parallel(1, 1)
+        build_real_fused_moe.n = getattr(build_real_fused_moe, "n", 0) + 1
+        layer = FusedMoE(num_experts=E, top_k=top_k, hidden_size=H, intermediate_size=I, params_dtype=torch.float16,
+                         renormalize=True, quant_config=cls(operand_mode=operand_mode),
+                         prefix=prefix or f"model.layers.{build_real_fused_moe.n}.mlp.experts", activation="swigluoai",
+                         has_bias=has_bias, apply_router_weight_on_input=apply_router_weight_on_input)
+    return layer, vc
+
+
+def test_real_vllm_fused_moe_accepts_the_method():
+    """vLLM 0.22 constructs FusedMoE with this plugin's quant method (no dummy class): isinstance holds, the parameters are the
+    ones V/model_executor/layers/quantization/bitsandbytes.py:508-575 registers, plus the gpt-oss bias pair."""
+    plug, cls = _vllm_or_skip()
+    from vllm.model_executor.layers.fused_moe.fused_moe_method_base import FusedMoEMethodBase
+    try:
+        layer, _ = build_real_fused_moe(cls)
+    except Exception as exc:
+        pytest.skip(f"vLLM cannot build a FusedMoE on this box: {type(exc).__name__}: {exc}")
+    assert isinstance(layer.quant_method, FusedMoEMethodBase) and isinstance(layer.quant_method, plug.build_method_class())
+    shapes = {n: tuple(p.shape) for n, p in layer.named_parameters()}
+    assert shapes == {"w13_weight": (4, 2 * 64 * 128 // 2, 1), "w2_weight": (4, 128 * 64 // 2, 1), "w13_bias": (4, 128),
+                      "w2_bias": (4, 128)}
+    assert layer.w13_weight.experts_shape == (4, 128, 128) and layer.w13_weight.use_bitsandbytes_4bit
+    assert layer.w13_weight.dtype == torch.uint8 and callable(layer.w13_weight.weight_loader)
+    assert layer.quant_method.get_fused_moe_quant_config(layer) is None
