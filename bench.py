@@ -45,8 +45,15 @@ def parse():
     p.add_argument("--absmax", default="nested", choices=["nested", "flat"])
     p.add_argument("--regime", default="auto", choices=["auto", "gemv", "gemm", "gemm_fast"],
                    help="auto = what the drop-in apply() uses: GEMV up to 8 tokens, decode tcgen05 kernel above")
+    p.add_argument("--ep-backend", default="auto", choices=["auto", "p2p", "nccl"],
+                   help="N>1 exchange: p2p = NVLink peer-memory kernels (drop-free, worst-case capacity), nccl = fixed-capacity "
+                        "all-to-all, auto = p2p when torch symmetric memory can be set up")
     p.add_argument("--ep-capacity-factor", type=float, default=2.0,
-                   help="N>1: rows reserved per peer = factor x mean load (an overflow is detected and fatal); 0 = worst case")
+                   help="N>1, nccl back end only: rows reserved per peer = factor x mean load (an overflow is detected and fatal); "
+                        "0 = worst case.  The p2p back end always uses the worst case (only rows that exist cross the link)")
+    p.add_argument("--no-sweep", action="store_true", help="skip the decode sweep / exact-operand / flat-absmax / T=256 extras")
+    p.add_argument("--shape", default="20b", choices=["20b", "120b"],
+                   help="120b = BASELINE.json configs[4]: 128 experts, 36 layers (expert-parallel runs; decode 256 + prefill 4096 legs)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-prefill", action="store_true", help="skip the extra 8192-token prefill measurement")
     p.add_argument("--prefill-tokens", type=int, default=8192)
@@ -233,6 +240,333 @@ def state_to_cpu(w, e):
             "shape": (w.rows, w.cols), "blocksize": 64}
 
 
+# ------------------------------------------------------------------------------------------------------- expert parallel
+def _graph_of(fn, warm=1):
+    """Capture fn() (kernels + collectives) into a CUDA graph on a side stream; None if capture is not possible."""
+    import torch
+    try:
+        g, side = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            for _ in range(warm):
+                fn()
+            torch.cuda.synchronize()
+            with torch.cuda.graph(g, stream=side):
+                fn()
+        torch.cuda.synchronize()
+        return g
+    except Exception as exc:   # noqa: BLE001
+        print(f"note: CUDA-graph capture failed ({type(exc).__name__}: {exc}); timing eager launches", file=sys.stderr, flush=True)
+        return None
+
+
+def _timed_max_over_ranks(step, K, dev, dist):
+    """K steps between two CUDA events, barrier + synchronize on both sides, MAX over ranks (ms per step)."""
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1) / K], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def run_ep(args, pkg, dev, rank, world, code2):
+    """N > 1: the decode stack with the experts sharded over `world` GPUs (BASELINE.json configs[3] / configs[4]).
+    `value`: --tokens tokens per rank (weak scaling in tokens; each rank streams only its E/world experts).  Beside it:
+    `strong_256` (256 tokens GLOBAL, the configs[3] shape as written), a skewed-routing run, a numerical check of the
+    expert-parallel output against the single-GPU layer on the same weights, and (120b shape) the prefill-4096 leg."""
+    import torch
+    import torch.distributed as dist
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    K_TOP = TOP_K
+    big = args.shape == "120b"
+    E = 128 if big else args.experts
+    L = 36 if big else args.layers
+    T, K, Wm = args.tokens, args.steps, max(3, args.warmup)
+    nested = args.absmax == "nested"
+    plan = ep.EPPlan(rank, world, E)
+    El = plan.experts_per_rank
+    Ts = max(1, 256 // world)                                     # tokens per rank of the 256-global strong-scaling shape
+    Tp = (4096 // world) if big else 0                            # tokens per rank of the configs[4] prefill leg
+    Tmax = max(T, Ts, Tp)
+    cap_factor = (args.ep_capacity_factor or None) if args.ep_backend == "nccl" else None
+    exchange, xnote = ep.make_exchange(plan, K_TOP, H, Tmax, dev, backend=args.ep_backend, capacity_factor=cap_factor)
+    if exchange.kind == "nccl" and args.ep_backend == "auto":
+        cap_factor = args.ep_capacity_factor or None
+        exchange = ep.NcclExchange(plan, plan.capacity(Tmax, K_TOP, cap_factor), H, dev)
+    g = torch.Generator(device=dev).manual_seed(SEED + 17 * rank)
+    gc = torch.Generator(device=dev).manual_seed(SEED)            # common seed: layer 0 is the same full expert set on every rank
+    s = slice(plan.local_experts.start, plan.local_experts.stop)
+    full13 = pkg.NF4ExpertWeights.quantize((torch.randn(E, 2 * I, H, generator=gc, device=dev) * 0.02).half(), code2)
+    full2 = pkg.NF4ExpertWeights.quantize((torch.randn(E, H, I, generator=gc, device=dev) * 0.02).half(), code2)
+    weights = [(ep.shard_experts(full13, plan), ep.shard_experts(full2, plan))]
+    for _ in range(L - 1):
+        weights.append((pkg.NF4ExpertWeights.quantize((torch.randn(El, 2 * I, H, generator=g, device=dev) * 0.02).half(), code2),
+                        pkg.NF4ExpertWeights.quantize((torch.randn(El, H, I, generator=g, device=dev) * 0.02).half(), code2)))
+
+    def make_layers(tokens):
+        return [ep.EPMoELayer(w13, w2, plan, K_TOP, H, tokens, dev, device_ops=ep.CudaEPOps(nested=nested), exchange=exchange)
+                for w13, w2 in weights]
+
+    def inputs(tokens, skew=False, seed=0):
+        gi = torch.Generator(device=dev).manual_seed(SEED + 1000 * seed + rank)
+        x = torch.randn(tokens, H, generator=gi, device=dev).half()
+        lgs = []
+        for _ in range(L):
+            lg = torch.randn(tokens, E, generator=gi, device=dev).float()
+            if skew:   # SURVEY 8(d): logits += 2 * onehot(t mod 4): the first experts (rank 0's) get most of the rows
+                lg[torch.arange(tokens, device=dev), torch.arange(tokens, device=dev) % 4] += 2.0
+            lgs.append(lg.half())
+        return x, lgs
+
+    def timed_stack(tokens, skew=False, seed=0, steps=K):
+        layers = make_layers(tokens)
+        x, lgs = inputs(tokens, skew, seed)
+        outs = [torch.empty(tokens, H, dtype=torch.float16, device=dev) for _ in range(L)]
+
+        def fwd():
+            for l, layer in enumerate(layers):
+                layer.forward(x, router_logits=lgs[l], out=outs[l])
+        fwd()
+        torch.cuda.synchronize()
+        dist.barrier()
+        graph = _graph_of(fwd)
+        flag = torch.tensor([1 if graph is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        step = graph.replay if int(flag.item()) else fwd
+        for _ in range(Wm):
+            step()
+        ms = _timed_max_over_ranks(step, steps, dev, dist)
+        for layer in layers:
+            layer.check_overflow()
+        return ms, layers, x, lgs, outs, bool(int(flag.item()))
+
+    # ---- numerical check first: EP output of layer 0 == the single-GPU layer on the same full weights, this rank's tokens ----
+    chk_layers = make_layers(T)
+    cx, clg = inputs(T, False, 7)
+    ep_out = chk_layers[0].forward(cx, router_logits=clg[0])
+    single = pkg.ops.moe_forward(cx, full13, full2, K_TOP, router_logits=clg[0], nested=nested,
+                                 regime=chk_layers[0].regime_resolved)
+    torch.cuda.synchronize()
+    same = torch.tensor([1 if torch.equal(ep_out, single) else 0], device=dev)
+    maxdiff = (ep_out.float() - single.float()).abs().max().reshape(1)
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    dist.all_reduce(maxdiff, op=dist.ReduceOp.MAX)
+    ep_matches, ep_maxdiff = bool(int(same.item())), float(maxdiff.item())
+    del chk_layers
+    if world > 1:
+        del full13, full2   # layer 0's shards are views of them; the views keep the storage alive
+
+    # ---- value: T tokens per rank ----
+    sampler = ClockSampler(dev.index or 0)
+    sampler.start()
+    time.sleep(0.25)
+    t0 = time.time()
+    ms_per_step, layers, x, lgs, outs, graphed_ok = timed_stack(T)
+    clocks = sampler.stop(t0, time.time())
+
+    # ---- e2e: host buffers, H2D of x + logits and D2H of the output inside the timed region ----
+    hx = x.cpu().pin_memory()
+    hlg = torch.stack([l.cpu() for l in lgs]).pin_memory()
+    hout = torch.empty(T, H, dtype=torch.float16).pin_memory()
+
+    def stack_apply(dx, dlg):
+        o = None
+        for l, layer in enumerate(layers):
+            o = layer.forward(dx, router_logits=dlg[l])
+        return o
+
+    e2e_api = "EPMoELayer.forward(x, router_logits) x layers launched eagerly, pinned host buffers, per rank"
+    if graphed_ok:
+        graphed = pkg.GraphedForward(stack_apply, [x, torch.stack(lgs)])
+        step_e2e = lambda: graphed(hx, hlg, out=hout)
+        e2e_api = ("GraphedForward(EPMoELayer.forward(x, router_logits) x layers)(host x, host logits) -> host out per rank: pinned H2D, "
+                   "one CUDA-graph replay (exchange inside), D2H, stream sync; host wall clock, max over ranks")
+    else:
+        def step_e2e():
+            o = stack_apply(hx.to(dev, non_blocking=True), hlg.to(dev, non_blocking=True))
+            hout.copy_(o, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+    for _ in range(Wm):
+        step_e2e()
+    torch.cuda.synchronize()
+    dist.barrier()
+    tw = time.perf_counter()
+    for _ in range(K):
+        step_e2e()
+    ms3 = torch.tensor([(time.perf_counter() - tw) * 1e3 / K], device=dev, dtype=torch.float64)
+    dist.all_reduce(ms3, op=dist.ReduceOp.MAX)
+    e2e_ms = float(ms3.item())
+
+    # ---- per-rank compute-only time of the expert kernels (roofline of this rank's weight stream) ----
+    def compute_all():
+        for layer in layers:
+            layer.compute()
+    cg = _graph_of(compute_all)
+    tk = []
+    for rep in range(4):
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        (cg.replay if cg is not None else compute_all)()
+        a1.record()
+        torch.cuda.synchronize()
+        if rep:
+            tk.append(a0.elapsed_time(a1) / L)
+    peak, peak_src = measured_peaks()
+    wbytes = El * (weights[1][0].nbytes(nested) + weights[1][1].nbytes(nested))
+    d = statistics.mean(tk) * 1e-3
+
+    # ---- beside it: the 256-global strong-scaling shape, skewed routing, (120b) the prefill leg ----
+    extras = {}
+    if not args.no_sweep:
+        ms_s, *_ = timed_stack(Ts, False, 11, steps=max(5, K // 2))
+        extras["strong_256"] = {"global_tokens": Ts * world, "tokens_per_rank": Ts, "ms_per_step": ms_s, "per_layer_us": ms_s * 1e3 / L,
+                                "tokens_per_s": Ts * world / (ms_s * 1e-3),
+                                "note": "BASELINE.json configs[3] as written: 256 tokens GLOBAL over N GPUs; the N=1 anchor is `strong_256` of "
+                                        "the N=1 line (efficiency = this / (N x anchor) is the driver's to compute)"}
+        ms_k, *_ = timed_stack(T, True, 13, steps=max(5, K // 2))
+        extras["skewed_routing"] = {"tokens_per_rank": T, "ms_per_step": ms_k, "per_layer_us": ms_k * 1e3 / L, "tokens_per_s": T * world / (ms_k * 1e-3),
+                                    "routing": "logits += 2 * onehot(t mod 4) (SURVEY 8(d)): rank 0's experts take most rows",
+                                    "dropped_pairs": 0 if exchange.kind == "p2p" else "checked after the run (overflow would have raised)"}
+        if big:
+            ms_p, *_ = timed_stack(Tp, False, 17, steps=3)
+            flops = 2.0 * Tp * world * K_TOP * (2 * I * H + H * I) * L
+            extras["prefill_4096"] = {"global_tokens": Tp * world, "tokens_per_rank": Tp, "ms_per_step": ms_p, "per_layer_us": ms_p * 1e3 / L,
+                                      "tokens_per_s": Tp * world / (ms_p * 1e-3), "tflops_all_ranks": flops / (ms_p * 1e-3) / 1e12,
+                                      "tensor_frac_of_nominal_per_gpu": flops / (ms_p * 1e-3) / 1e12 / world / 2250.0}
+    wire = layers[0].wire_bytes()
+    if rank == 0:
+        T_all = T * world
+        shape_name = "gpt-oss-120b-shape" if big else "gpt-oss-20b"
+        line = {"metric": METRIC, "value": T_all / (ms_per_step * 1e-3), "unit": "tokens/s", "n_gpus": world, "steps": K,
+                "warmup": Wm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "nf4 weights -> f16 mma operands, f32 accumulate, f16 activations",
+                "data": "synthetic (seeded N(0,0.02^2) weights quantised on device, N(0,1) tokens and logits)",
+                "config": {"workload": f"{shape_name} {L}-layer NF4 MoE stack decode, {T} tokens per rank ({T_all} global), "
+                                       f"{E} experts expert-parallel over {world} GPUs ({El} per GPU), dispatch/combine over {xnote} "
+                                       f"(BASELINE.json configs[{4 if big else 3}] shape)", "hidden": H, "intermediate": I, "experts": E,
+                           "top_k": K_TOP, "layers": L, "tokens_per_rank": T, "absmax": args.absmax, "parallelism": f"ep{world}",
+                           "exchange": exchange.kind, "exchange_note": xnote,
+                           "regime": {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "gemm_exact",
+                                      pkg.REGIME_GEMM_FAST: "gemm_fast (decode tcgen05 kernel)"}.get(layers[0].regime_resolved, "auto"),
+                           "capacity_rows_per_peer": layers[0].cap,
+                           "capacity": ("worst case (T*k rows per peer): nothing can be dropped" if cap_factor is None else
+                                        f"{cap_factor} x mean load per peer, overflow checked after the run (none)"),
+                           "cuda_graph": graphed_ok,
+                           "l2": f"{wbytes * L / 1e9:.2f} GB of weights streamed per rank per step >> 126 MB L2",
+                           "per_layer_us": ms_per_step * 1e3 / L},
+                "clocks": clocks,
+                "ep_matches_single_gpu": ep_matches, "ep_vs_single_gpu_max_abs_diff": ep_maxdiff,
+                "e2e": {"value": T_all / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2 + hlg.numel() * 2,
+                        "d2h_bytes_per_step": hout.numel() * 2, "ms_per_step": e2e_ms, "api": e2e_api},
+                "gpu_launches": (pkg.ops.last_launch_count() + (7 if exchange.kind == "p2p" else 5)) * L * K,
+                "collectives_per_layer": exchange.collectives_per_layer, "wire_bytes_per_rank_per_layer": wire,
+                "roofline": {"bound": "hbm", "kernel": "expert_rows chain (bucket + permute + w13 + w2) on this rank's experts",
+                             "achieved": wbytes / d / 1e9, "peak": peak, "unit": "GB/s", "frac": wbytes / d / 1e9 / peak,
+                             "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": wbytes,
+                             "avg_launch_us": d * 1e6}}
+        line.update(extras)
+        print(json.dumps(line), flush=True)
+    # Leave without NCCL teardown: destroying a communicator that a live CUDA graph captured can block forever, and a
+    # benchmark process has nothing left to release.  Every rank has finished its collectives at this point.
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
+def stack_and_kernel_times(pkg, dev, stack, T, E, regime, nested, seed, reps=6):
+    """One configuration beside the headline: the whole 24-layer stack (CUDA-graph replay, CUDA events) and the w13 / w2 kernels
+    alone (one graph each, all layers back to back), for T tokens in `regime` with the given absmax form."""
+    import torch
+    L = len(stack)
+    g = torch.Generator(device=dev).manual_seed(SEED + seed)
+    x = torch.randn(T, H, generator=g, device=dev).half()
+    logits = [torch.randn(T, E, generator=g, device=dev).half() for _ in range(L)]
+    outs = [torch.empty(T, H, dtype=torch.float16, device=dev) for _ in range(L)]
+    ws = pkg.ops.new_workspace(dev, T, E, H, I, TOP_K)
+    eff = pkg.ops.auto_regime(T, TOP_K, E) if regime == pkg.REGIME_AUTO else regime
+    use_tc = eff != pkg.REGIME_GEMV
+
+    def fwd():
+        for l, (w13, w2) in enumerate(stack):
+            pkg.ops.moe_forward(x, w13, w2, TOP_K, router_logits=logits[l], out=outs[l], workspace=ws, nested=nested, regime=regime)
+    graph = _graph_of(fwd)
+    prep = []
+    for l in range(L):
+        ids, _ = pkg.ops.route_topk(logits[l], TOP_K)
+        b = pkg.ops.bucket(ids, E, want_tiles=use_tc)
+        prep.append((b, pkg.ops.permute_rows(x, b, TOP_K) if use_tc else x))
+    eact = sum(int(b["meta"][0].item()) for b, _ in prep) / L
+    hs = []
+
+    def run13():
+        hs.clear()
+        hs.extend(pkg.ops.expert_w13(xin, w13, b, T, TOP_K, nested=nested, regime=eff) for (w13, _), (b, xin) in zip(stack, prep))
+
+    def run2():
+        for hbuf, (_, w2), (b, _) in zip(hs, stack, prep):
+            pkg.ops.expert_w2(hbuf, w2, b, T, TOP_K, nested=nested, regime=eff)
+    side = torch.cuda.Stream()
+    run13(); run2(); torch.cuda.synchronize()
+    g13, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g13, stream=side):
+            run13()
+        with torch.cuda.graph(g2, stream=side):
+            run2()
+    torch.cuda.synchronize()
+    ts, t13, t2 = [], [], []
+    for rep in range(reps + 2):
+        a = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        a[0].record(); graph.replay(); a[1].record(); g13.replay(); a[2].record(); g2.replay(); a[3].record()
+        torch.cuda.synchronize()
+        if rep >= 2:
+            ts.append(a[0].elapsed_time(a[1])); t13.append(a[1].elapsed_time(a[2]) / L); t2.append(a[2].elapsed_time(a[3]) / L)
+    pkg.ops.check_status(ws)
+    peak, _ = measured_peaks()
+    ms = statistics.mean(ts)
+    b13 = eact * stack[0][0].nbytes(nested) + T * H * 2 + T * TOP_K * I * 2
+    b2 = eact * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2
+    d13, d2 = statistics.mean(t13) * 1e-3, statistics.mean(t2) * 1e-3
+    name = {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "tcgen05 exact operand", pkg.REGIME_GEMM_FAST: "tcgen05 fast operand"}[eff]
+    return {"tokens": T, "regime": name, "absmax": "nested" if nested else "flat", "experts_active_mean": eact,
+            "ms_per_step": ms, "per_layer_us": ms * 1e3 / L, "tokens_per_s": T / (ms * 1e-3),
+            "w13_us": d13 * 1e6, "w13_gbs": b13 / d13 / 1e9, "w13_frac": b13 / d13 / 1e9 / peak,
+            "w2_us": d2 * 1e6, "w2_gbs": b2 / d2 / 1e9, "w2_frac": b2 / d2 / 1e9 / peak,
+            "whole_step_frac": (b13 + b2) * L / (ms * 1e-3) / 1e9 / peak}
+
+
+def oracle_check_of_benched_output(pkg, stack, x, logits0, out0, nested, sample=8):
+    """The output the timed step produced for layer 0, compared with the CPU oracle on `sample` tokens (checker only; outside
+    every timed region).  Returns (max_abs, rel_l2, ok)."""
+    import numpy as np
+    import torch
+    from oracle import nf4_oracle as orc
+    w13, w2 = stack[0]
+    T = x.shape[0]
+    pick = np.unique(np.linspace(0, T - 1, sample).astype(np.int64))
+    lg = logits0[pick].cpu().numpy()
+    ids, _ = orc.route_topk(lg, TOP_K)
+    E = w13.num_experts
+    d13 = np.zeros((E, w13.rows, w13.cols), np.float16)
+    d2 = np.zeros((E, w2.rows, w2.cols), np.float16)
+    for e in np.unique(ids):
+        d13[e], d2[e] = orc.dequant_state(state_to_cpu(w13, int(e))), orc.dequant_state(state_to_cpu(w2, int(e)))
+    ref = orc.moe_forward_ref(x[pick].cpu().numpy(), lg, d13, d2, k=TOP_K).astype(np.float32)
+    got = out0[pick].float().cpu().numpy()
+    max_abs = float(np.abs(got - ref).max())
+    rel = float(np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-12))
+    return max_abs, rel, bool(max_abs <= 1e-2 and rel <= 2e-3)
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -257,8 +591,7 @@ def run_ours(args):
     nested = args.absmax == "nested"
     code2 = torch.from_numpy(orc.create_dynamic_map())
     if world > 1:
-        ep = importlib.import_module("gpt-oss-vllm_b200.ep")
-        return ep.bench_ep(args, pkg, dev, rank, world, code2, ClockSampler, measured_peaks, METRIC)
+        return run_ep(args, pkg, dev, rank, world, code2)
 
     regime = {"auto": pkg.REGIME_AUTO, "gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "gemm_fast": pkg.REGIME_GEMM_FAST}[args.regime]
     eff = pkg.ops.auto_regime(T, TOP_K, E) if regime == pkg.REGIME_AUTO else regime     # what AUTO resolves to
@@ -437,6 +770,19 @@ def run_ours(args):
             "gpu_launches": launches_per_layer * L * K, "launches_per_layer": launches_per_layer,
             "roofline": roof, "step_ms_min_max": [min(step_ms), max(step_ms)]}
 
+    mx, rel, ok = oracle_check_of_benched_output(pkg, stack, x, logits[0], outs[0], nested)
+    line["parity_of_benched_output"] = {"layer": 0, "tokens_checked": 8, "max_abs": mx, "rel_l2": rel, "within_1e-2_2e-3": ok,
+                                        "checker": "oracle (numpy) on the routed experts, outside the timed region"}
+    pkg.ops.check_status()
+    if not args.no_sweep:
+        # configs[1] says batch 1-64: the whole range in the driver-visible line (regime = what apply() uses at each T)
+        line["decode_sweep"] = [stack_and_kernel_times(pkg, dev, stack, t, E, pkg.REGIME_AUTO, nested, 100 + t) for t in (1, 2, 4, 8, 16, 32, 64)]
+        # the bit-exact-dequant operand through the same decode-regime kernel (north_star: "a bit-exact-dequant NF4 MoE layer")
+        line["exact_operand_decode"] = stack_and_kernel_times(pkg, dev, stack, T, E, pkg.REGIME_GEMM, nested, 201)
+        # the vLLM-bound layout (flat fp32 absmax, SURVEY 8(d) "A = 1,555,200"): same kernels, more algorithmic bytes per expert
+        line["flat_absmax_decode"] = stack_and_kernel_times(pkg, dev, stack, T, E, regime, False, 202)
+        # the 1-GPU anchor of BASELINE.json configs[3] (256 tokens global)
+        line["strong_256"] = stack_and_kernel_times(pkg, dev, stack, 256, E, regime, nested, 203)
     if not args.no_prefill:
         line["prefill"] = prefill_section(pkg, dev, stack[0], E, nested)
 

@@ -24,8 +24,9 @@ EXPORTED = (
     "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
     "nf4moe_last_launch_count", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
     "nf4moe_workspace_status_offset", "nf4moe_expert_rows_bias", "nf4moe_combine_indexed_bias",
+    "nf4moe_ep_dispatch_p2p", "nf4moe_ep_return_p2p", "nf4moe_ep_wait",
 )
-STATUS_EP_OVERFLOW, STATUS_DEC_NOFIT, STATUS_GEMM_NOFIT = 1, 2, 4
+STATUS_EP_OVERFLOW, STATUS_DEC_NOFIT, STATUS_GEMM_NOFIT, STATUS_EP_TIMEOUT = 1, 2, 4, 8
 
 
 class Nf4MoeError(RuntimeError):
@@ -77,8 +78,11 @@ def _declare(lib):
     lib.nf4moe_ep_pack.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp]
     lib.nf4moe_expert_rows.argtypes = [vp, vp, qp, qp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
     lib.nf4moe_combine_indexed.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
-    lib.nf4moe_expert_rows_bias.argtypes = [vp, vp, qp, qp, vp, vp, i32, i32, i32, i32, i32, i32, vp, sz, vp]
+    lib.nf4moe_expert_rows_bias.argtypes = [vp, vp, qp, qp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, sz, vp]
     lib.nf4moe_combine_indexed_bias.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
+    lib.nf4moe_ep_dispatch_p2p.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
+    lib.nf4moe_ep_return_p2p.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, vp, vp]
+    lib.nf4moe_ep_wait.argtypes = [vp, i32, vp, vp, vp]
     for name in EXPORTED:
         fn = getattr(lib, name)
         if name not in ("nf4moe_version", "nf4moe_auto_regime", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_last_launch_count",

@@ -84,4 +84,146 @@ __global__ void __launch_bounds__(256) combine_indexed_kernel(const __half* __re
   }
 }
 
+
+// =====================================================================================================================
+// Peer-memory exchange (NVLink / NVSwitch, no NCCL on the data path).
+//
+// Every rank owns, in memory its peers can address (torch symmetric memory; any peer-mapped allocation works):
+//   recv_rows fp16 [W, cap, H]   chunk q = the rows rank q routed to this rank's experts      (written by q's dispatch kernel)
+//   recv_ids  int32 [W, cap]     local expert id per row, -1 = unused slot                     (written by q's dispatch kernel)
+//   back_rows fp16 [W, cap, H]   chunk p = expert outputs of the rows this rank sent to rank p (written by p's return kernel)
+//   flags     u64  [2, W]        [0][q] = epoch of q's last completed dispatch to this rank, [1][p] = ... of p's last return
+// and a private counter block ctr u32 [8] (tickets and epochs).  The dispatch kernel stores rows straight from x into the
+// OWNER's recv_rows over NVLink (only rows that exist travel, so the worst-case capacity cap = T*k costs nothing on the wire
+// and no pair is ever dropped -- round 1's fixed-capacity NCCL all-to-all moved W*cap rows each way and had to trade drops
+// against bytes), then the LAST CTA to finish publishes the epoch to every peer (release at system scope).  The consumer
+// side is a one-warp kernel that spins (acquire at system scope) until all W flags carry its own epoch; epochs live in
+// device memory and advance once per launch, so the whole layer replays from a CUDA graph, in lock step on every rank.
+// Buffer reuse needs no extra handshake: a rank starts the next layer's dispatch only after its combine, which waited for
+// every owner's return, which every owner issued after its expert kernels had consumed the rows of this layer.
+// =====================================================================================================================
+constexpr int kEpMaxWorld = 16;
+struct EpPeers {
+  __half* rows[kEpMaxWorld];              // peer p's recv_rows (dispatch) or back_rows (return)
+  int32_t* ids[kEpMaxWorld];              // peer p's recv_ids (dispatch only)
+  unsigned long long* flags[kEpMaxWorld]; // peer p's flag row to write into (this rank's entry is [rank])
+};
+
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Last-CTA-done: every CTA fences its (peer) stores at system scope and takes a ticket; the CTA that draws the last one
+// bumps the epoch and publishes it to all peers.  ctr[0] = ticket, ctr[1] = epoch (reset / advanced here).
+__device__ __forceinline__ void ep_publish_epoch(unsigned int* ctr, const EpPeers& peers, int world, int rank) {
+  __shared__ unsigned int s_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    s_last = atomicAdd(ctr, 1u) == gridDim.x - 1 ? 1u : 0u;
+  }
+  __syncthreads();
+  if (s_last) {
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      ctr[0] = 0u;
+      ctr[1] += 1u;
+    }
+    __syncthreads();
+    const unsigned long long epoch = ctr[1];
+    if ((int)threadIdx.x < world) st_release_sys_u64(peers.flags[threadIdx.x] + rank, epoch);
+  }
+}
+
+// Dispatch: slot (p, j) of this rank's pair list (sorted by global expert id, so grouped by owner) -> owner p's chunk `rank`.
+__global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* __restrict__ x, const int32_t* __restrict__ ids,
+                                                          const int32_t* __restrict__ expert_offsets,
+                                                          const int32_t* __restrict__ sorted_pairs, int k, int H, int world, int rank,
+                                                          int e_local, int cap, const EpPeers peers, int32_t* __restrict__ pair_slot,
+                                                          unsigned int* __restrict__ ctr, int32_t* __restrict__ status) {
+  grid_dep_launch();
+  grid_dep_wait();
+  const int lane = threadIdx.x & 31;
+  const int n_slots = world * cap;
+  const int vec = H / 8;
+  for (int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; slot < n_slots; slot += (gridDim.x * blockDim.x) >> 5) {
+    const int p = slot / cap, j = slot - p * cap;
+    const int start = expert_offsets[p * e_local];
+    const int cnt = expert_offsets[(p + 1) * e_local] - start;
+    if (j == 0 && lane == 0 && cnt > cap) atomicOr(status, 1);
+    const long long dst_slot = (long long)rank * cap + j;
+    if (j < cnt) {
+      const int pair = sorted_pairs[start + j];
+      const uint4* src = reinterpret_cast<const uint4*>(x + (long long)(pair / k) * H);
+      uint4* dst = reinterpret_cast<uint4*>(peers.rows[p] + dst_slot * H);
+      for (int i0 = 0; i0 < vec; i0 += 128) {     // 4 chunks per lane in flight
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) v[u] = __ldg(src + i); }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) dst[i] = v[u]; }
+      }
+      if (lane == 0) {
+        peers.ids[p][dst_slot] = ids[pair] - p * e_local;
+        pair_slot[pair] = slot;
+      }
+    } else if (lane == 0) {
+      peers.ids[p][dst_slot] = -1;
+    }
+  }
+  ep_publish_epoch(ctr, peers, world, rank);
+}
+
+// Return: row (q, j) of this rank's expert outputs (valid where recv_ids >= 0) -> home rank q's back_rows chunk `rank`.
+__global__ void __launch_bounds__(256) ep_return_kernel(const __half* __restrict__ y_rows, const int32_t* __restrict__ recv_ids, int H,
+                                                        int world, int rank, int cap, const EpPeers peers,
+                                                        unsigned int* __restrict__ ctr) {
+  grid_dep_launch();
+  grid_dep_wait();
+  const int lane = threadIdx.x & 31;
+  const int n_slots = world * cap;
+  const int vec = H / 8;
+  for (int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; slot < n_slots; slot += (gridDim.x * blockDim.x) >> 5) {
+    if (recv_ids[slot] < 0) continue;
+    const int q = slot / cap, j = slot - q * cap;
+    const uint4* src = reinterpret_cast<const uint4*>(y_rows + (long long)slot * H);
+    uint4* dst = reinterpret_cast<uint4*>(peers.rows[q] + ((long long)rank * cap + j) * H);
+    for (int i0 = 0; i0 < vec; i0 += 128) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) v[u] = __ldg(src + i); }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) dst[i] = v[u]; }
+    }
+  }
+  ep_publish_epoch(ctr, peers, world, rank);
+}
+
+// One warp: advance this rank's wait epoch (ctr[0]) and spin until every peer's flag has reached it.  A peer that never
+// arrives (a crashed rank) raises NF4MOE_STATUS_EP_TIMEOUT after 2^27 polls (about half a minute) instead of hanging the GPU for ever.
+__global__ void __launch_bounds__(32) ep_wait_kernel(const unsigned long long* __restrict__ flags, int world, unsigned int* __restrict__ ctr,
+                                                     int32_t* __restrict__ status) {
+  grid_dep_launch();
+  grid_dep_wait();
+  const int lane = threadIdx.x;
+  unsigned int epoch = 0;
+  if (lane == 0) { epoch = ctr[0] + 1u; ctr[0] = epoch; }
+  epoch = __shfl_sync(0xffffffffu, epoch, 0);
+  bool ok = true;
+  if (lane < world) {
+    unsigned long long spins = 0;
+    while (ld_acquire_sys_u64(flags + lane) < (unsigned long long)epoch) {
+      if (++spins > (1ull << 27)) { ok = false; break; }   // ~half a minute: a peer died or never launched
+      __nanosleep(64);
+    }
+  }
+  if (!ok) atomicOr(status, 8);
+  __threadfence_system();
+}
+
 }  // namespace nf4moe

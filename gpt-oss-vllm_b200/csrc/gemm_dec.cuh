@@ -48,9 +48,18 @@ constexpr int kDecSlots = 3;                               // A-operand slots in
 constexpr int kDecAccCols = 32;                            // per accumulator (two of them)
 constexpr uint32_t kDecRawBytes = 128 * 128;               // raw NF4 of one stage: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kDecSmemBytes = 232448 - 1024;
-// registers per thread after setmaxnreg (the launch bound gives every warp 65536 / kDecThreads, rounded down to 8)
-constexpr int kDecRegsDq = kDecDqWarps <= 8 ? 160 : kDecDqWarps <= 12 ? 120 : kDecDqWarps <= 16 ? 96 : kDecDqWarps <= 20 ? 72 : 64;
+// Registers per thread.  The CTA is launched with kDecRegsLaunch per thread (what __launch_bounds__(kDecThreads, 1) lets ptxas
+// use, and with setmaxnreg in the kernel it takes all of it); setmaxnreg then moves registers from the control warpgroup to
+// the dequant warps.  The pool is what the CTA was LAUNCHED with -- an increase beyond what the decreases released blocks
+// forever -- so the dequant figure is derived from the budget, and dec_launch() checks the budget against the kernel's
+// real register count (cudaFuncGetAttributes) before the first launch instead of trusting this arithmetic.
+constexpr int kDecRegsLaunch = (65536 / kDecThreads) / 8 * 8 > 255 ? 248 : (65536 / kDecThreads) / 8 * 8;
 constexpr int kDecRegsCtl = 40;
+constexpr int kDecRegsDqBudget = (kDecRegsLaunch * kDecThreads - 128 * kDecRegsLaunch - 128 * kDecRegsCtl) / (32 * kDecDqWarps) / 8 * 8;
+constexpr int kDecRegsDq = kDecRegsDqBudget > 232 ? 232 : kDecRegsDqBudget;
+static_assert(kDecRegsDq >= kDecRegsLaunch, "the dequant warps never give registers away");
+static_assert(32 * kDecDqWarps * kDecRegsDq + 128 * kDecRegsLaunch + 128 * kDecRegsCtl <= kDecRegsLaunch * kDecThreads,
+              "setmaxnreg budget: increases must fit in what the decreases release");
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
   asm volatile(
@@ -234,7 +243,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 
   if (warp < kDecDqWarps) {
     // =============================== dequant: NF4 -> fp16 A operand in TMEM ===============================
-    set_max_regs_inc<kDecRegsDq>();
+    if constexpr (kDecRegsDq > kDecRegsLaunch) set_max_regs_inc<kDecRegsDq>();
     const int q = warp & 3, hh = (warp >> 2) % kDecSplit, pp = (warp >> 2) / kDecSplit;   // pp = dequant group
     const int r = q * 32 + lane;
     const uint32_t lut_lane = pin(lut | ((uint32_t)lane << (FAST ? 2 : 3)));
@@ -605,6 +614,20 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
                  !make_map_2d(&map_x32, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32)))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
   cudaError_t e;
+  {   // once per kernel: the register pool the CTA is launched with must cover the setmaxnreg plan (else the kernel would hang)
+    static std::atomic<int> regs_ok[2] = {{0}, {0}};
+    int ok = regs_ok[fast].load(std::memory_order_acquire);
+    if (ok == 0) {
+      cudaFuncAttributes fa;
+      e = fast ? cudaFuncGetAttributes(&fa, dec_kernel<W13, true, false>) : cudaFuncGetAttributes(&fa, dec_kernel<W13, false, false>);
+      if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncGetAttributes: %s", name, cudaGetErrorString(e)); return (int)e; }
+      const int launched = (fa.numRegs + 7) / 8 * 8;
+      ok = (32 * kDecDqWarps * std::max(kDecRegsDq, launched) + 128 * launched + 128 * std::min(kDecRegsCtl, launched) <= launched * kDecThreads &&
+            launched <= kDecRegsDq) ? 1 : -1;
+      regs_ok[fast].store(ok, std::memory_order_release);
+    }
+    if (ok < 0) return fail(NF4MOE_EINVAL, "register plan of the decode kernel does not fit the registers it is launched with (build problem)");
+  }
 #ifdef NF4MOE_EXPERIMENTS
   if (W13 && fast && a.dbg != nullptr) {   // the cycle-counter build exists for FAST w13 only (scripts/dec_roles.py)
     e = ensure_dyn_smem<dec_kernel<W13, true, W13>>((int)kDecSmemBytes);

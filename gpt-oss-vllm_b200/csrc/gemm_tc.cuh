@@ -38,6 +38,16 @@ namespace nf4moe {
 constexpr int kDecMaxMeanRows = 40;     // mean routed rows per expert up to which token tiles are 32 rows (decode tcgen05 kernel)
 constexpr int kDecAutoMinTokens = 8;    // tokens; up to this nf4moe_moe_forward(AUTO) uses the GEMV, above it a tcgen05 kernel
 constexpr int kDqGroups = 3;            // dequant warpgroups; k-block c of a CTA belongs to group c % 3
+#ifndef NF4MOE_GEMM_CLUSTER
+#define NF4MOE_GEMM_CLUSTER 1
+#endif
+// CTAs per thread-block cluster of the prefill kernel.  The CTAs of a cluster work on neighbouring 128-row weight tiles of the
+// SAME token tile, so they all need the same activation tile: each loads 1/C of its rows and TMA-multicasts them into every
+// CTA's shared memory.  At M = 128 x N = 160 a lone CTA pulls 24 KB per k-block from L2 (20 KB of it activations): 9 TB/s over
+// the chip, the L2 -> SM fabric's ceiling, with the tensor pipe idle half the time (round 1: 46 % active); sharing the tile
+// across C CTAs divides the activation traffic by C.
+constexpr int kGemmCluster = NF4MOE_GEMM_CLUSTER;
+static_assert(kGemmCluster == 1 || kGemmCluster == 2 || kGemmCluster == 4, "NF4MOE_GEMM_CLUSTER must be 1, 2 or 4");
 constexpr int kGemmThreads = (4 + 4 * kDqGroups + 4) * 32;   // 640: control WG, 3 dequant WGs, epilogue WG
 constexpr int kGemmTokTile = 160;       // largest MMA N: two accumulators of 160 columns leave 192 TMEM columns = 3 slots of 2 k-blocks
 constexpr int kGemmRowTile = 128;       // MMA M
@@ -73,6 +83,26 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
       ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
+}
+// The same load delivered to every CTA of `mask` (same shared-memory offset, same mbarrier offset in each of them).
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar), "h"(mask)
+      : "memory");
+}
+// tcgen05.commit that arrives on the mbarrier at this offset in EVERY CTA of `mask`
+__device__ __forceinline__ void tc_commit_mc(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 // One lane of a CONVERGED warp.  The single-thread roles run their loops warp-uniformly and predicate only the
 // tcgen05 / TMA instruction on this: operands then stay in uniform registers (a `lane == 0` branch makes ptxas emit an
@@ -264,6 +294,8 @@ template <bool W13, bool FAST>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a, const __grid_constant__ CUtensorMap map_w,
                                                               const __grid_constant__ CUtensorMap map_x,
                                                               const __grid_constant__ CUtensorMap map_xw) {
+  // map_x: 32-row activation boxes (ragged tiles); map_xw: boxes of tile_tokens / kGemmCluster rows (this CTA's share of a
+  // whole tile)
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumGemmBars];
   __shared__ uint32_t s_tmem;
@@ -298,7 +330,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   if (tid == 0) {
     gemm_plan(base, lut, kGemmSmemBytes, nkb, nested, a.tile_tokens, a.kps, n_a, a.want_b, &s_plan);
     for (int i = 0; i < kMaxWStages; ++i) { mbar_init(bar(kBarWFull + i), 1); mbar_init(bar(kBarWEmpty + i), 4 * kDqGroups); }
-    for (int i = 0; i < kMaxAStages; ++i) { mbar_init(bar(kBarFull + i), 4 * a.kps + 1); mbar_init(bar(kBarEmpty + i), 1); }
+    for (int i = 0; i < kMaxAStages; ++i) { mbar_init(bar(kBarFull + i), 4 * a.kps + 1); mbar_init(bar(kBarEmpty + i), kGemmCluster); }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kBarDFull + i), 1); mbar_init(bar(kBarDEmpty + i), 4);
       mbar_init(bar(kBarMFull + i), 1); mbar_init(bar(kBarMEmpty + i), 4 * kDqGroups);
@@ -324,6 +356,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   grid_dep_wait();
   tc_fence_before();
   __syncthreads();
+  if (kGemmCluster > 1) cluster_sync_all();   // every CTA's barriers exist before a peer multicasts into them
   tc_fence_after();
   const uint32_t tmem = s_tmem;
   const int n_bst = s_plan.n_b, n_wst = s_plan.n_w;
@@ -331,8 +364,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
 
   const bool dbg_on = a.dbg != nullptr && blockIdx.x == 0 && lane == 0;
   long long dbg_acc[6] = {0, 0, 0, 0, 0, 0};
+  // Work items.  A CLUSTER walks (token tile, group of kGemmCluster neighbouring row tiles); CTA `cr` of the cluster takes row
+  // tile rtg * C + cr.  When the row tiles do not divide by C the last group's surplus CTAs redo the last real row tile (they
+  // must keep loading their share of the activations and committing) and store nothing.
   const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
-  const int n_items = n_bst > 0 ? a.meta[2] * n_row_tiles : 0;   // (n_bst == 0: K too large for the stage budget: status bit 2)
+  const int n_rtg = (n_row_tiles + kGemmCluster - 1) / kGemmCluster;
+  const int cr = kGemmCluster > 1 ? (int)cluster_ctarank() : 0;
+  const int item0 = (int)blockIdx.x / kGemmCluster, item_step = (int)gridDim.x / kGemmCluster;
+  const int n_items = n_bst > 0 ? a.meta[2] * n_rtg : 0;   // (n_bst == 0: K too large for the stage budget: status bit 2)
+  auto item_tile = [&](int item, int& tile, int& rt) -> bool {   // returns false for a surplus (store-nothing) CTA
+    tile = item / n_rtg;
+    const int raw = (item - tile * n_rtg) * kGemmCluster + cr;
+    rt = min(raw, n_row_tiles - 1);
+    return raw < n_row_tiles;
+  };
+  constexpr uint16_t kMcMask = (uint16_t)((1u << kGemmCluster) - 1u);
 
   if (warp < 4) {
     set_max_regs_dec<48>();
@@ -346,11 +392,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       const uint32_t slot_bytes = (uint32_t)kps * b_bytes, ring_end = b_ring + (uint32_t)n_bst * b_bytes;
       uint32_t full_a = full0, empty_a = empty0, dst = b_ring, pe = 0;
       int cs = 0;                                         // slots issued so far
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int tile = item / n_row_tiles;
+      const int share = a.tile_tokens / kGemmCluster;      // rows of a whole tile this CTA loads (for every CTA of the cluster)
+      for (int item = item0; item < n_items; item += item_step) {
+        const int tile = item / n_rtg;
         const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
-        const bool whole = n_tok == a.tile_tokens;   // a full tile is one box; a ragged one only the 32-row boxes it really has
+        const bool whole = n_tok == a.tile_tokens;   // a full tile is one box per CTA; a ragged one only the 32-row boxes it really has
         const int n_box = (n_tok + kGemmBoxRows - 1) / kGemmBoxRows;
+        // bytes that LAND in this CTA's stage, whoever loads them
         const uint32_t kb_bytes = whole ? b_bytes : (uint32_t)n_box * (kGemmBoxRows * 128u);
         for (int kb0 = 0; kb0 < nkb; kb0 += kps, ++cs) {
           if (cs >= lead) {                          // the MMAs that read these B stages (slot cs - lead) are done
@@ -362,12 +410,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           if (elect_one()) {
             mbar_expect_tx(full_a, (uint32_t)nreal * kb_bytes);
             for (int u = 0; u < nreal; ++u) {
-              if (whole) {
-                tma_load_2d(dst + (uint32_t)u * b_bytes, &map_xw, (kb0 + u) * kBlock, row0, full_a);
-              } else {
-                for (int bx = 0; bx < n_box; ++bx)
-                  tma_load_2d(dst + (uint32_t)u * b_bytes + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, (kb0 + u) * kBlock,
-                              row0 + bx * kGemmBoxRows, full_a);
+              if (kGemmCluster == 1) {
+                if (whole) {
+                  tma_load_2d(dst + (uint32_t)u * b_bytes, &map_xw, (kb0 + u) * kBlock, row0, full_a);
+                } else {
+                  for (int bx = 0; bx < n_box; ++bx)
+                    tma_load_2d(dst + (uint32_t)u * b_bytes + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, (kb0 + u) * kBlock,
+                                row0 + bx * kGemmBoxRows, full_a);
+                }
+              } else if (whole) {   // this CTA's 1/C of the rows, delivered to the same stage of every CTA of the cluster
+                tma_load_2d_mc(dst + (uint32_t)u * b_bytes + (uint32_t)(cr * share) * 128u, &map_xw, (kb0 + u) * kBlock,
+                               row0 + cr * share, full_a, kMcMask);
+              } else {              // ragged: the 32-row boxes are dealt round-robin
+                for (int bx = cr; bx < n_box; bx += kGemmCluster)
+                  tma_load_2d_mc(dst + (uint32_t)u * b_bytes + (uint32_t)bx * (kGemmBoxRows * 128u), &map_x, (kb0 + u) * kBlock,
+                                 row0 + bx * kGemmBoxRows, full_a, kMcMask);
               }
             }
           }
@@ -376,6 +433,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
           if (dst == ring_end) dst = b_ring;
           full_a += 8u;
           if (full_a == full_end) full_a = full0;
+        }
+      }
+      if (kGemmCluster > 1) {
+        // A peer's MMA commits arrive on THIS CTA's `empty` barriers; none may still be in flight when the CTA exits.  Waiting
+        // out the slots not yet waited for (in order, as above) sees every peer's last arrival.
+        for (int i = min(cs, lead); i > 0; --i) {
+          mbar_wait(empty_a, pe);
+          empty_a += 8u;
+          if (empty_a == empty_end) { empty_a = empty0; pe ^= 1u; }
         }
       }
     } else if (warp == 2) {
@@ -390,14 +456,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       int sw = 0, it = 0;
       uint32_t phw = 0;
       // L2 prefetch runs kGemmWPrefetch stages ahead: (pf_item, pf_st) is its cursor, pf_row the weight row of pf_item's tile
-      int pf_item = blockIdx.x, pf_st = 0, pf_ahead = 0, pf_row = 0;
+      int pf_item = item0, pf_st = 0, pf_ahead = 0, pf_row = 0;
       auto item_row = [&](int item) -> int {
-        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+        int tile, rt;
+        item_tile(item, tile, rt);
         return a.tile_list[4 * tile] * a.w.rows + rt * kGemmRowTile;
       };
       if (pf_item < n_items) pf_row = item_row(pf_item);
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+      for (int item = item0; item < n_items; item += item_step, ++it) {
+        int tile, rt;
+        item_tile(item, tile, rt);
         const int e = a.tile_list[4 * tile];
         const int c1 = e * a.w.rows + rt * kGemmRowTile;
         {
@@ -420,7 +488,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
             ++pf_ahead;
             if (++pf_st == spi) {
               pf_st = 0;
-              pf_item += gridDim.x;
+              pf_item += item_step;
               if (pf_item < n_items) pf_row = item_row(pf_item);
             }
           }
@@ -444,8 +512,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       const uint32_t a_t0 = tmem + acol0, a_step = (uint32_t)kps * 32u, a_end = a_t0 + (uint32_t)n_a * a_step;
       uint32_t full_a = full0, pha = 0, b_lo = blo0, a_t = a_t0;
       int it = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        const int tile = item / n_row_tiles;
+      for (int item = item0; item < n_items; item += item_step, ++it) {
+        const int tile = item / n_rtg;
         const int n_tok = a.tile_list[4 * tile + 2];
         const uint32_t idesc = make_idesc(max(16, (n_tok + 15) & ~15));
         const int db = it & 1;
@@ -466,7 +534,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
                   tc_mma_ts(d_t, a_t + (uint32_t)(u * 32 + 8 * kk), desc + (uint64_t)(2 * kk), idesc, (uint32_t)(kb0 | u | kk));
               }
             }
-            tc_commit(full_a + 8u * (uint32_t)(kBarEmpty - kBarFull));   // frees the slot's A operand and activation stages
+            // frees the slot's A operand and activation stages -- the stages in EVERY CTA of the cluster, whose producers
+            // write into this CTA's copy too
+            if (kGemmCluster == 1) tc_commit(full_a + 8u * (uint32_t)(kBarEmpty - kBarFull));
+            else tc_commit_mc(full_a + 8u * (uint32_t)(kBarEmpty - kBarFull), kMcMask);
             if (kb0 + kps >= nkb) tc_commit(d_full0 + 8u * (uint32_t)db);
           }
           __syncwarp();
@@ -497,8 +568,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
     uint32_t phw = 0, pha = 0;
     while (sub >= kps) { sub -= kps; ++sl; }
     sub = g % kps; sl = g / kps;                 // g < 3 <= n_a * kps
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+    for (int item = item0; item < n_items; item += item_step, ++it) {
+      int tile, rt;
+      item_tile(item, tile, rt);
       const int e = a.tile_list[4 * tile];
       const int n = rt * kGemmRowTile + r;
       const int mb = it & 1;
@@ -579,8 +651,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
     const int r = q * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
     int it = 0;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+    for (int item = item0; item < n_items; item += item_step, ++it) {
+      int tile, rt;
+      const bool stores = item_tile(item, tile, rt);
       const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
       const int n = rt * kGemmRowTile + r;
       const int db = it & 1;
@@ -588,7 +661,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
       mbar_wait(bar(kBarDFull + db), (uint32_t)(it >> 1) & 1u);
       GEMM_DBG_ADD(0);
       tc_fence_after();
-      const bool row_ok = n < a.w.rows;
+      const bool row_ok = stores && n < a.w.rows;
       for (int c0 = 0; c0 < n_tok; c0 += 32) {
         uint32_t v[32];
         tmem_ld32(t_lane + (uint32_t)(db * a.tile_tokens + c0), v);
@@ -650,6 +723,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
   // ---- teardown ----
   tc_fence_before();
   __syncthreads();
+  if (kGemmCluster > 1) cluster_sync_all();   // no CTA leaves while a peer may still write its shared memory or barriers
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
@@ -710,7 +784,7 @@ inline int gemm_tile_tokens(int T, int k, int E, bool nested = false) {
 template <bool W13>
 int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
                 const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err,
-                size_t err_len, int* launches, int32_t* status = nullptr) {
+                size_t err_len, int* launches, int32_t* status = nullptr, int tile_rows = 0) {
   const char* name = W13 ? "gemm_w13" : "gemm_w2";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
   if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
@@ -738,7 +812,7 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.meta = meta;
   a.tile_list = tile_list;
   a.act = act;
-  a.tile_tokens = gemm_tile_tokens(T, k, E, w->absmax_f32 == nullptr);
+  a.tile_tokens = tile_rows > 0 ? tile_rows : gemm_tile_tokens(T, k, E, w->absmax_f32 == nullptr);
   a.kps = a.tile_tokens <= 32 ? 4 : 2;
   a.n_a = std::min(kMaxAStages, (512 - 2 * a.tile_tokens) / (32 * a.kps));
   a.want_b = a.tile_tokens <= 32 ? 12 : 4;
@@ -755,14 +829,43 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
   if (!make_map_2d(&map_x, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, kGemmBoxRows))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
-  CUtensorMap map_xw;   // whole-tile boxes [tile_tokens x 64] for full tiles
-  if (!make_map_2d(&map_xw, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, (uint32_t)a.tile_tokens))
+  CUtensorMap map_xw;   // one CTA's share of a full tile: boxes [tile_tokens / cluster x 64]
+  if (a.tile_tokens % (8 * kGemmCluster)) return fail(NF4MOE_EINVAL, "tile rows must split into 1 KB-aligned shares across the cluster");
+  if (!make_map_2d(&map_xw, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock,
+                   (uint32_t)(a.tile_tokens / kGemmCluster)))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activation tiles");
   const bool fast = mode == NF4MOE_GEMM_FAST;
   cudaError_t e = fast ? ensure_dyn_smem<gemm_kernel<W13, true>>((int)kGemmSmemBytes) : ensure_dyn_smem<gemm_kernel<W13, false>>((int)kGemmSmemBytes);
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e)); return (int)e; }
-  if (fast) e = launch_pdl(gemm_kernel<W13, true>, dim3(sms), dim3(kGemmThreads), kGemmSmemBytes, (cudaStream_t)stream, a, map_w, map_x, map_xw);
-  else e = launch_pdl(gemm_kernel<W13, false>, dim3(sms), dim3(kGemmThreads), kGemmSmemBytes, (cudaStream_t)stream, a, map_w, map_x, map_xw);
+  int n_clusters = sms / kGemmCluster;
+  if (kGemmCluster > 1) {
+    // clusters live inside one GPC: ask how many can be resident at once (a GPC with an SM count that C does not divide
+    // strands SMs) and launch exactly that many, so that no cluster waits for another to finish
+    static std::atomic<int> cached[64];
+    int c = dev < 64 ? cached[dev].load(std::memory_order_acquire) : 0;
+    if (c == 0) {
+      cudaLaunchConfig_t q = {};
+      q.gridDim = dim3((unsigned)(n_clusters * kGemmCluster));
+      q.blockDim = dim3(kGemmThreads);
+      q.dynamicSmemBytes = kGemmSmemBytes;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = kGemmCluster;
+      qa[0].val.clusterDim.y = 1;
+      qa[0].val.clusterDim.z = 1;
+      q.attrs = qa;
+      q.numAttrs = 1;
+      int got = 0;
+      cudaError_t qe = fast ? cudaOccupancyMaxActiveClusters(&got, gemm_kernel<W13, true>, &q) : cudaOccupancyMaxActiveClusters(&got, gemm_kernel<W13, false>, &q);
+      if (qe != cudaSuccess || got <= 0) { cudaGetLastError(); got = n_clusters; }
+      c = std::min(got, n_clusters);
+      if (dev < 64) cached[dev].store(c, std::memory_order_release);
+    }
+    n_clusters = c;
+  }
+  const dim3 grid((unsigned)(n_clusters * kGemmCluster));
+  if (fast) e = launch_pdl_cluster(gemm_kernel<W13, true>, grid, dim3(kGemmThreads), kGemmSmemBytes, (cudaStream_t)stream, kGemmCluster, a, map_w, map_x, map_xw);
+  else e = launch_pdl_cluster(gemm_kernel<W13, false>, grid, dim3(kGemmThreads), kGemmSmemBytes, (cudaStream_t)stream, kGemmCluster, a, map_w, map_x, map_xw);
   ++*launches;
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }

@@ -309,8 +309,8 @@ int nf4moe_permute_rows(const void* x, const int32_t* sorted_pairs, const int32_
   DevInfo di;
   if (int rc = device_info(&di)) return rc;
   const long long rows = (long long)T * k;
-  const int grid = (int)std::min<long long>((rows + 7) / 8, (long long)di.sms * 8);
-  launch_pdl(permute_rows_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __half*)x, sorted_pairs, meta, (int)rows, k, H,
+  const int grid = (int)std::min<long long>(rows, (long long)di.sms * 16);
+  launch_pdl(permute_rows_kernel, dim3(grid), dim3(128), 0, (cudaStream_t)stream, (const __half*)x, sorted_pairs, meta, (int)rows, k, H,
              (__half*)x_sorted);
   CHECK_LAUNCH("permute_rows_kernel");
   return 0;
@@ -389,23 +389,27 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
   return launch_gemv<false>(a, T, w2->absmax_f32 == nullptr, di.sms, (cudaStream_t)stream);
 }
 
+// tile_rows: the token-tile size the tile list was built with (0 = what the library derives from (T, k, E)); <= 32 rows go to the
+// decode-regime kernel, larger tiles to the prefill grouped GEMM
 static int gemm_w13_any(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* meta, const int32_t* tile_list, int T,
-                        int k, int E, int act, int mode, void* h_sorted, void* stream, const void* bias, int32_t* status) {
-  if (dec_serves(T, k, E, mode))
+                        int k, int E, int act, int mode, void* h_sorted, void* stream, const void* bias, int32_t* status,
+                        int tile_rows = 0) {
+  if (tile_rows > 0 ? tile_rows <= 32 : dec_serves(T, k, E, mode))
     return dec_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err, sizeof(g_err),
                             &g_launches, bias, status);
   if (bias) return fail(NF4MOE_EINVAL, "gemm_w13: the fused bias exists in the decode-regime kernel only");
   return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err, sizeof(g_err),
-                           &g_launches, status);
+                           &g_launches, status, tile_rows);
 }
 
 static int gemm_w2_any(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* sorted_pairs, const int32_t* meta,
-                       const int32_t* tile_list, int T, int k, int E, int mode, void* y, void* stream, int32_t* status) {
-  if (dec_serves(T, k, E, mode))
+                       const int32_t* tile_list, int T, int k, int E, int mode, void* y, void* stream, int32_t* status,
+                       int tile_rows = 0) {
+  if (tile_rows > 0 ? tile_rows <= 32 : dec_serves(T, k, E, mode))
     return dec_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, g_err, sizeof(g_err),
                              &g_launches, nullptr, status);
   return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, g_err, sizeof(g_err),
-                            &g_launches, status);
+                            &g_launches, status, tile_rows);
 }
 
 int nf4moe_gemm_w13_swiglu(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* expert_offsets,
@@ -423,26 +427,29 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 }
 
 // bucket -> (permute) -> w13 (+activation) -> w2 for the (row, slot) pairs of `ids` [T, k]; y fp16 [T*k, H] in pair order.
+// policy_T: the token count the regime and the token-tile size are chosen for (an expert-parallel owner passes the rows it
+// EXPECTS, not the capacity of its receive buffer); buffers and TMA maps are always sized by T.
 static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* y, int T,
                        int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches,
-                       const void* w13_bias = nullptr) {
+                       const void* w13_bias = nullptr, int policy_T = 0) {
   cudaStream_t st = (cudaStream_t)stream;
+  if (policy_T <= 0 || policy_T > T) policy_T = T;
   if (regime == NF4MOE_REGIME_AUTO) {
     // the tcgen05 kernels need 16-row / 64-column granularity and K <= 4096; other shapes stay on the GEMV
     const bool tc_ok = w13->rows % 16 == 0 && w2->rows % 16 == 0 && w13->cols % kBlock == 0 && w2->cols % kBlock == 0 &&
                        w13->cols <= 4096 && w2->cols <= 4096;
-    regime = tc_ok ? nf4moe_auto_regime(T, k, E) : NF4MOE_REGIME_GEMV;
+    regime = tc_ok ? nf4moe_auto_regime(policy_T, k, E) : NF4MOE_REGIME_GEMV;
   }
   if (regime != NF4MOE_REGIME_GEMV && regime != NF4MOE_REGIME_GEMM && regime != NF4MOE_REGIME_GEMM_FAST)
     return fail(NF4MOE_EINVAL, "unknown regime %d", regime);
   const bool gemm = regime != NF4MOE_REGIME_GEMV;
   const int mode = regime == NF4MOE_REGIME_GEMM_FAST ? NF4MOE_GEMM_FAST : NF4MOE_GEMM_EXACT;
-  const int tile_rows = gemm ? gemm_tile_tokens(T, k, E, w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr) : 0;
+  const int tile_rows = gemm ? gemm_tile_tokens(policy_T, k, E, w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr) : 0;
   if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
   *launches += g_launches; g_launches = 0;
   // with an up-projection bias the w13 kernels store their raw products and bias_act_kernel applies bias + activation
   // (the decode tcgen05 kernel adds the bias inside its fused SwiGLU epilogue instead)
-  const bool bias_fused = w13_bias && gemm && act == NF4MOE_ACT_SWIGLU_OAI && dec_serves(T, k, E, mode);
+  const bool bias_fused = w13_bias && gemm && act == NF4MOE_ACT_SWIGLU_OAI && tile_rows <= 32;
   const bool bias_split = w13_bias && !bias_fused;
   const int act_k = bias_split ? NF4MOE_ACT_CHUNK_SILU : act;   // CHUNK_SILU = "store raw [rows, 2I]" for the w13 kernels
   __half* h_dst = act_k == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
@@ -450,7 +457,7 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
     if (int rc = gemm_w13_any(ws.xs, w13, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream, bias_fused ? w13_bias : nullptr,
-                              ws.status)) return rc;
+                              ws.status, tile_rows)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w13_swiglu(x, w13, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, act_k, h_dst, stream)) return rc;
   }
@@ -470,7 +477,7 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     *launches += g_launches; g_launches = 0;
   }
   if (gemm) {
-    if (int rc = gemm_w2_any(ws.h, w2, ws.sorted, ws.meta, ws.tiles, T, k, E, mode, y, stream, ws.status)) return rc;
+    if (int rc = gemm_w2_any(ws.h, w2, ws.sorted, ws.meta, ws.tiles, T, k, E, mode, y, stream, ws.status, tile_rows)) return rc;
   } else {
     if (int rc = nf4moe_gemv_w2(ws.h, w2, ws.offsets, ws.sorted, ws.active, ws.meta, T, k, E, y, stream)) return rc;
   }
@@ -529,12 +536,12 @@ int nf4moe_moe_forward_bias(const void* x, const void* router_logits, int logits
 int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
                        void* y_rows, int n_rows, int E, int H, int I, int act, int regime, void* workspace,
                        size_t workspace_bytes, void* stream) {
-  return nf4moe_expert_rows_bias(rows, row_expert, w13, w2, nullptr, y_rows, n_rows, E, H, I, act, regime, workspace, workspace_bytes,
+  return nf4moe_expert_rows_bias(rows, row_expert, w13, w2, nullptr, y_rows, n_rows, 0, E, H, I, act, regime, workspace, workspace_bytes,
                                  stream);
 }
 
 int nf4moe_expert_rows_bias(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
-                            const void* w13_bias, void* y_rows, int n_rows, int E, int H, int I, int act, int regime,
+                            const void* w13_bias, void* y_rows, int n_rows, int rows_hint, int E, int H, int I, int act, int regime,
                             void* workspace, size_t workspace_bytes, void* stream) {
   g_launches = 0;
   if (w13_bias && !aligned16(w13_bias)) return fail(NF4MOE_EALIGN, "expert_rows: w13_bias must be 16-byte aligned");
@@ -548,7 +555,7 @@ int nf4moe_expert_rows_bias(const void* rows, const int32_t* row_expert, const n
   if (!aligned16(workspace) || !aligned16(rows) || !aligned16(y_rows))
     return fail(NF4MOE_EALIGN, "expert_rows: rows, y_rows and workspace must be 16-byte aligned");
   int launches = 0;
-  if (int rc = run_experts(rows, row_expert, w13, w2, y_rows, n_rows, E, H, I, 1, act, regime, ws, stream, &launches, w13_bias)) return rc;
+  if (int rc = run_experts(rows, row_expert, w13, w2, y_rows, n_rows, E, H, I, 1, act, regime, ws, stream, &launches, w13_bias, rows_hint)) return rc;
   g_launches += launches;
   return 0;
 }
@@ -593,6 +600,65 @@ int nf4moe_combine_indexed_bias(const void* y, const float* weights, const int32
   combine_indexed_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y, weights, pair_slot, ids, (const __half*)w2_bias, E, T,
                                                                  k, H, (__half*)out);
   CHECK_LAUNCH("combine_indexed_kernel");
+  return 0;
+}
+
+// ---- peer-memory exchange -----------------------------------------------------------------------------------------------
+static int fill_peers(EpPeers* peers, void* const* rows, void* const* ids, void* const* flags, int world, bool want_ids, const char* name) {
+  if (world <= 0 || world > kEpMaxWorld) return fail(NF4MOE_EINVAL, "%s: world must be in 1..%d", name, kEpMaxWorld);
+  if (!rows || !flags || (want_ids && !ids)) return fail(NF4MOE_EINVAL, "%s: null peer pointer table", name);
+  for (int p = 0; p < kEpMaxWorld; ++p) {
+    peers->rows[p] = p < world ? (__half*)rows[p] : nullptr;
+    peers->ids[p] = (p < world && want_ids) ? (int32_t*)ids[p] : nullptr;
+    peers->flags[p] = p < world ? (unsigned long long*)flags[p] : nullptr;
+    if (p < world && (!rows[p] || !flags[p] || (want_ids && !ids[p]) || !aligned16(rows[p])))
+      return fail(NF4MOE_EINVAL, "%s: peer %d has a null or misaligned buffer", name, p);
+  }
+  return 0;
+}
+
+int nf4moe_ep_dispatch_p2p(const void* x, const int32_t* ids, const int32_t* expert_offsets, const int32_t* sorted_pairs, int T, int k,
+                           int E, int H, int world, int rank, int cap, void* const* peer_recv_rows, void* const* peer_recv_ids,
+                           void* const* peer_flags, int32_t* pair_slot, uint32_t* ctr, int32_t* status, void* stream) {
+  if (!x || !ids || !expert_offsets || !sorted_pairs || !pair_slot || !ctr || !status || T < 0 || k <= 0 || E <= 0 || H <= 0 || H % 8 ||
+      cap <= 0 || rank < 0 || rank >= world || E % world)
+    return fail(NF4MOE_EINVAL, "ep_dispatch_p2p: bad arguments (E must be a multiple of world, H of 8)");
+  if (!aligned16(x)) return fail(NF4MOE_EALIGN, "ep_dispatch_p2p: x must be 16-byte aligned");
+  EpPeers peers;
+  if (int rc = fill_peers(&peers, peer_recv_rows, peer_recv_ids, peer_flags, world, true, "ep_dispatch_p2p")) return rc;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(pair_slot, 0xFF, (size_t)T * k * 4, st);   // -1: not dispatched
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(pair_slot)");
+  const long long slots = (long long)world * cap;
+  const int grid = (int)std::min<long long>((slots + 7) / 8, (long long)di.sms * 4);
+  ep_dispatch_kernel<<<grid, 256, 0, st>>>((const __half*)x, ids, expert_offsets, sorted_pairs, k, H, world, rank, E / world, cap, peers,
+                                          pair_slot, ctr, status);
+  CHECK_LAUNCH("ep_dispatch_kernel");
+  return 0;
+}
+
+int nf4moe_ep_return_p2p(const void* y_rows, const int32_t* recv_ids, int H, int world, int rank, int cap, void* const* peer_back_rows,
+                         void* const* peer_flags, uint32_t* ctr, void* stream) {
+  if (!y_rows || !recv_ids || !ctr || H <= 0 || H % 8 || cap <= 0 || rank < 0 || rank >= world)
+    return fail(NF4MOE_EINVAL, "ep_return_p2p: bad arguments");
+  if (!aligned16(y_rows)) return fail(NF4MOE_EALIGN, "ep_return_p2p: y_rows must be 16-byte aligned");
+  EpPeers peers;
+  if (int rc = fill_peers(&peers, peer_back_rows, nullptr, peer_flags, world, false, "ep_return_p2p")) return rc;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  const long long slots = (long long)world * cap;
+  const int grid = (int)std::min<long long>((slots + 7) / 8, (long long)di.sms * 4);
+  ep_return_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y_rows, recv_ids, H, world, rank, cap, peers, ctr);
+  CHECK_LAUNCH("ep_return_kernel");
+  return 0;
+}
+
+int nf4moe_ep_wait(const void* flags, int world, uint32_t* ctr, int32_t* status, void* stream) {
+  if (!flags || !ctr || !status || world <= 0 || world > kEpMaxWorld) return fail(NF4MOE_EINVAL, "ep_wait: bad arguments");
+  ep_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const unsigned long long*)flags, world, ctr, status);
+  CHECK_LAUNCH("ep_wait_kernel");
   return 0;
 }
 

@@ -65,6 +65,63 @@ __global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict_
   }
 }
 
+// Warp 0 of the bucket kernels: exclusive scan of the per-expert counts (E <= 256, 8 experts per lane) into s_off, and -- in
+// the same pass -- the compacted list of active experts, the token-tile list of the grouped GEMM and meta[0..3].  (Round 1 did
+// the compaction serially on one thread: ~5 us of the 11.8 us a 256-pair bucket launch took.)
+// Token tiles: an expert's c rows split into ceil(c / tile_rows) near-equal tiles (multiples of 16 rows).
+__device__ __forceinline__ void bucket_scan_and_lists(const int* s_count, int* s_off, int E, int lane, int32_t* expert_offsets,
+                                                      int32_t* active_experts, int32_t* meta, int32_t* tile_list, int tile_rows,
+                                                      bool write_global) {
+  int cnt[8], loc[8], tsz[8], run = 0, act = 0, tiles = 0, mx = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int e = lane * 8 + j;
+    const int c = e < E ? s_count[e] : 0;
+    cnt[j] = c;
+    loc[j] = run;
+    run += c;
+    tsz[j] = 0;
+    if (c > 0) {
+      ++act;
+      mx = max(mx, c);
+      const int ntl = (c + tile_rows - 1) / tile_rows;
+      tsz[j] = (((c + ntl - 1) / ntl) + 15) & ~15;
+      tiles += (c + tsz[j] - 1) / tsz[j];
+    }
+  }
+  int inc = run, inc_a = act, inc_t = tiles;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, inc, o), na = __shfl_up_sync(0xffffffffu, inc_a, o), nt = __shfl_up_sync(0xffffffffu, inc_t, o);
+    if (lane >= o) { inc += n; inc_a += na; inc_t += nt; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  const int base = inc - run;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s_off[lane * 8 + j] = base + loc[j];
+  if (lane == 31) s_off[256] = inc;
+  if (!write_global) return;
+  const int total = __shfl_sync(0xffffffffu, inc, 31), n_act = __shfl_sync(0xffffffffu, inc_a, 31), n_tiles = __shfl_sync(0xffffffffu, inc_t, 31);
+  int ia = inc_a - act, it = inc_t - tiles;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int e = lane * 8 + j, c = cnt[j];
+    if (e <= E) expert_offsets[e] = e < E ? base + loc[j] : total;
+    if (c > 0) {
+      active_experts[ia++] = e;
+      if (tile_list)
+        for (int r = 0; r < c; r += tsz[j]) {
+          *reinterpret_cast<int4*>(tile_list + 4 * it) = make_int4(e, base + loc[j] + r, min(tsz[j], c - r), 0);
+          ++it;
+        }
+    }
+  }
+  if (E == 256 && lane == 31) expert_offsets[256] = total;
+  for (int i = n_act + lane; i < E; i += 32) active_experts[i] = -1;
+  if (lane == 0) { meta[0] = n_act; meta[1] = total; meta[2] = n_tiles; meta[3] = mx; }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // (2) bucketing: ONE CTA of 1024 threads; ids staged in shared memory as bytes (E <= 256; 0xFF = dropped).
 // Warp w owns experts w, w+32, ...: a counting pass and a placement pass over all pairs with ballots, so the
@@ -108,45 +165,8 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
     if (lane == 0) s_count[e] = c;
   }
   __syncthreads();
-  if (warp == 0) {  // exclusive scan over <= 256 experts, 8 per lane
-    int loc[8], run = 0;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { loc[j] = run; run += s_count[lane * 8 + j]; }
-    int inc = run;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += n;
-    }
-    const int base = inc - run;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s_off[lane * 8 + j] = base + loc[j];
-    if (lane == 31) s_off[256] = inc;
-  }
+  if (warp == 0) bucket_scan_and_lists(s_count, s_off, E, lane, expert_offsets, active_experts, meta, tile_list, tile_rows, true);
   __syncthreads();
-  for (int e = tid; e <= E; e += kBucketThreads) expert_offsets[e] = s_off[e];
-  if (tid == 0) {  // E <= 256 entries: serial compaction is a few hundred cycles
-    int na = 0, nt = 0, mx = 0;
-    for (int e = 0; e < E; ++e) {
-      const int c = s_count[e];
-      if (c > 0) {
-        active_experts[na++] = e;
-        mx = max(mx, c);
-        // token tiles of the grouped GEMM: an expert's rows split into ceil(c / tile_rows) near-equal tiles (multiples of 16)
-        const int ntl = (c + tile_rows - 1) / tile_rows;
-        const int sz = (((c + ntl - 1) / ntl) + 15) & ~15;
-        if (tile_list)
-          for (int r = 0; r < c; r += sz) {
-            tile_list[4 * nt] = e; tile_list[4 * nt + 1] = s_off[e] + r; tile_list[4 * nt + 2] = min(sz, c - r); tile_list[4 * nt + 3] = 0;
-            ++nt;
-          }
-        else
-          nt += (c + sz - 1) / sz;
-      }
-    }
-    for (int i = na; i < E; ++i) active_experts[i] = -1;
-    meta[0] = na; meta[1] = s_off[E]; meta[2] = nt; meta[3] = mx;
-  }
   for (int e = warp; e < E; e += 32) {
     const uint32_t pat = 0x01010101u * (uint32_t)e;
     int run = s_off[e];
@@ -222,46 +242,8 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_cluster_kernel(const in
     s_before[tid] = before;
   }
   __syncthreads();
-  if (warp == 0) {  // exclusive scan over <= 256 experts, 8 per lane
-    int loc[8], run = 0;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { loc[j] = run; run += s_tot[lane * 8 + j]; }
-    int inc = run;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, inc, o);
-      if (lane >= o) inc += n;
-    }
-    const int base = inc - run;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) s_off[lane * 8 + j] = base + loc[j];
-    if (lane == 31) s_off[256] = inc;
-  }
+  if (warp == 0) bucket_scan_and_lists(s_tot, s_off, E, lane, expert_offsets, active_experts, meta, tile_list, tile_rows, rank == 0);
   __syncthreads();
-  if (rank == 0) {
-    for (int e = tid; e <= E; e += kBucketThreads) expert_offsets[e] = s_off[e];
-    if (tid == 0) {
-      int na = 0, nt = 0, mx = 0;
-      for (int e = 0; e < E; ++e) {
-        const int c = s_tot[e];
-        if (c > 0) {
-          active_experts[na++] = e;
-          mx = max(mx, c);
-          const int ntl = (c + tile_rows - 1) / tile_rows;
-          const int sz = (((c + ntl - 1) / ntl) + 15) & ~15;
-          if (tile_list)
-            for (int r = 0; r < c; r += sz) {
-              tile_list[4 * nt] = e; tile_list[4 * nt + 1] = s_off[e] + r; tile_list[4 * nt + 2] = min(sz, c - r); tile_list[4 * nt + 3] = 0;
-              ++nt;
-            }
-          else
-            nt += (c + sz - 1) / sz;
-        }
-      }
-      for (int i = na; i < E; ++i) active_experts[i] = -1;
-      meta[0] = na; meta[1] = s_off[E]; meta[2] = nt; meta[3] = mx;
-    }
-  }
   for (int e = warp; e < E; e += 32) {
     const uint32_t pat = 0x01010101u * (uint32_t)e;
     int run = s_off[e] + s_before[e];
@@ -285,24 +267,39 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_cluster_kernel(const in
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
-// x_sorted[s,:] = x[sorted_pairs[s]/k,:]; one warp per row, 16-byte accesses.  Rows past meta[1] are zeroed so the
-// grouped GEMM's last tile reads defined data.
-__global__ void __launch_bounds__(256) permute_rows_kernel(const __half* __restrict__ x,
+// x_sorted[s,:] = x[sorted_pairs[s]/k,:]; one CTA of 128 threads per row pass (a 2880-wide row = 360 16-byte chunks = three per
+// thread, all in flight at once: round 1 walked a row with one warp, twelve dependent round trips, 5.8 us for 256 rows).
+// Rows past meta[1] are zeroed so the grouped GEMM's last tile reads defined data.
+__global__ void __launch_bounds__(128) permute_rows_kernel(const __half* __restrict__ x,
                                                            const int32_t* __restrict__ sorted_pairs,
                                                            const int32_t* __restrict__ meta, int n_rows, int k, int H,
                                                            __half* __restrict__ xs) {
   grid_dep_launch();
   grid_dep_wait();
-  const int lane = threadIdx.x & 31;
   const int n_kept = meta[1];
   const int vec = H / 8;
-  for (int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; s < n_rows; s += (gridDim.x * blockDim.x) >> 5) {
+  // rows past the kept pairs are only ever read as padding of the LAST token tile (<= 256 rows): zero that much, not a whole
+  // mostly empty fixed-capacity buffer
+  n_rows = min(n_rows, n_kept + 256);
+  for (int s = blockIdx.x; s < n_rows; s += gridDim.x) {
     uint4* dst = reinterpret_cast<uint4*>(xs + (long long)s * H);
     if (s < n_kept) {
       const uint4* src = reinterpret_cast<const uint4*>(x + (long long)(sorted_pairs[s] / k) * H);
-      for (int i = lane; i < vec; i += 32) dst[i] = __ldg(src + i);
+      for (int i0 = 0; i0 < vec; i0 += 4 * 128) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * 128 + (int)threadIdx.x;
+          if (i < vec) v[u] = __ldg(src + i);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * 128 + (int)threadIdx.x;
+          if (i < vec) dst[i] = v[u];
+        }
+      }
     } else {
-      for (int i = lane; i < vec; i += 32) dst[i] = make_uint4(0, 0, 0, 0);
+      for (int i = threadIdx.x; i < vec; i += 128) dst[i] = make_uint4(0, 0, 0, 0);
     }
   }
 }
@@ -322,24 +319,43 @@ __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__
        i += (long long)gridDim.x * blockDim.x) {
     const int t = (int)(i / vec), c = (int)(i - (long long)t * vec);
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int s = 0; s < k; ++s) {
-      int e = 0;
-      if (ids) {
-        e = ids[(long long)t * k + s];
-        if (e < 0 || e >= E) continue;
-      }
-      const float ws = w[(long long)t * k + s];
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(y + ((long long)t * k + s) * H) + c);
-      const __half2* h = reinterpret_cast<const __half2*>(&v);
-      uint4 bv = make_uint4(0u, 0u, 0u, 0u);
-      if (bias) bv = __ldg(reinterpret_cast<const uint4*>(bias + (long long)e * H) + c);
-      const __half2* bh = reinterpret_cast<const __half2*>(&bv);
+    // slots in chunks of 4 with every load of a chunk issued before its first use (round 1 walked the slots one dependent
+    // round trip at a time); the sum itself stays strictly slot-ascending in fp32
+    for (int s0 = 0; s0 < k; s0 += 4) {
+      int e[4];
+      float ws[4];
+      uint4 v[4], bv[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float2 f = __half22float2(h[j]);
-        if (bias) { const float2 b = __half22float2(bh[j]); f.x = __fadd_rn(f.x, b.x); f.y = __fadd_rn(f.y, b.y); }
-        acc[2 * j] = __fadd_rn(acc[2 * j], __fmul_rn(ws, f.x));
-        acc[2 * j + 1] = __fadd_rn(acc[2 * j + 1], __fmul_rn(ws, f.y));
+      for (int u = 0; u < 4; ++u) {
+        const int s = s0 + u;
+        e[u] = -1;
+        if (s < k) {
+          e[u] = ids ? ids[(long long)t * k + s] : 0;
+          ws[u] = w[(long long)t * k + s];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const bool ok = e[u] >= 0 && e[u] < (ids ? E : 1);
+        if (!ok) e[u] = -1;
+        v[u] = bv[u] = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) {
+          v[u] = __ldg(reinterpret_cast<const uint4*>(y + ((long long)t * k + s0 + u) * H) + c);
+          if (bias) bv[u] = __ldg(reinterpret_cast<const uint4*>(bias + (long long)e[u] * H) + c);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (e[u] < 0) continue;
+        const __half2* h = reinterpret_cast<const __half2*>(&v[u]);
+        const __half2* bh = reinterpret_cast<const __half2*>(&bv[u]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float2 f = __half22float2(h[j]);
+          if (bias) { const float2 b = __half22float2(bh[j]); f.x = __fadd_rn(f.x, b.x); f.y = __fadd_rn(f.y, b.y); }
+          acc[2 * j] = __fadd_rn(acc[2 * j], __fmul_rn(ws[u], f.x));
+          acc[2 * j + 1] = __fadd_rn(acc[2 * j + 1], __fmul_rn(ws[u], f.y));
+        }
       }
     }
     uint4 o;

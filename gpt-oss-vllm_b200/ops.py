@@ -256,7 +256,7 @@ def ep_pack(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: int, cap
 def expert_rows(rows: torch.Tensor, row_expert: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights,
                 y_rows: torch.Tensor, act: int = _lib.ACT_SWIGLU_OAI, regime: int = _lib.REGIME_AUTO,
                 nested: bool | None = None, workspace: torch.Tensor | None = None,
-                w13_bias: torch.Tensor | None = None) -> torch.Tensor:
+                w13_bias: torch.Tensor | None = None, rows_hint: int = 0) -> torch.Tensor:
     """y_rows[r] = W2[e] act(W13[e] rows[r] + w13_bias[e]) for e = row_expert[r] in [0, E_local); other rows are left untouched.
     w13_bias: fp16 [E_local, 2I] or None."""
     _require_cuda(rows, "rows")
@@ -272,7 +272,7 @@ def expert_rows(rows: torch.Tensor, row_expert: torch.Tensor, w13: NF4ExpertWeig
     with torch.cuda.device(rows.device):
         _lib.check(_lib.load_library().nf4moe_expert_rows_bias(
             rows.data_ptr(), row_expert.data_ptr(), C.byref(q13), C.byref(q2), None if w13_bias is None else w13_bias.data_ptr(),
-            y_rows.data_ptr(), n, E, H, I, act, regime, workspace.data_ptr(), workspace.numel(), _stream_ptr(rows.device)))
+            y_rows.data_ptr(), n, rows_hint, E, H, I, act, regime, workspace.data_ptr(), workspace.numel(), _stream_ptr(rows.device)))
     return y_rows
 
 
@@ -296,3 +296,32 @@ def combine_indexed(y: torch.Tensor, weights: torch.Tensor, pair_slot: torch.Ten
             y.data_ptr(), weights.data_ptr(), pair_slot.data_ptr(), None if w2_bias is None else ids.data_ptr(),
             None if w2_bias is None else w2_bias.data_ptr(), E, T, k, H, out.data_ptr(), _stream_ptr(y.device)))
     return out
+
+
+# ---- peer-memory exchange (nf4moe_ep_dispatch_p2p / nf4moe_ep_wait / nf4moe_ep_return_p2p) ---------------------------------
+def ep_dispatch_p2p(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: int, rank: int, cap: int, peer_recv_rows,
+                    peer_recv_ids, peer_flags, pair_slot: torch.Tensor, ctr: torch.Tensor, status: torch.Tensor) -> None:
+    """Store this rank's routed rows straight into their owners' receive buffers (peer_* are ctypes arrays of device pointers)."""
+    _require_cuda(x, "x")
+    T, H = x.shape
+    k = ids.shape[1]
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load_library().nf4moe_ep_dispatch_p2p(
+            x.data_ptr(), ids.data_ptr(), b["expert_offsets"].data_ptr(), b["sorted_pairs"].data_ptr(), T, k, E, H, world, rank, cap,
+            C.cast(peer_recv_rows, C.c_void_p), C.cast(peer_recv_ids, C.c_void_p), C.cast(peer_flags, C.c_void_p),
+            pair_slot.data_ptr(), ctr.data_ptr(), status.data_ptr(), _stream_ptr(x.device)))
+
+
+def ep_return_p2p(y_rows: torch.Tensor, recv_ids: torch.Tensor, world: int, rank: int, cap: int, peer_back_rows, peer_flags,
+                  ctr: torch.Tensor) -> None:
+    H = y_rows.shape[-1]
+    with torch.cuda.device(y_rows.device):
+        _lib.check(_lib.load_library().nf4moe_ep_return_p2p(
+            y_rows.data_ptr(), recv_ids.data_ptr(), H, world, rank, cap, C.cast(peer_back_rows, C.c_void_p),
+            C.cast(peer_flags, C.c_void_p), ctr.data_ptr(), _stream_ptr(y_rows.device)))
+
+
+def ep_wait(flags: torch.Tensor, world: int, ctr: torch.Tensor, status: torch.Tensor) -> None:
+    with torch.cuda.device(flags.device):
+        _lib.check(_lib.load_library().nf4moe_ep_wait(flags.data_ptr(), world, ctr.data_ptr(), status.data_ptr(),
+                                                      _stream_ptr(flags.device)))

@@ -214,9 +214,11 @@ int nf4moe_expert_rows(const void* rows, const int32_t* row_expert, const nf4moe
                        size_t workspace_bytes, void* stream);
 
 /* The same with gpt-oss's up-projection bias (w13_bias fp16 [E, 2I], LOCAL expert index; NULL = none), added before the
- * activation exactly as nf4moe_moe_forward_bias does. */
+ * activation exactly as nf4moe_moe_forward_bias does.  rows_hint (0 = n_rows): how many of the n_rows slots are EXPECTED to hold a
+ * row -- a fixed-capacity receive buffer is mostly empty, and the regime / token-tile size should follow the rows that exist
+ * (round 1 chose them by capacity: a worst-case buffer ran the prefill pipeline over 2048 nearly empty slots). */
 int nf4moe_expert_rows_bias(const void* rows, const int32_t* row_expert, const nf4moe_qweight* w13, const nf4moe_qweight* w2,
-                            const void* w13_bias, void* y_rows, int n_rows, int E, int H, int I, int act, int regime,
+                            const void* w13_bias, void* y_rows, int n_rows, int rows_hint, int E, int H, int I, int act, int regime,
                             void* workspace, size_t workspace_bytes, void* stream);
 
 /* Combine side.  out[t, :] = fp16( sum_slot weights[t,slot] * y[pair_slot[t*k+slot], :] ) -- nf4moe_combine's arithmetic and
@@ -229,6 +231,28 @@ int nf4moe_combine_indexed(const void* y, const float* weights, const int32_t* p
  * the expert-parallel result equals nf4moe_moe_forward_bias bit for bit.  w2_bias == NULL: ids / E are ignored. */
 int nf4moe_combine_indexed_bias(const void* y, const float* weights, const int32_t* pair_slot, const int32_t* ids,
                                 const void* w2_bias, int E, int T, int k, int H, void* out, void* stream);
+
+/* ---- the same exchange over PEER MEMORY (NVLink / NVSwitch), no collective library on the data path ------------------------
+ * Each rank owns, in memory its peers can address, recv_rows fp16 [world, cap, H], recv_ids int32 [world, cap], back_rows fp16
+ * [world, cap, H] and flags uint64 [2, world] (zeroed once), plus a private counter block ctr uint32 (zeroed once; 2 words per
+ * entry point below).  The tables peer_*[p] are HOST arrays of `world` DEVICE pointers into rank p's copies.
+ *   nf4moe_ep_dispatch_p2p   home rank: stores row (p, j) of its pair list straight into owner p's recv_rows[rank, j] and the local
+ *                            expert id into recv_ids[rank, j] (-1 for unused slots), pair_slot[pair] = p*cap + j, then publishes a
+ *                            new epoch to flags[0][rank] of every peer.  Only rows that exist cross the link, so cap = T*k (which
+ *                            can never overflow) costs nothing: the exchange is drop-free.
+ *   nf4moe_ep_wait           spins (system-scope acquire) until all `world` entries of one flag row carry this rank's next epoch;
+ *                            status |= NF4MOE_STATUS_EP_TIMEOUT if a peer never arrives.
+ *   nf4moe_ep_return_p2p     owner rank: stores y_rows[q*cap + j] (where recv_ids >= 0) into home rank q's back_rows[rank, j] and
+ *                            publishes to flags[1][rank] of every peer; nf4moe_combine_indexed[_bias] then reads back_rows.
+ * Epochs live in device memory and advance once per launch, so a layer built from these calls replays from a CUDA graph.  Every
+ * rank must issue the same sequence of calls (SPMD).  Replaces nothing in the reference (single GPU, P/gpt_oss_server.py:25). */
+#define NF4MOE_STATUS_EP_TIMEOUT 8
+int nf4moe_ep_dispatch_p2p(const void* x, const int32_t* ids, const int32_t* expert_offsets, const int32_t* sorted_pairs, int T, int k,
+                           int E, int H, int world, int rank, int cap, void* const* peer_recv_rows, void* const* peer_recv_ids,
+                           void* const* peer_flags, int32_t* pair_slot, uint32_t* ctr, int32_t* status, void* stream);
+int nf4moe_ep_return_p2p(const void* y_rows, const int32_t* recv_ids, int H, int world, int rank, int cap, void* const* peer_back_rows,
+                         void* const* peer_flags, uint32_t* ctr, void* stream);
+int nf4moe_ep_wait(const void* flags, int world, uint32_t* ctr, int32_t* status, void* stream);
 
 /* Number of kernels the last nf4moe_moe_forward / nf4moe_expert_rows on this thread launched (bench.py's gpu_launches). */
 int nf4moe_last_launch_count(void);

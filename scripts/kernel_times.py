@@ -67,6 +67,10 @@ for T in a.tokens:
             for h, (_, w2) in zip(hs, stack):
                 pkg.ops.expert_w2(h, w2, b, T, 4, nested=nested, regime=regime)
         hs = run13(); run2(hs); torch.cuda.synchronize()
+        # order-independent fingerprints of layer 0's outputs: pool shapes / cluster sizes must not change a single bit
+        y0 = pkg.ops.expert_w2(hs[0], stack[0][1], b, T, 4, nested=nested, regime=regime)
+        fp = [int(t.contiguous().view(torch.int16).to(torch.int64).square().sum().item()) & 0xFFFFFFFFFFFF for t in (hs[0], y0)]
+        print(f"# {a.tag}T={T} {mode}: fingerprint h {fp[0]:012x} y {fp[1]:012x}", flush=True)
         g13, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         side = torch.cuda.Stream()
         with torch.cuda.stream(side):

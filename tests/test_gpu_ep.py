@@ -87,6 +87,89 @@ def test_virtual_ranks_default_regime_and_capacity_factor(pkg, cuda_device, worl
         assert_moe_close(out.cpu().numpy(), ref)
 
 
+@pytest.mark.parametrize("world,T,E,regime,bias", [(2, 9, 32, "gemv", False), (4, 16, 32, "auto", True), (8, 64, 32, "auto", False),
+                                                  (8, 40, 32, "gemm", True), (8, 6, 128, "gemv", False), (1, 5, 32, "gemv", True)])
+def test_peer_memory_exchange_virtual_ranks(pkg, cuda_device, world, T, E, regime, bias):
+    """The NVLink peer-memory exchange (nf4moe_ep_dispatch_p2p / nf4moe_ep_wait / nf4moe_ep_return_p2p) with `world` virtual
+    ranks on one GPU: every rank's dispatch kernel stores into the OTHER ranks' receive buffers through the pointer tables (here
+    device-local, on a multi-GPU box NVLink peer addresses), publishes its epoch, the owners' wait kernels see the flags, the
+    return path mirrors it.  Several layers in a row through ONE set of buffers (epochs advance, buffers are reused), ragged
+    token counts, one rank sending nearly everything to rank 0, expert biases: bit-identical to the single-GPU layer, and
+    nothing is ever dropped (capacity = worst case)."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    H, I, k = 192, 128, 4
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 500 + world + T, E, H, I)
+    rng = np.random.default_rng(15)
+    reg = {"gemm": pkg.REGIME_GEMM, "gemv": pkg.REGIME_GEMV, "auto": pkg.REGIME_AUTO}[regime]
+    b13 = torch.from_numpy((rng.standard_normal((E, 2 * I)) * 0.3).astype(np.float16)).to(cuda_device) if bias else None
+    b2 = torch.from_numpy((rng.standard_normal((E, H)) * 0.3).astype(np.float16)).to(cuda_device) if bias else None
+    plans = [ep.EPPlan(r, world, E) for r in range(world)]
+    exs = [ep.PeerExchange.local(pl, pl.capacity(T, k), H, cuda_device) for pl in plans]
+    for ex in exs:
+        ex.connect(exs)
+    layers = []
+    for r, pl in enumerate(plans):
+        lo, hi = pl.local_experts.start, pl.local_experts.stop
+        layers.append(ep.EPMoELayer(ep.shard_experts(w13, pl), ep.shard_experts(w2, pl), pl, k, H, T, cuda_device, regime=reg,
+                                    exchange=exs[r], w13_bias=None if b13 is None else b13[lo:hi].contiguous(), w2_bias=b2))
+        assert layers[-1].cap == T * k
+    for rep in range(3):                                               # three "layers" through the same buffers
+        xs, lgs = [], []
+        for r in range(world):
+            Tr = T - (r % 3)
+            xs.append(torch.from_numpy(rng.standard_normal((Tr, H)).astype(np.float16)).to(cuda_device))
+            lg = rng.standard_normal((Tr, E)).astype(np.float16)
+            if r == 1:
+                lg[:, :4] += 6
+            lgs.append(torch.from_numpy(lg).to(cuda_device))
+        for r in range(world):
+            layers[r].prepare(xs[r], router_logits=lgs[r])             # dispatch kernels of all ranks (stores + flags)
+        for l in layers:
+            l.dispatch()                                               # wait kernels: every flag is already there
+            l.compute()
+        for l in layers:
+            l.x.ret()
+        for r in range(world):
+            layers[r].x.wait_return()
+            out = layers[r].finish()
+            layers[r].check_overflow()
+            single = pkg.ops.moe_forward(xs[r], w13, w2, k, router_logits=lgs[r], regime=reg, w13_bias=b13, w2_bias=b2)
+            if regime != "auto":      # same kernels on both sides: bit-identical; AUTO may pick another regime for the owner's rows
+                assert torch.equal(out, single), f"rank {r} rep {rep} differs from the single-GPU layer"
+            ref = orc.moe_forward_from_states(xs[r].cpu().numpy(), lgs[r].cpu().numpy(), st13, st2, k=k,
+                                              b13=None if b13 is None else b13.cpu().numpy(), b2=None if b2 is None else b2.cpu().numpy())
+            assert_moe_close(out.cpu().numpy(), ref)
+    assert int(exs[0].flags[0, 0].item()) == 3 and int(exs[0].flags[1, world - 1].item()) == 3     # epochs advanced once per layer
+
+
+def test_nccl_exchange_layer_with_biases(pkg, cuda_device):
+    """The collective back end with expert biases: w13_bias applied on the owner (local expert index), w2_bias at home."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    world, T, E, H, I, k = 4, 12, 32, 192, 128, 4
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 611, E, H, I)
+    rng = np.random.default_rng(3)
+    b13 = torch.from_numpy((rng.standard_normal((E, 2 * I)) * 0.3).astype(np.float16)).to(cuda_device)
+    b2 = torch.from_numpy((rng.standard_normal((E, H)) * 0.3).astype(np.float16)).to(cuda_device)
+    layers, xs, lgs = [], [], []
+    for r in range(world):
+        pl = ep.EPPlan(r, world, E)
+        lo, hi = pl.local_experts.start, pl.local_experts.stop
+        layers.append(ep.EPMoELayer(ep.shard_experts(w13, pl), ep.shard_experts(w2, pl), pl, k, H, T, cuda_device, regime=pkg.REGIME_GEMV,
+                                    w13_bias=b13[lo:hi].contiguous(), w2_bias=b2))
+        xs.append(torch.from_numpy(rng.standard_normal((T, H)).astype(np.float16)).to(cuda_device))
+        lgs.append(torch.from_numpy(rng.standard_normal((T, E)).astype(np.float16)).to(cuda_device))
+        layers[r].prepare(xs[r], router_logits=lgs[r])
+    exchange([l.send_ids for l in layers], [l.recv_ids for l in layers], world)
+    exchange([l.send_rows for l in layers], [l.recv_rows for l in layers], world)
+    for l in layers:
+        l.compute()
+    exchange([l.y_rows for l in layers], [l.back_rows for l in layers], world)
+    for r in range(world):
+        out = layers[r].finish()
+        single = pkg.ops.moe_forward(xs[r], w13, w2, k, router_logits=lgs[r], regime=pkg.REGIME_GEMV, w13_bias=b13, w2_bias=b2)
+        assert torch.equal(out, single)
+
+
 def test_ep_pack_layout_and_overflow_flag(pkg, cuda_device):
     ep = importlib.import_module("gpt-oss-vllm_b200.ep")
     E, H, I, k, T, world = 8, 64, 64, 2, 12, 4
