@@ -135,6 +135,16 @@ __device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.w
 // grid_dep_wait() until this grid has completed): launch latency, CTA rasterisation and the next kernel's input-independent
 // prologue overlap this kernel.  Called first thing by every kernel that is launched with launch_pdl().
 __device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// A load of something the PREVIOUS kernel wrote, for kernels launched with launch_pdl().  Through a `const T* __restrict__`
+// parameter (or __ldg) the compiler treats the location as invariant for the whole kernel and may hoist the load ABOVE
+// grid_dep_wait() -- it did, for the bucket metadata in permute_rows_kernel (round 2: LDG.E.CONSTANT ahead of ACQBULK in the
+// SASS, stale routing under back-to-back launches).  This form stays where it is written; tests/test_abi_host.py scans the
+// built library's SASS for global loads ahead of the wait.
+__device__ __forceinline__ int ld_dep_s32(const int32_t* p) {
+  int v;
+  asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {

@@ -81,19 +81,6 @@ inline bool make_map_x3d(CUtensorMap* m, const void* ptr, uint64_t cols, uint64_
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-struct DecArgs {
-  QW w;
-  void* out;
-  const int32_t* sorted_pairs;
-  const int32_t* meta;
-  const int32_t* tile_list;
-  int act;
-  const __half* bias;   // w13 only, optional: fp16 [E, rows] up-projection bias, added (fp16) before the fused SwiGLU
-  int32_t* status;      // optional device word: bit 1 is raised when the shared-memory plan does not fit (nothing is computed then)
-  long long* dbg;       // NF4MOE_EXPERIMENTS builds only
-  int b3d;              // the activation maps are the 3-D form (one TMA per stage) rather than 2-D (one per k-block)
-  int hole_code2;       // FAST + nested + one code2 table for all experts: the table sits, per lane, in the decode table's holes
-};
 
 // ---- shared-memory plan -------------------------------------------------------------------------------------------------
 // Two regions around the 64 KB-aligned decode table: [align1024(base), lut) and [lut + 64 KB, base + kDecSmemBytes).  Wanted:
@@ -154,6 +141,25 @@ __host__ __device__ inline bool dec_plan(uint32_t base, uint32_t lut, int nkb, b
   p->n_raw = 0;
   return false;
 }
+
+struct DecArgs {
+  QW w;
+  void* out;
+  const int32_t* sorted_pairs;
+  const int32_t* meta;
+  const int32_t* tile_list;
+  int act;
+  const __half* bias;   // w13 only, optional: fp16 [E, rows] up-projection bias, added (fp16) before the fused SwiGLU
+  int32_t* status;      // optional device word: bit 1 is raised when the shared-memory plan does not fit (nothing is computed then)
+  long long* dbg;       // NF4MOE_EXPERIMENTS builds only
+  int b3d;              // the activation maps are the 3-D form (one TMA per stage) rather than 2-D (one per k-block)
+  int hole_code2;       // FAST + nested + one code2 table for all experts: the table sits, per lane, in the decode table's holes
+  // The shared-memory plans, computed on the host for the two places the dynamic shared memory can start (1 KB / 2 KB into the
+  // CTA's window) x the two MMA widths (16 / 32): a lone device thread needs ~1.5 us for dec_plan(), on the critical path of
+  // every launch.  The kernel falls back to computing it only if its window starts somewhere else.
+  uint32_t plan_base[2];
+  DecPlan plan[4];      // [base index * 2 + (bmax == 32)]
+};
 
 // barrier slots
 //   RFull[i]  <- TMA bytes of raw stage i AND of the matching activation stage (one expect_tx): waited on by the dequant warps
@@ -219,7 +225,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
   // ---- one-time setup ----
   if (tid == 0) {
-    if (!dec_plan(base, lut, nkb, nested, !hole, bmax, &s_plan) && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
+    const int bi = base == a.plan_base[0] ? 0 : base == a.plan_base[1] ? 1 : -1;
+    if (bi >= 0) s_plan = a.plan[bi * 2 + (bmax == 32 ? 1 : 0)];
+    else dec_plan(base, lut, nkb, nested, !hole, bmax, &s_plan);
+    if (s_plan.n_raw == 0 && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
     for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
     for (int i = 0; i < kDecMaxB; ++i) mbar_init(bar(kDbDone + i), 1);
     for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecStageWarps);
@@ -556,16 +565,6 @@ inline bool dec_serves(int T, int k, int E, int mode) {
   return (mode == NF4MOE_GEMM_FAST || mode == NF4MOE_GEMM_EXACT) && gemm_tile_tokens(T, k, E) <= 32;
 }
 
-// Does the pipeline fit in shared memory for this K / absmax form, whatever the largest token tile turns out to be?  The
-// dynamic shared memory starts 1 KB (static control block) or 2 KB (+ the 1 KB the driver reserves) into the CTA's window.
-inline bool dec_shape_fits(int nkb, bool nested, bool stage_code2) {
-  DecPlan p;
-  for (uint32_t base : {1024u, 2048u})
-    for (int bmax : {16, 32})
-      if (!dec_plan(base, kGemmLutBytes, nkb, nested, stage_code2, bmax, &p)) return false;
-  return true;
-}
-
 template <bool W13>
 int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
                const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err, size_t err_len,
@@ -603,8 +602,12 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   a.status = status ? status : const_cast<int32_t*>(meta) + 4;
   a.dbg = gemm_debug_buffer();
   a.hole_code2 = fast && nested && w->code2_stride == 0;
-  if (!dec_shape_fits(a.w.nkb, nested, nested && !a.hole_code2))
-    return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form");
+  for (int bi = 0; bi < 2; ++bi) {
+    a.plan_base[bi] = bi ? 2048u : 1024u;
+    for (int wide = 0; wide < 2; ++wide)
+      if (!dec_plan(a.plan_base[bi], kGemmLutBytes, a.w.nkb, nested, nested && !a.hole_code2, wide ? 32 : 16, &a.plan[bi * 2 + wide]))
+        return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form");
+  }
   CUtensorMap map_w, map_x16, map_x32;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");

@@ -402,7 +402,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a)
 // reference-variant activation on a raw [n, 2I] buffer: silu(h[:, :I]) * h[:, I:]  (P/unsloth_to_vllm_converter.py:312-315)
 __global__ void __launch_bounds__(256) chunk_silu_kernel(const __half* __restrict__ raw, const int32_t* __restrict__ meta,
                                                          int I, __half* __restrict__ h) {
-  const long long total = (long long)meta[1] * I;
+  const long long total = (long long)ld_dep_s32(meta + 1) * I;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const long long r = i / I, c = i - r * I;
@@ -418,7 +418,7 @@ __global__ void __launch_bounds__(256) bias_act_kernel(const __half* __restrict_
                                                        const int32_t* __restrict__ meta, int I, int act, __half* __restrict__ h) {
   grid_dep_launch();
   grid_dep_wait();
-  const long long total = (long long)meta[1] * I;
+  const long long total = (long long)ld_dep_s32(meta + 1) * I;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const long long r = i / I, c = i - r * I;

@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(128) permute_rows_kernel(const __half* __restr
                                                            __half* __restrict__ xs) {
   grid_dep_launch();
   grid_dep_wait();
-  const int n_kept = meta[1];
+  const int n_kept = ld_dep_s32(meta + 1);
   const int vec = H / 8;
   // rows past the kept pairs are only ever read as padding of the LAST token tile (<= 256 rows): zero that much, not a whole
   // mostly empty fixed-capacity buffer

@@ -88,6 +88,33 @@ def test_shipped_library_reads_no_environment_on_the_launch_path():
     assert "NF4MOE_LIB" not in open(os.path.join(ROOT, "gpt-oss-vllm_b200", "_lib.py")).read()
 
 
+def test_no_global_load_ahead_of_the_grid_dependency_wait(pkg):
+    """Kernels launched with programmatic dependent launch start while their predecessor is still running; everything they
+    read from it must be loaded AFTER griddepcontrol.wait (SASS: ACQBULK).  The compiler may hoist loads through
+    `const __restrict__` pointers above the wait (round 2: permute_rows_kernel read stale bucket metadata that way), so the built
+    library's SASS is scanned: no global / TMA load may precede the first ACQBULK, except the decode kernel's copy of the
+    constant code2 table (weights, written before any launch)."""
+    import shutil
+    import subprocess
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    lib = os.path.join(os.path.dirname(pkg.__file__), "libnf4moe.so")
+    sass = subprocess.run([cuobjdump, "-sass", lib], capture_output=True, text=True, check=True).stdout
+    checked = 0
+    for part in re.split(r"\n\s*Function : ", sass)[1:]:
+        name = part.split("\n", 1)[0]
+        ins = re.findall(r"/\*[0-9a-f]{4,}\*/\s+(.*?);", part)
+        acq = [i for i, t in enumerate(ins) if "ACQBULK" in t]
+        if not acq:
+            continue
+        checked += 1
+        early = [t.strip() for t in ins[:acq[0]] if re.search(r"\bLDG|\bLD\.|UTMALDG|UBLKCP|LDGSTS", t)]
+        allowed = 1 if "dec_kernel" in name else 0
+        assert len(early) <= allowed, f"{name}: loads ahead of the dependency wait: {early}"
+    assert checked >= 10, "expected the PDL kernels (route, bucket, permute, GEMV, tcgen05, combine) in the library"
+
+
 def test_config_and_create_weights_mirror_reference(pkg):
     cfg = pkg.B200NF4MoEConfig()
     assert cfg.get_name() == "bnb_moe_4bit"                                 # P/bnb_moe_4bit.py:33

@@ -197,8 +197,8 @@ def test_bitsandbytes_cross_check_or_recorded_absence(pkg, cuda_device):
 def test_decode_kernel_exact_operand_is_bit_exact_dequant(pkg, cuda_device, nested):
     """One-hot activations through the DECODE-regime tcgen05 kernel (token tiles <= 32 rows) in EXACT mode return the
     dequantised weight columns themselves: the A operand must be bit-identical to bnb's dequantize_4bit; K = 320 (5 k-blocks:
-    one full 4-block stage + a padded one) and rows % 128 != 0."""
-    E, H, I, k = 2, 320, 96, 1
+    one full 4-block stage + a padded one), 3 row tiles."""
+    E, H, I, k = 2, 320, 192, 1
     st13, st2, w13, w2 = make_layer(pkg, cuda_device, 157, E, H, I)
     T = 24                                        # 12 tokens per expert -> 32-row tiles -> dec_kernel
     d13 = np.stack([orc.dequant_state(s) for s in st13])      # [E, 2I, H]
