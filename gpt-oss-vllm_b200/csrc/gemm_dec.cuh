@@ -28,7 +28,7 @@
 namespace nf4moe {
 
 #ifndef NF4MOE_DEC_GROUPS
-#define NF4MOE_DEC_GROUPS 4
+#define NF4MOE_DEC_GROUPS 3
 #endif
 #ifndef NF4MOE_DEC_SPLIT
 #define NF4MOE_DEC_SPLIT 1
@@ -120,24 +120,31 @@ __host__ __device__ inline bool dec_plan_try(uint32_t base, uint32_t lut, uint32
   p->n_b = n_b;
   p->n_raw = 0;
   for (int i = 0; i < kDecMaxRaw; ++i) { const uint32_t at = place(kDecRawBytes); if (!at) break; p->raw[p->n_raw++] = at; }
-  return p->n_raw >= 2;
+  // A raw stage must always be consumed by the SAME dequant group (stage cs -> group cs % kDecGroups, raw slot cs % n_raw): an
+  // mbarrier parity wait is only sound when the waiter has itself seen the slot's previous phase complete; a group that met
+  // the slot for the first time at its second use took "nothing has landed yet" for "landed" (round 2: wrong results and
+  // faults with 2 or 3 raw stages under 4 groups).  So: a multiple of the group count.
+  p->n_raw = p->n_raw / kDecGroups * kDecGroups;
+  return p->n_raw >= kDecGroups;
 }
 
-// bmax = largest MMA N of the launch (16 or 32).  Takes the deepest activation ring that still leaves >= 4 raw stages; failing
-// that, the plan with the most raw stages (>= 2).  Returns false when nothing fits (K too large for this pipeline).
+// bmax = largest MMA N of the launch (16 or 32).  Takes the deepest activation ring that still leaves one raw stage per
+// dequant group (measured, K = 2880 nested, 64 tokens: 3 raw stages 80.4 us vs 6 raw stages 79.7 us per w13 launch, but 3
+// activation stages 91.6 us vs 6 stages 79.7 us: the activation ring is what has to be deep, its slots are only released by
+// retiring MMAs).  The activation ring is never shorter
+// than the group count either: a dequant warp waits on Done[stage - 3] knowing only that Done[stage - 3 - groups] completed,
+// which covers the barrier's previous phase (stage - 3 - n_b) only if n_b >= groups.  Returns false when nothing fits (K too
+// large for this pipeline).
 __host__ __device__ inline bool dec_plan(uint32_t base, uint32_t lut, int nkb, bool nested, bool stage_code2, int bmax, DecPlan* p) {
   p->m_bytes = dec_absmax_stage_bytes(nkb, nested, stage_code2, &p->m_code2);
   p->b_stage = 4u * (uint32_t)bmax * 128u;
   const int want_b = bmax == 16 ? kDecMaxB : 5;
-  DecPlan best = *p;
-  best.n_raw = 0;
-  for (int n_b = want_b; n_b >= 3; --n_b) {
+  for (int n_b = want_b; n_b >= (kDecGroups > 3 ? kDecGroups : 3); --n_b) {
     DecPlan t = *p;
     if (!dec_plan_try(base, lut, p->m_bytes, p->b_stage, n_b, &t)) continue;
-    if (t.n_raw >= 4) { *p = t; return true; }
-    if (t.n_raw > best.n_raw) best = t;
+    *p = t;   // dec_plan_try only succeeds with n_raw >= kDecGroups
+    return true;
   }
-  if (best.n_raw >= 2) { *p = best; return true; }
   p->n_raw = 0;
   return false;
 }
@@ -162,14 +169,16 @@ struct DecArgs {
 };
 
 // barrier slots
-//   RFull[i]  <- TMA bytes of raw stage i AND of the matching activation stage (one expect_tx): waited on by the dequant warps
-//                that own the stage; the MMA thread never waits on it (its wait on AFull is causally after all of theirs)
+//   RFull[i]  <- TMA bytes of raw stage i: waited on by the dequant warps that own the stage
+//   BFull[c]  <- TMA bytes of activation stage c (ring of n_b): waited on by the MMA thread.  (Round 2 first counted them on
+//                RFull, so that the MMA thread had a single wait; but then a stage's dequant could not start before its
+//                activations had landed, and those are only requested once the MMAs n_b stages back retire.)
 //   REmpty[i] <- the stage's dequant warps, as soon as their LDS.128 are done (the stage refills while they decode)
 //   AFull[s]  <- the stage's dequant warps, A operand of the stage written to TMEM slot s
 //   Done[c]   <- ONE tcgen05.commit per stage (ring of n_b): frees A slot c % 3 for the dequant warps of stage + 3
 //                and activation stage c for the producer of stage + n_b
 constexpr int kDbRFull = 0, kDbREmpty = kDbRFull + kDecMaxRaw, kDbDone = kDbREmpty + kDecMaxRaw,
-              kDbAFull = kDbDone + kDecMaxB, kDbDFull = kDbAFull + kDecSlots, kDbDEmpty = kDbDFull + 2,
+              kDbBFull = kDbDone + kDecMaxB, kDbAFull = kDbBFull + kDecMaxB, kDbDFull = kDbAFull + kDecSlots, kDbDEmpty = kDbDFull + 2,
               kDbMFull = kDbDEmpty + 2, kDbMEmpty = kDbMFull + 2, kNumDecBars = kDbMEmpty + 2;
 
 __device__ __forceinline__ void ring_advance(int& idx, uint32_t& phase, int step, int n) {
@@ -194,6 +203,13 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   __shared__ DecPlan s_plan;
   grid_dep_launch();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // DBG builds: a timeline (globaltimer, ns) of CTA 0 (slots 32..) and of the last CTA (slots 48..) -- see scripts/dec_roles.py
+  const bool tl_on = DBG && a.dbg != nullptr && lane == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1);
+  long long* tl = DBG && a.dbg != nullptr ? a.dbg + (blockIdx.x == 0 ? 32 : 48) : nullptr;
+  auto stamp = [&](int i) {
+    if (DBG && tl_on) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tl[i] = (long long)t; }
+  };
+  if (tid == 0) stamp(0);
   const int nkb = a.w.nkb;
   const int nst = (nkb + 3) >> 2;                       // stages per item (the last one may be partly padding)
   const bool nested = a.w.absmax_f32 == nullptr;
@@ -206,22 +222,38 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   // ---- prologue that depends on nothing the previous kernel wrote: decode table (weights are constants), TMEM allocation.
   // Under programmatic dependent launch it overlaps the previous kernel's tail; everything below the wait may read bucket /
   // GEMM outputs ----
-  for (int i = tid; i < 256 * 32; i += kDecThreads) {
-    const int b = i >> 5, l = i & 31;
-    if (FAST) {
-      sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
-      if (hole) sts32(lut + (uint32_t)b * 256u + 128u + (uint32_t)l * 4u, __float_as_uint(__ldg(a.w.code2 + b)));
-    } else {
-      const uint32_t p = lut + (uint32_t)b * 256u + (uint32_t)l * 8u;
-      sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
-      sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
+  {
+    constexpr int kFill = (256 * 32 + kDecThreads - 1) / kDecThreads;
+    float c2[kFill];
+    if (hole) {   // all of a thread's code2 loads in flight at once (one dependent round trip per row cost 2 us per launch)
+#pragma unroll
+      for (int j = 0; j < kFill; ++j) {
+        const int i = tid + j * kDecThreads;
+        c2[j] = i < 256 * 32 ? __ldg(a.w.code2 + (i >> 5)) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kFill; ++j) {
+      const int i = tid + j * kDecThreads;
+      if (i >= 256 * 32) break;
+      const int b = i >> 5, l = i & 31;
+      if (FAST) {
+        sts32(lut + (uint32_t)b * 256u + (uint32_t)l * 4u, pack_half2(kNF4[b >> 4], kNF4[b & 15]));
+        if (hole) sts32(lut + (uint32_t)b * 256u + 128u + (uint32_t)l * 4u, __float_as_uint(c2[j]));
+      } else {
+        const uint32_t p = lut + (uint32_t)b * 256u + (uint32_t)l * 8u;
+        sts32(p, __float_as_uint(kNF4[b >> 4]));        // element 2j   (high nibble)
+        sts32(p + 4u, __float_as_uint(kNF4[b & 15]));   // element 2j+1 (low nibble)
+      }
     }
   }
   if (warp == kDecWarpMma) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  if (tid == 0) stamp(1);
   grid_dep_wait();
+  if (tid == 0) stamp(2);
   const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
   // ---- one-time setup ----
   if (tid == 0) {
@@ -230,7 +262,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     else dec_plan(base, lut, nkb, nested, !hole, bmax, &s_plan);
     if (s_plan.n_raw == 0 && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
     for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
-    for (int i = 0; i < kDecMaxB; ++i) mbar_init(bar(kDbDone + i), 1);
+    for (int i = 0; i < kDecMaxB; ++i) { mbar_init(bar(kDbDone + i), 1); mbar_init(bar(kDbBFull + i), 1); }
     for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecStageWarps);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(kDbDFull + i), 1); mbar_init(bar(kDbDEmpty + i), 4);
@@ -241,6 +273,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (tid == 0) stamp(3);
   const uint32_t tmem = s_tmem;
   const int n_raw = s_plan.n_raw, n_b = s_plan.n_b;
   const uint32_t b_ring = s_plan.b0, b_stage = s_plan.b_stage, m_code2 = s_plan.m_code2;
@@ -294,6 +327,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
       for (; st < nst; st += kDecGroups) {
         mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
+        if (DBG && warp == 0 && it == 0 && st == 0) stamp(4);
         GEMM_DBG_ADD(1);
         const uint32_t wst = pin(s_plan.raw[sw]);
         const int kb0 = st * 4 + hh * kDecKpw;
@@ -364,6 +398,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         bu2 = u | (u << 16);
       }
       mbar_wait(bar(kDbDFull + db), (uint32_t)(it >> 1) & 1u);
+      if (DBG && q == 0) stamp(it == 0 ? 6 : 7);          // first / last accumulator finished
       tc_fence_after();
       const bool row_ok = n < a.w.rows;
       uint32_t v[32];
@@ -445,16 +480,12 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
           __syncwarp();
         }
         GEMM_DBG_ADD(0);
-        const int n_tok = a.tile_list[4 * tile + 2];
-        const uint32_t b_tile = n_tok <= 16 ? 2048u : 4096u;
         for (int st = 0; st < nst; ++st) {
           mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);          // the dequant warps of the stage n_raw back have read it
           GEMM_DBG_ADD(1);
-          const int nreal = min(4, nkb - st * 4);
           if (elect_one()) {
             const uint32_t full = rfull0 + 8u * (uint32_t)sw;
-            // the activation producer adds its bytes to the same barrier; a 3-D box always delivers 4 tiles (zero-filled)
-            mbar_expect_tx(full, kDecRawBytes + (uint32_t)(a.b3d ? 4 : nreal) * b_tile);
+            mbar_expect_tx(full, kDecRawBytes);
             tma_load_2d(s_plan.raw[sw], &map_w, st * 128, c1, full);
           }
           __syncwarp();
@@ -465,12 +496,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[24 + i] = dbg_acc[i];
     } else if (warp == kDecWarpAct) {
       // =============================== TMA producer: activations per stage ===============================
-      // Its bytes complete on the SAME barrier as the stage's raw NF4 (the raw producer's expect_tx covers both), so the dequant
-      // warps' one wait covers both and the MMA thread waits on nothing but AFull.  It waits for REmpty too: the barrier's
-      // previous phase (stage cs - n_raw) must be over before bytes of stage cs may be counted on it.
-      const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), done0 = bar(kDbDone);
-      int sw = 0, sb = 0;
-      uint32_t phw = 0, phb = 0;
+      // Runs n_b stages ahead of the MMAs, independent of the raw-weight ring.
+      const uint32_t bfull0 = bar(kDbBFull), done0 = bar(kDbDone);
+      int sb = 0;
+      uint32_t phb = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
         const int tile = item / n_row_tiles;
         const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
@@ -478,11 +507,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         const uint32_t b_tile = (uint32_t)nb * 128u;
         const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
         for (int st = 0; st < nst; ++st) {
-          mbar_wait(rempty0 + 8u * (uint32_t)sw, phw ^ 1u);
           mbar_wait(done0 + 8u * (uint32_t)sb, phb ^ 1u);            // the MMAs of the stage n_b back have read its activations
           const int nreal = min(4, nkb - st * 4);
           if (elect_one()) {
-            const uint32_t full = rfull0 + 8u * (uint32_t)sw, dst = b_ring + (uint32_t)sb * b_stage;
+            const uint32_t full = bfull0 + 8u * (uint32_t)sb, dst = b_ring + (uint32_t)sb * b_stage;
+            mbar_expect_tx(full, (uint32_t)(a.b3d ? 4 : nreal) * b_tile);   // a 3-D box always delivers 4 tiles (zero-filled)
             if (a.b3d) {
               tma_load_3d(dst, map_x, 0, row0, st * 4, full);
             } else {
@@ -490,7 +519,6 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
             }
           }
           __syncwarp();
-          if (++sw == n_raw) { sw = 0; phw ^= 1u; }
           if (++sb == n_b) { sb = 0; phb ^= 1u; }
         }
       }
@@ -499,12 +527,12 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       // A lone warp runs at one dependent instruction per ~6 cycles and every mbarrier / tcgen05 instruction costs it 60-100, so
       // this loop is kept to one wait, the MMAs (running addresses, constant accumulate flag except in an item's first stage)
       // and one commit per stage.
-      const uint32_t afull0 = bar(kDbAFull), done0 = bar(kDbDone);
+      const uint32_t afull0 = bar(kDbAFull), done0 = bar(kDbDone), bfull0 = bar(kDbBFull);
       const uint32_t desc_hi = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version 1, SWIZZLE_128B
       const uint32_t blo0 = (b_ring & 0x3FFFFu) >> 4, bstep = b_stage >> 4;
       const uint32_t a_t0 = tmem + acol0;
       int sb = 0, slot = 0, it = 0;
-      uint32_t pha = 0;
+      uint32_t pha = 0, phb = 0;
       auto issue = [&](const uint32_t d_t, const uint32_t a_t, const uint32_t b_lo, const uint32_t blo_step, const uint32_t idesc,
                        const int nreal, const bool first) {
 #pragma unroll
@@ -529,7 +557,9 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         mbar_wait(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
         GEMM_DBG_ADD(0);
         for (int st = 0; st < nst; ++st) {
-          mbar_wait(afull0 + 8u * (uint32_t)slot, pha);     // A operand written by the stage's dequant warps (who saw its TMA land)
+          mbar_wait(bfull0 + 8u * (uint32_t)sb, phb);       // activations landed (long ago, normally: they run n_b stages ahead)
+          mbar_wait(afull0 + 8u * (uint32_t)slot, pha);     // A operand written by the stage's dequant warps
+          if (DBG && it == 0 && st == 0) stamp(5);
           tc_fence_after();
           GEMM_DBG_ADD(2);
           const int nreal = min(4, nkb - st * 4);
@@ -543,7 +573,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
           __syncwarp();
           GEMM_DBG_ADD(3);
           if (++slot == kDecSlots) { slot = 0; pha ^= 1u; }
-          if (++sb == n_b) sb = 0;
+          if (++sb == n_b) { sb = 0; phb ^= 1u; }
         }
       }
       if (dbg_on) for (int i = 0; i < 6; ++i) a.dbg[16 + i] = dbg_acc[i];
@@ -551,8 +581,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   }
 
   // ---- teardown ----
+  if (DBG && warp == kDecDqWarps) stamp(8);               // epilogue warp 0 done with its stores
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) stamp(9);
   if (warp == kDecWarpMma) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
@@ -608,6 +640,12 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
       if (!dec_plan(a.plan_base[bi], kGemmLutBytes, a.w.nkb, nested, nested && !a.hole_code2, wide ? 32 : 16, &a.plan[bi * 2 + wide]))
         return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form");
   }
+#ifdef NF4MOE_EXPERIMENTS
+  for (int i = 0; i < 4; ++i) {   // shallower rings for pipeline-depth measurements
+    a.plan[i].n_raw = std::max(kDecGroups, std::min(a.plan[i].n_raw, experiment_env("NF4MOE_DEC_MAXRAW", kDecMaxRaw)) / kDecGroups * kDecGroups);
+    a.plan[i].n_b = std::max(std::max(3, kDecGroups), std::min(a.plan[i].n_b, experiment_env("NF4MOE_DEC_MAXB", kDecMaxB)));
+  }
+#endif
   CUtensorMap map_w, map_x16, map_x32;
   if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
     return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");

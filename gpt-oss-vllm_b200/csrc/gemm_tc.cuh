@@ -816,6 +816,9 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.kps = a.tile_tokens <= 32 ? 4 : 2;
   a.n_a = std::min(kMaxAStages, (512 - 2 * a.tile_tokens) / (32 * a.kps));
   a.want_b = a.tile_tokens <= 32 ? 12 : 4;
+  // a dequant group must meet every use of an A slot it waits on (mbarrier parity waits are only sound for a waiter that saw the
+  // previous phase complete): the ring of n_a x kps k-blocks has to be a whole number of rounds over the groups
+  if ((a.n_a * a.kps) % kDqGroups) return fail(NF4MOE_EINVAL, "token-tile size leaves an A-operand ring the dequant groups do not divide");
   a.dbg = gemm_debug_buffer();
   a.status = status ? status : const_cast<int32_t*>(meta) + 4;
   {   // the dynamic shared memory starts 1 KB (static control block) or 2 KB (+ the driver's reserved 1 KB) into the window
