@@ -26,7 +26,7 @@ EXPORTED = (
     "nf4moe_workspace_status_offset", "nf4moe_expert_rows_bias", "nf4moe_combine_indexed_bias",
     "nf4moe_ep_dispatch_p2p", "nf4moe_ep_return_p2p", "nf4moe_ep_wait",
 )
-STATUS_EP_OVERFLOW, STATUS_DEC_NOFIT, STATUS_GEMM_NOFIT, STATUS_EP_TIMEOUT = 1, 2, 4, 8
+STATUS_EP_OVERFLOW, STATUS_DEC_NOFIT, STATUS_GEMM_NOFIT, STATUS_EP_TIMEOUT, STATUS_DEP_TIMEOUT = 1, 2, 4, 8, 16
 
 
 class Nf4MoeError(RuntimeError):

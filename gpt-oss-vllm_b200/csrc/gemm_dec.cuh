@@ -149,12 +149,24 @@ __host__ __device__ inline bool dec_plan(uint32_t base, uint32_t lut, int nkb, b
   return false;
 }
 
-struct DecArgs {
+// One launch serves the up projection (side 0: w13, SwiGLU epilogue, output h in sorted-row order), the down projection
+// (side 1: w2, output scattered to (token, slot) rows), or BOTH (template SIDES = 2): the persistent CTAs walk the w13 items
+// and carry straight on into the w2 items, whose activations are the h rows other CTAs have just written.  A w2 item of token
+// tile t may start once all row tiles of w13 for tile t are stored: the w13 epilogue counts them in tile_list[4 t + 3] (zeroed
+// by the bucket kernel), the activation producer of the w2 item spins on that word.  All w13 items precede all w2 items in
+// every CTA's sequence and every CTA is resident (one per SM), so the wait cannot deadlock; the weights of the first w2 items
+// stream in while the last w13 items are still being multiplied, which is the point: two separate launches pay the pipeline
+// fill, the drain and the launch gap twice (7.6 us from CTA entry to the first MMA + ~1 us drain, measured, of a 79 + 46 us
+// pair).
+struct DecSide {
   QW w;
   void* out;
+};
+struct DecArgs {
+  DecSide s[2];
   const int32_t* sorted_pairs;
   const int32_t* meta;
-  const int32_t* tile_list;
+  int32_t* tile_list;   // [4 t + 3] is the tile's count of finished w13 row tiles when SIDES = 2
   int act;
   const __half* bias;   // w13 only, optional: fp16 [E, rows] up-projection bias, added (fp16) before the fused SwiGLU
   int32_t* status;      // optional device word: bit 1 is raised when the shared-memory plan does not fit (nothing is computed then)
@@ -193,10 +205,14 @@ __device__ __forceinline__ void ring_advance(int& idx, uint32_t& phase, int step
 //   next 4 warps             epilogue
 //   then                     TMA producer (absmax per item; raw NF4 per stage), MMA issuer (+ TMEM allocator), TMA producer
 //                            of the activation stages, one idle warp
-template <bool W13, bool FAST, bool DBG>
-__global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, const __grid_constant__ CUtensorMap map_w,
+// SIDES: 0 = w13 only, 1 = w2 only, 2 = w13 then w2 (see DecSide).  The tensor maps of the side that is not served are unused.
+template <int SIDES, bool FAST, bool DBG>
+__global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, const __grid_constant__ CUtensorMap map_w13,
                                                             const __grid_constant__ CUtensorMap map_x16,
-                                                            const __grid_constant__ CUtensorMap map_x32) {
+                                                            const __grid_constant__ CUtensorMap map_x32,
+                                                            const __grid_constant__ CUtensorMap map_w2,
+                                                            const __grid_constant__ CUtensorMap map_h16,
+                                                            const __grid_constant__ CUtensorMap map_h32) {
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumDecBars];
   __shared__ uint32_t s_tmem;
@@ -210,9 +226,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     if (DBG && tl_on) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tl[i] = (long long)t; }
   };
   if (tid == 0) stamp(0);
-  const int nkb = a.w.nkb;
-  const int nst = (nkb + 3) >> 2;                       // stages per item (the last one may be partly padding)
-  const bool nested = a.w.absmax_f32 == nullptr;
+  constexpr int kSide0 = SIDES == 1 ? 1 : 0;            // the first (or only) side of this launch
+  const bool nested = a.s[kSide0].w.absmax_f32 == nullptr;   // both sides of a launch use the same absmax form
   const bool hole = FAST && a.hole_code2 != 0;
   const uint32_t base = smem_u32(dyn_smem);
   const uint32_t lut = pin((base + kGemmLutBytes - 1u) & ~(kGemmLutBytes - 1u));
@@ -229,7 +244,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 #pragma unroll
       for (int j = 0; j < kFill; ++j) {
         const int i = tid + j * kDecThreads;
-        c2[j] = i < 256 * 32 ? __ldg(a.w.code2 + (i >> 5)) : 0.f;
+        c2[j] = i < 256 * 32 ? __ldg(a.s[kSide0].w.code2 + (i >> 5)) : 0.f;   // SIDES = 2: both sides share the table (host-checked)
       }
     }
 #pragma unroll
@@ -259,7 +274,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   if (tid == 0) {
     const int bi = base == a.plan_base[0] ? 0 : base == a.plan_base[1] ? 1 : -1;
     if (bi >= 0) s_plan = a.plan[bi * 2 + (bmax == 32 ? 1 : 0)];
-    else dec_plan(base, lut, nkb, nested, !hole, bmax, &s_plan);
+    else dec_plan(base, lut, SIDES == 2 ? max(a.s[0].w.nkb, a.s[1].w.nkb) : a.s[kSide0].w.nkb, nested, !hole, bmax, &s_plan);
     if (s_plan.n_raw == 0 && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
     for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
     for (int i = 0; i < kDecMaxB; ++i) { mbar_init(bar(kDbDone + i), 1); mbar_init(bar(kDbBFull + i), 1); }
@@ -276,9 +291,24 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
   if (tid == 0) stamp(3);
   const uint32_t tmem = s_tmem;
   const int n_raw = s_plan.n_raw, n_b = s_plan.n_b;
-  const uint32_t b_ring = s_plan.b0, b_stage = s_plan.b_stage, m_code2 = s_plan.m_code2;
-  const int n_row_tiles = (a.w.rows + kGemmRowTile - 1) / kGemmRowTile;
-  const int n_items = n_raw > 0 ? a.meta[2] * n_row_tiles : 0;
+  const uint32_t b_ring = s_plan.b0, b_stage = s_plan.b_stage;
+  // Items: (token tile, 128-row weight tile) of the first side, tile-major; with SIDES = 2 the second side's items follow.
+  const int nrt0 = (a.s[kSide0].w.rows + kGemmRowTile - 1) / kGemmRowTile;
+  const int nrt1 = SIDES == 2 ? (a.s[1].w.rows + kGemmRowTile - 1) / kGemmRowTile : 0;
+  const int n_items0 = n_raw > 0 ? a.meta[2] * nrt0 : 0;
+  const int n_items = n_items0 + (n_raw > 0 ? a.meta[2] * nrt1 : 0);
+  auto item_of = [&](int item, int& side, int& tile, int& rt) {
+    if (SIDES == 2 && item >= n_items0) {
+      side = 1;
+      item -= n_items0;
+      tile = item / nrt1;
+      rt = item - tile * nrt1;
+    } else {
+      side = kSide0;
+      tile = item / nrt0;
+      rt = item - tile * nrt0;
+    }
+  };
   const uint32_t acol0 = 2u * kDecAccCols;   // TMEM: accumulators at columns 0 and 32, A slots after them
   const bool dbg_on = DBG && a.dbg != nullptr && blockIdx.x == 0 && lane == 0;   // DBG = false: every counter below folds away
   long long dbg_acc[6] = {0, 0, 0, 0, 0, 0};
@@ -305,7 +335,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     ring_advance(sw, phw, pp, max(n_raw, 1));
     ring_advance(dn, pdn, pp + n_b - 3, max(n_b, 1));
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+      int side, tile, rt;
+      item_of(item, side, tile, rt);
+      const QW& w = a.s[side].w;
+      const int nkb = w.nkb, nst = (nkb + 3) >> 2;          // stages of this item (the last one may be partly padding)
       const int e = a.tile_list[4 * tile];
       const int n = rt * kGemmRowTile + r;
       const int mb = it & 1;
@@ -313,11 +346,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       float a2_lo = 0.f, a2_hi = 0.f, off_e = 0.f;
       long long blk_hi = 0;
       if (nested) {
-        const long long blk0 = (long long)min(n, a.w.rows - 1) * nkb;
+        const long long blk0 = (long long)min(n, w.rows - 1) * nkb;
         const long long i2 = blk0 >> 8;
-        a2_lo = __ldg(a.w.absmax2 + (long long)e * a.w.n2 + i2);
-        a2_hi = __ldg(a.w.absmax2 + (long long)e * a.w.n2 + min(i2 + 1, a.w.n2 - 1));
-        off_e = __ldg(a.w.offset + e);
+        a2_lo = __ldg(w.absmax2 + (long long)e * w.n2 + i2);
+        a2_hi = __ldg(w.absmax2 + (long long)e * w.n2 + min(i2 + 1, w.n2 - 1));
+        off_e = __ldg(w.offset + e);
         blk_hi = ((i2 + 1) << 8) - blk0;
       }
       GEMM_DBG_T0();
@@ -325,6 +358,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       GEMM_DBG_ADD(0);
       const uint32_t m_st = pin(s_plan.mst[mb]);
       const uint32_t m_row = m_st + (uint32_t)(r * nkb) * (nested ? 1u : 4u);
+      const uint32_t m_code2 = ((uint32_t)(kGemmRowTile * nkb) * (nested ? 1u : 4u) + 15u) & ~15u;   // staged code2 table, if any
       for (; st < nst; st += kDecGroups) {
         mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
         if (DBG && warp == 0 && it == 0 && st == 0) stamp(4);
@@ -386,13 +420,17 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
     int it = 0;
     for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+      int side, tile, rt;
+      item_of(item, side, tile, rt);
+      const bool up_side = side == 0;                       // w13: activation epilogue; w2: scatter epilogue
+      const int w_rows = a.s[side].w.rows;
+      void* const out = a.s[side].out;
       const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
       const int n = rt * kGemmRowTile + r;
       const int db = it & 1;
       uint32_t bg2 = 0u, bu2 = 0u;   // this lane pair's gate / up bias, broadcast to both halves (zero = none)
-      if (W13 && a.bias != nullptr && a.act == NF4MOE_ACT_SWIGLU_OAI && n < a.w.rows) {
-        const __half* be = a.bias + (long long)a.tile_list[4 * tile] * a.w.rows + (n & ~1);
+      if (up_side && a.bias != nullptr && a.act == NF4MOE_ACT_SWIGLU_OAI && n < w_rows) {
+        const __half* be = a.bias + (long long)a.tile_list[4 * tile] * w_rows + (n & ~1);
         const uint32_t g = __half_as_ushort(__ldg(be)), u = __half_as_ushort(__ldg(be + 1));
         bg2 = g | (g << 16);
         bu2 = u | (u << 16);
@@ -400,18 +438,18 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       mbar_wait(bar(kDbDFull + db), (uint32_t)(it >> 1) & 1u);
       if (DBG && q == 0) stamp(it == 0 ? 6 : 7);          // first / last accumulator finished
       tc_fence_after();
-      const bool row_ok = n < a.w.rows;
+      const bool row_ok = n < w_rows;
       uint32_t v[32];
       tmem_ld32(t_lane + (uint32_t)(db * kDecAccCols), v);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(kDbDEmpty + db));   // the accumulator is in registers: hand it back before the stores
-      if (W13 && a.act == NF4MOE_ACT_SWIGLU_OAI) {
+      if (up_side && a.act == NF4MOE_ACT_SWIGLU_OAI) {
         // rows 2j / 2j+1 (gate / up) sit in adjacent lanes; products rounded to fp16 first (the reference stores the GEMM
         // result as fp16 before the activation); even lane takes tokens 0..15, odd lane tokens 16..31 of the tile
-        __half* h = reinterpret_cast<__half*>(a.out);
-        const int I = a.w.rows >> 1;
+        __half* h = reinterpret_cast<__half*>(out);
+        const int I = w_rows >> 1;
         const bool odd = lane & 1;
         uint32_t p[16];
 #pragma unroll
@@ -437,17 +475,24 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
             if (t0 + 2 * i + 1 < n_tok) dst[(long long)(2 * i + 1) * I] = __ushort_as_half((unsigned short)(r2 >> 16));
           }
         }
-      } else if (W13) {
-        __half* raw = reinterpret_cast<__half*>(a.out);
+      } else if (up_side) {
+        __half* raw = reinterpret_cast<__half*>(out);
 #pragma unroll
         for (int i = 0; i < 32; ++i)
-          if (row_ok && i < n_tok) raw[(long long)(row0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
+          if (row_ok && i < n_tok) raw[(long long)(row0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
       } else {
-        __half* y = reinterpret_cast<__half*>(a.out);
+        __half* y = reinterpret_cast<__half*>(out);
 #pragma unroll
         for (int i = 0; i < 32; ++i)
           if (row_ok && i < n_tok)
-            y[(long long)__ldg(a.sorted_pairs + row0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
+            y[(long long)__ldg(a.sorted_pairs + row0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
+      }
+      if (SIDES == 2 && up_side) {
+        // publish this row tile of h: every epilogue thread's stores are ordered before the count (fence, then the four warps
+        // meet on named barrier 1, then ONE release-increment at GPU scope); the w2 items of this token tile wait for all nrt0
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (q == 0 && lane == 0) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(a.tile_list + 4 * tile + 3) : "memory");
       }
     }
   } else {
@@ -456,26 +501,31 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       // =============================== TMA producer: absmax per item, raw NF4 per stage ===============================
       const uint64_t pol = l2_policy_evict_first();   // weights are read exactly once per step
       const uint32_t am_elt = nested ? 1u : 4u;
-      const uint8_t* am_base = nested ? a.w.absmax_u8 : reinterpret_cast<const uint8_t*>(a.w.absmax_f32);
       const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty);
       const bool stage_code2 = nested && !hole;
       int sw = 0, it = 0;
       uint32_t phw = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         GEMM_DBG_T0();
-        const int tile = item / n_row_tiles, rt = item - tile * n_row_tiles;
+        int side, tile, rt;
+        item_of(item, side, tile, rt);
+        const QW& w = a.s[side].w;
+        const int nkb = w.nkb, nst = (nkb + 3) >> 2;
+        const uint8_t* am_base = nested ? w.absmax_u8 : reinterpret_cast<const uint8_t*>(w.absmax_f32);
+        const CUtensorMap* map_w = side == 0 ? &map_w13 : &map_w2;
+        const uint32_t m_code2 = ((uint32_t)(kGemmRowTile * nkb) * am_elt + 15u) & ~15u;
         const int e = a.tile_list[4 * tile];
-        const int c1 = e * a.w.rows + rt * kGemmRowTile;
+        const int c1 = e * w.rows + rt * kGemmRowTile;
         {
           const int mb = it & 1;
-          const int rows_here = min(kGemmRowTile, a.w.rows - rt * kGemmRowTile);
+          const int rows_here = min(kGemmRowTile, w.rows - rt * kGemmRowTile);
           const uint32_t bytes = (uint32_t)(rows_here * nkb) * am_elt;
           mbar_wait(bar(kDbMEmpty + mb), ((uint32_t)(it >> 1) & 1u) ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(bar(kDbMFull + mb), bytes + (stage_code2 ? 1024u : 0u));
-            bulk_g2s(s_plan.mst[mb], am_base + ((long long)e * a.w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
+            bulk_g2s(s_plan.mst[mb], am_base + ((long long)e * w.nb + (long long)rt * kGemmRowTile * nkb) * am_elt, bytes,
                      bar(kDbMFull + mb), pol);
-            if (stage_code2) bulk_g2s(s_plan.mst[mb] + m_code2, a.w.code2 + (long long)e * a.w.code2_stride, 1024u, bar(kDbMFull + mb), pol);
+            if (stage_code2) bulk_g2s(s_plan.mst[mb] + m_code2, w.code2 + (long long)e * w.code2_stride, 1024u, bar(kDbMFull + mb), pol);
           }
           __syncwarp();
         }
@@ -486,7 +536,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
           if (elect_one()) {
             const uint32_t full = rfull0 + 8u * (uint32_t)sw;
             mbar_expect_tx(full, kDecRawBytes);
-            tma_load_2d(s_plan.raw[sw], &map_w, st * 128, c1, full);
+            tma_load_2d(s_plan.raw[sw], map_w, st * 128, c1, full);
           }
           __syncwarp();
           GEMM_DBG_ADD(2);
@@ -501,11 +551,30 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       int sb = 0;
       uint32_t phb = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-        const int tile = item / n_row_tiles;
+        int side, tile, rt;
+        item_of(item, side, tile, rt);
+        const int nkb = a.s[side].w.nkb, nst = (nkb + 3) >> 2;
         const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
         const int nb = n_tok <= 16 ? 16 : 32;
         const uint32_t b_tile = (uint32_t)nb * 128u;
-        const CUtensorMap* map_x = nb == 16 ? &map_x16 : &map_x32;
+        const CUtensorMap* map_x = side == 0 ? (nb == 16 ? &map_x16 : &map_x32) : (nb == 16 ? &map_h16 : &map_h32);
+        if (SIDES == 2 && side == 1) {
+          // the tile's h rows come from the w13 items of this very launch: wait until all nrt0 of them are counted, then order
+          // the (generic-proxy) acquire before the TMA (async-proxy) reads that follow
+          const int32_t* cnt = a.tile_list + 4 * tile + 3;
+          int seen;
+          unsigned int polls = 0;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(cnt) : "memory");
+            if (seen < nrt0) {
+              __nanosleep(100);
+              // every CTA is resident and w13 items wait for nothing, so this ends within microseconds; if the grid was NOT
+              // fully resident (SMs held by something that itself waits for this stream) give up loudly rather than hang
+              if (++polls > (1u << 26)) { if (lane == 0 && a.status) atomicOr(a.status, 16); break; }
+            }
+          } while (seen < nrt0);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         for (int st = 0; st < nst; ++st) {
           mbar_wait(done0 + 8u * (uint32_t)sb, phb ^ 1u);            // the MMAs of the stage n_b back have read its activations
           const int nreal = min(4, nkb - st * 4);
@@ -546,7 +615,9 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         }
       };
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        const int tile = item / n_row_tiles;
+        int side, tile, rt;
+        item_of(item, side, tile, rt);
+        const int nkb = a.s[side].w.nkb, nst = (nkb + 3) >> 2;
         const int n_tok = a.tile_list[4 * tile + 2];
         const int nb = n_tok <= 16 ? 16 : 32;
         const uint32_t idesc = make_idesc(nb);
@@ -597,24 +668,41 @@ inline bool dec_serves(int T, int k, int E, int mode) {
   return (mode == NF4MOE_GEMM_FAST || mode == NF4MOE_GEMM_EXACT) && gemm_tile_tokens(T, k, E) <= 32;
 }
 
-template <bool W13>
-int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
-               const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err, size_t err_len,
-               int* launches, const void* bias = nullptr, int32_t* status = nullptr) {
-  const char* name = W13 ? "gemm_w13(decode)" : "gemm_w2(decode)";
+struct DecHostSide {
+  const nf4moe_qweight* w;
+  const void* act_in;   // fp16 [T * k, w->cols] rows in sorted order
+  void* out;
+};
+
+// SIDES as in dec_kernel: 0 = w13 (hs[0]), 1 = w2 (hs[1]), 2 = both in one launch (hs[1].act_in == hs[0].out: the h rows).
+template <int SIDES>
+int dec_launch_sides(const DecHostSide (&hs)[2], const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T,
+                     int k, int E, int act, int mode, void* stream, char* err, size_t err_len, int* launches, const void* bias,
+                     int32_t* status) {
+  const char* name = SIDES == 0 ? "gemm_w13(decode)" : SIDES == 1 ? "gemm_w2(decode)" : "gemm_w13_w2(decode)";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
-  if (!act_in || !w || !w->packed || !meta || !tile_list || !out || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
-  if (!W13 && !sorted_pairs) return fail(NF4MOE_EINVAL, "sorted_pairs required");
+  constexpr int s_lo = SIDES == 1 ? 1 : 0, s_hi = SIDES == 0 ? 0 : 1;
+  if (!meta || !tile_list || T < 0 || k <= 0 || E <= 0) return fail(NF4MOE_EINVAL, "bad arguments");
+  if (SIDES != 0 && !sorted_pairs) return fail(NF4MOE_EINVAL, "sorted_pairs required");
   if (mode != NF4MOE_GEMM_EXACT && mode != NF4MOE_GEMM_FAST) return fail(NF4MOE_EINVAL, "mode must be NF4MOE_GEMM_EXACT or NF4MOE_GEMM_FAST");
-  if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "cols must be a multiple of 64");
-  if (W13 && (w->rows & 1)) return fail(NF4MOE_EINVAL, "w13 rows must be even");
-  if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "absmax missing");
-  if (w->rows % 16 || w->cols > 4096) return fail(NF4MOE_EINVAL, "the tcgen05 regime needs rows % 16 == 0 and cols <= 4096");
-  if ((reinterpret_cast<uintptr_t>(act_in) & 15u) || (reinterpret_cast<uintptr_t>(w->packed) & 15u) ||
-      (reinterpret_cast<uintptr_t>(w->absmax_f32) & 15u) || (reinterpret_cast<uintptr_t>(w->absmax_u8) & 15u) ||
-      (!w->absmax_f32 && ((reinterpret_cast<uintptr_t>(w->code2) & 15u) || (w->code2_stride & 3))))
-    return fail(NF4MOE_EALIGN, "activations, packed weights, absmax and code2 must be 16-byte aligned");
-  if (W13 && act != NF4MOE_ACT_SWIGLU_OAI && act != NF4MOE_ACT_CHUNK_SILU) return fail(NF4MOE_EINVAL, "bad activation");
+  for (int sd = s_lo; sd <= s_hi; ++sd) {
+    const nf4moe_qweight* w = hs[sd].w;
+    if (!hs[sd].act_in || !w || !w->packed || !hs[sd].out) return fail(NF4MOE_EINVAL, "bad arguments");
+    if (w->rows <= 0 || w->cols <= 0 || w->cols % kBlock) return fail(NF4MOE_EINVAL, "cols must be a multiple of 64");
+    if (sd == 0 && (w->rows & 1)) return fail(NF4MOE_EINVAL, "w13 rows must be even");
+    if (!w->absmax_f32 && !(w->absmax_u8 && w->absmax2 && w->code2 && w->offset)) return fail(NF4MOE_EINVAL, "absmax missing");
+    if (w->rows % 16 || w->cols > 4096) return fail(NF4MOE_EINVAL, "the tcgen05 regime needs rows % 16 == 0 and cols <= 4096");
+    if ((reinterpret_cast<uintptr_t>(hs[sd].act_in) & 15u) || (reinterpret_cast<uintptr_t>(w->packed) & 15u) ||
+        (reinterpret_cast<uintptr_t>(w->absmax_f32) & 15u) || (reinterpret_cast<uintptr_t>(w->absmax_u8) & 15u) ||
+        (!w->absmax_f32 && ((reinterpret_cast<uintptr_t>(w->code2) & 15u) || (w->code2_stride & 3))))
+      return fail(NF4MOE_EALIGN, "activations, packed weights, absmax and code2 must be 16-byte aligned");
+  }
+  if (SIDES != 1 && act != NF4MOE_ACT_SWIGLU_OAI && act != NF4MOE_ACT_CHUNK_SILU) return fail(NF4MOE_EINVAL, "bad activation");
+  if (SIDES == 2) {
+    if (act != NF4MOE_ACT_SWIGLU_OAI) return fail(NF4MOE_EINVAL, "the merged launch needs the fused activation");
+    if ((hs[0].w->absmax_f32 == nullptr) != (hs[1].w->absmax_f32 == nullptr)) return fail(NF4MOE_EINVAL, "w13 and w2 must use the same absmax form");
+    if (hs[1].act_in != hs[0].out || hs[1].w->cols * 2 != hs[0].w->rows) return fail(NF4MOE_EINVAL, "w2 must read the rows w13 writes");
+  }
   if (T == 0) return 0;
   int dev = 0, sms = 0, cc = 0;
   cudaGetDevice(&dev);
@@ -622,22 +710,31 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
   cudaDeviceGetAttribute(&cc, cudaDevAttrComputeCapabilityMajor, dev);
   if (cc != 10) return fail(NF4MOE_EARCH, "needs an sm_100 device");
   const bool fast = mode == NF4MOE_GEMM_FAST;
-  const bool nested = w->absmax_f32 == nullptr;
+  const bool nested = hs[s_lo].w->absmax_f32 == nullptr;
   DecArgs a;
-  a.w = make_qw(*w);
-  a.out = out;
+  memset(&a, 0, sizeof(a));
+  int nkb_max = 0;
+  bool hole = fast && nested;
+  for (int sd = s_lo; sd <= s_hi; ++sd) {
+    a.s[sd].w = make_qw(*hs[sd].w);
+    a.s[sd].out = hs[sd].out;
+    nkb_max = std::max(nkb_max, a.s[sd].w.nkb);
+    hole = hole && hs[sd].w->code2_stride == 0;
+  }
+  // one code2 table for every expert of every side served (same device pointer) lets it live in the decode table's holes
+  if (SIDES == 2 && hs[0].w->code2 != hs[1].w->code2) hole = false;
   a.sorted_pairs = sorted_pairs;
   a.meta = meta;
-  a.tile_list = tile_list;
+  a.tile_list = const_cast<int32_t*>(tile_list);
   a.act = act;
-  a.bias = W13 ? (const __half*)bias : nullptr;
+  a.bias = SIDES != 1 ? (const __half*)bias : nullptr;
   a.status = status ? status : const_cast<int32_t*>(meta) + 4;
   a.dbg = gemm_debug_buffer();
-  a.hole_code2 = fast && nested && w->code2_stride == 0;
+  a.hole_code2 = hole;
   for (int bi = 0; bi < 2; ++bi) {
     a.plan_base[bi] = bi ? 2048u : 1024u;
     for (int wide = 0; wide < 2; ++wide)
-      if (!dec_plan(a.plan_base[bi], kGemmLutBytes, a.w.nkb, nested, nested && !a.hole_code2, wide ? 32 : 16, &a.plan[bi * 2 + wide]))
+      if (!dec_plan(a.plan_base[bi], kGemmLutBytes, nkb_max, nested, nested && !hole, wide ? 32 : 16, &a.plan[bi * 2 + wide]))
         return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form");
   }
 #ifdef NF4MOE_EXPERIMENTS
@@ -646,21 +743,34 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
     a.plan[i].n_b = std::max(std::max(3, kDecGroups), std::min(a.plan[i].n_b, experiment_env("NF4MOE_DEC_MAXB", kDecMaxB)));
   }
 #endif
-  CUtensorMap map_w, map_x16, map_x32;
-  if (!make_map_2d(&map_w, w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
-    return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
-  a.b3d = make_map_x3d(&map_x16, act_in, (uint64_t)w->cols, (uint64_t)T * k, 16) &&
-          make_map_x3d(&map_x32, act_in, (uint64_t)w->cols, (uint64_t)T * k, 32);
-  if (!a.b3d && (!make_map_2d(&map_x16, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 16) ||
-                 !make_map_2d(&map_x32, act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32)))
-    return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
+  CUtensorMap map_w[2], map_a16[2], map_a32[2];
+  memset(map_w, 0, sizeof(map_w)); memset(map_a16, 0, sizeof(map_a16)); memset(map_a32, 0, sizeof(map_a32));
+  a.b3d = 1;
+  for (int pass = 0; pass < 2; ++pass) {   // pass 0 tries the 3-D activation maps for every side, pass 1 falls back to 2-D for all
+    bool ok = true;
+    for (int sd = s_lo; sd <= s_hi && ok; ++sd) {
+      const nf4moe_qweight* w = hs[sd].w;
+      if (pass == 0) ok = make_map_x3d(&map_a16[sd], hs[sd].act_in, (uint64_t)w->cols, (uint64_t)T * k, 16) &&
+                          make_map_x3d(&map_a32[sd], hs[sd].act_in, (uint64_t)w->cols, (uint64_t)T * k, 32);
+      else ok = make_map_2d(&map_a16[sd], hs[sd].act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 16) &&
+                make_map_2d(&map_a32[sd], hs[sd].act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32);
+    }
+    if (ok) break;
+    if (pass == 1) return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
+    a.b3d = 0;
+  }
+  for (int sd = s_lo; sd <= s_hi; ++sd) {
+    const nf4moe_qweight* w = hs[sd].w;
+    if (!make_map_2d(&map_w[sd], w->packed, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, (uint64_t)w->cols / 2, (uint64_t)E * w->rows, 128, 128))
+      return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the packed weights");
+  }
   cudaError_t e;
   {   // once per kernel: the register pool the CTA is launched with must cover the setmaxnreg plan (else the kernel would hang)
     static std::atomic<int> regs_ok[2] = {{0}, {0}};
     int ok = regs_ok[fast].load(std::memory_order_acquire);
     if (ok == 0) {
       cudaFuncAttributes fa;
-      e = fast ? cudaFuncGetAttributes(&fa, dec_kernel<W13, true, false>) : cudaFuncGetAttributes(&fa, dec_kernel<W13, false, false>);
+      e = fast ? cudaFuncGetAttributes(&fa, dec_kernel<SIDES, true, false>) : cudaFuncGetAttributes(&fa, dec_kernel<SIDES, false, false>);
       if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncGetAttributes: %s", name, cudaGetErrorString(e)); return (int)e; }
       const int launched = (fa.numRegs + 7) / 8 * 8;
       ok = (32 * kDecDqWarps * std::max(kDecRegsDq, launched) + 128 * launched + 128 * std::min(kDecRegsCtl, launched) <= launched * kDecThreads &&
@@ -669,23 +779,42 @@ int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorte
     }
     if (ok < 0) return fail(NF4MOE_EINVAL, "register plan of the decode kernel does not fit the registers it is launched with (build problem)");
   }
+  const dim3 grid(sms), block(kDecThreads);
+  const cudaStream_t st = (cudaStream_t)stream;
 #ifdef NF4MOE_EXPERIMENTS
-  if (W13 && fast && a.dbg != nullptr) {   // the cycle-counter build exists for FAST w13 only (scripts/dec_roles.py)
-    e = ensure_dyn_smem<dec_kernel<W13, true, W13>>((int)kDecSmemBytes);
-    if (e == cudaSuccess) e = launch_pdl(dec_kernel<W13, true, W13>, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
+  if (SIDES == 0 && fast && a.dbg != nullptr) {   // the cycle-counter build exists for FAST w13 only (scripts/dec_roles.py)
+    e = ensure_dyn_smem<dec_kernel<0, true, true>>((int)kDecSmemBytes);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<0, true, true>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1]);
   } else
 #endif
   if (fast) {
-    e = ensure_dyn_smem<dec_kernel<W13, true, false>>((int)kDecSmemBytes);
-    if (e == cudaSuccess) e = launch_pdl(dec_kernel<W13, true, false>, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
+    e = ensure_dyn_smem<dec_kernel<SIDES, true, false>>((int)kDecSmemBytes);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<SIDES, true, false>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1]);
   } else {
-    e = ensure_dyn_smem<dec_kernel<W13, false, false>>((int)kDecSmemBytes);
-    if (e == cudaSuccess) e = launch_pdl(dec_kernel<W13, false, false>, dim3(sms), dim3(kDecThreads), kDecSmemBytes, (cudaStream_t)stream, a, map_w, map_x16, map_x32);
+    e = ensure_dyn_smem<dec_kernel<SIDES, false, false>>((int)kDecSmemBytes);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<SIDES, false, false>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1]);
   }
   ++*launches;
   if (e == cudaSuccess) e = cudaGetLastError();
   if (e != cudaSuccess) { snprintf(err, err_len, "%s: %s", name, cudaGetErrorString(e)); return (int)e; }
   return 0;
+}
+
+template <bool W13>
+int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
+               const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err, size_t err_len,
+               int* launches, const void* bias = nullptr, int32_t* status = nullptr) {
+  DecHostSide hs[2] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
+  hs[W13 ? 0 : 1] = DecHostSide{w, act_in, out};
+  return dec_launch_sides<W13 ? 0 : 1>(hs, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, err, err_len, launches, bias, status);
+}
+
+// w13 + SwiGLU and w2 in ONE launch: x_sorted [T k, H] -> h [T k, I] -> y [(token, slot) rows, H]
+inline int dec_launch_both(const void* x_sorted, const nf4moe_qweight* w13, void* h, const nf4moe_qweight* w2, void* y,
+                           const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act,
+                           int mode, void* stream, char* err, size_t err_len, int* launches, const void* bias, int32_t* status) {
+  const DecHostSide hs[2] = {{w13, x_sorted, h}, {w2, h, y}};
+  return dec_launch_sides<2>(hs, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, err, err_len, launches, bias, status);
 }
 
 }  // namespace nf4moe

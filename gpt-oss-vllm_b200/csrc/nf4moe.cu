@@ -456,6 +456,14 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
   if (gemm) {
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
+    // decode regime with the fused activation: w13 and w2 in ONE persistent launch (gemm_dec.cuh, DecSide)
+    if (tile_rows <= 32 && act == NF4MOE_ACT_SWIGLU_OAI && !bias_split && (w13->absmax_f32 == nullptr) == (w2->absmax_f32 == nullptr) &&
+        experiment_env("NF4MOE_DEC_MERGED", 1) != 0) {
+      if (int rc = dec_launch_both(ws.xs, w13, ws.h, w2, y, ws.sorted, ws.meta, ws.tiles, T, k, E, act, mode, stream, g_err, sizeof(g_err),
+                                   &g_launches, bias_fused ? w13_bias : nullptr, ws.status)) return rc;
+      *launches += g_launches; g_launches = 0;
+      return 0;
+    }
     if (int rc = gemm_w13_any(ws.xs, w13, ws.meta, ws.tiles, T, k, E, act_k, mode, h_dst, stream, bias_fused ? w13_bias : nullptr,
                               ws.status, tile_rows)) return rc;
   } else {

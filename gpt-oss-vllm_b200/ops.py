@@ -79,7 +79,8 @@ def check_status(workspace: torch.Tensor | None = None) -> None:
         st = workspace_status(b)
         if st:
             raise _lib.Nf4MoeError(-100, f"kernel status word = {st:#x} (2: decode tcgen05 kernel could not place its pipeline in "
-                                         f"shared memory, 4: prefill tcgen05 kernel likewise); the output is not valid")
+                                         f"shared memory, 4: prefill tcgen05 kernel likewise, 16: the merged decode launch was not fully "
+                                         f"resident and gave up waiting); the output is not valid")
 
 
 def route_topk(logits: torch.Tensor, k: int) -> tuple[torch.Tensor, torch.Tensor]:

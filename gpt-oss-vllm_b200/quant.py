@@ -34,6 +34,19 @@ def _require_cuda(t: torch.Tensor, name: str) -> None:
         raise ValueError(f"{name} must be contiguous")
 
 
+_CODE2_TABLES: dict = {}
+
+
+def _shared_code2(t: torch.Tensor | None) -> torch.Tensor | None:
+    """One device copy per distinct 256-entry double-quant table: w13 and w2 of a layer (of every layer, in practice: bnb's
+    dynamic map) then hand the SAME pointer to the library, which is what lets the merged w13+w2 decode launch park the table in
+    its decode table's holes (csrc/gemm_dec.cuh, dec_launch_sides)."""
+    if t is None or not t.is_cuda or t.dim() != 1 or t.numel() != 256 or t.dtype != torch.float32:
+        return t
+    key = (t.device.index, t.detach().cpu().numpy().tobytes())
+    return _CODE2_TABLES.setdefault(key, t)
+
+
 @dataclass
 class NF4ExpertWeights:
     """One fused expert matrix set: E experts x [rows, cols]."""
@@ -56,6 +69,7 @@ class NF4ExpertWeights:
             raise ValueError("packed has the wrong number of bytes for [E, rows, cols]")
         if self.absmax is None and not self.has_nested:
             raise ValueError("give a flat absmax or the nested state")
+        self.code2 = _shared_code2(self.code2)
 
     @property
     def has_nested(self) -> bool:

@@ -106,6 +106,8 @@ size_t nf4moe_workspace_status_offset(int T, int E, int H, int I, int k);
 #define NF4MOE_STATUS_EP_OVERFLOW 1  /* nf4moe_ep_pack: a peer got more rows than its capacity (written to ITS status argument) */
 #define NF4MOE_STATUS_DEC_NOFIT 2    /* decode tcgen05 kernel: shared-memory plan did not fit */
 #define NF4MOE_STATUS_GEMM_NOFIT 4   /* prefill tcgen05 kernel: shared-memory plan did not fit */
+#define NF4MOE_STATUS_DEP_TIMEOUT 16 /* merged w13+w2 decode launch: a w2 tile waited > 2^26 polls for its w13 row tiles (the
+                                        grid was not fully resident); EP_TIMEOUT = 8 is defined with nf4moe_ep_wait below */
 
 /* ---- NF4 (de)quantisation ------------------------------------------------------------------------------------ */
 

@@ -62,7 +62,9 @@ def test_status_word_and_pool_contract(pkg):
     assert pool.buffers() == []
     assert (pkg._lib.STATUS_EP_OVERFLOW, pkg._lib.STATUS_DEC_NOFIT, pkg._lib.STATUS_GEMM_NOFIT) == (1, 2, 4)
     header = open(os.path.join(ROOT, "include", "nf4moe.h")).read()
-    for name, val in (("NF4MOE_STATUS_EP_OVERFLOW", 1), ("NF4MOE_STATUS_DEC_NOFIT", 2), ("NF4MOE_STATUS_GEMM_NOFIT", 4)):
+    assert (pkg._lib.STATUS_EP_TIMEOUT, pkg._lib.STATUS_DEP_TIMEOUT) == (8, 16)
+    for name, val in (("NF4MOE_STATUS_EP_OVERFLOW", 1), ("NF4MOE_STATUS_DEC_NOFIT", 2), ("NF4MOE_STATUS_GEMM_NOFIT", 4),
+                      ("NF4MOE_STATUS_EP_TIMEOUT", 8), ("NF4MOE_STATUS_DEP_TIMEOUT", 16)):
         assert re.search(rf"#define {name} {val}\b", header)
 
 
@@ -92,7 +94,7 @@ def test_no_global_load_ahead_of_the_grid_dependency_wait(pkg):
     """Kernels launched with programmatic dependent launch start while their predecessor is still running; everything they
     read from it must be loaded AFTER griddepcontrol.wait (SASS: ACQBULK).  The compiler may hoist loads through
     `const __restrict__` pointers above the wait (round 2: permute_rows_kernel read stale bucket metadata that way), so the built
-    library's SASS is scanned: no global / TMA load may precede the first ACQBULK, except the decode kernel's copy of the
+    library's SASS is scanned: no global / TMA load may precede the first ACQBULK, except the decode kernel's preload of the
     constant code2 table (weights, written before any launch)."""
     import shutil
     import subprocess
@@ -110,7 +112,9 @@ def test_no_global_load_ahead_of_the_grid_dependency_wait(pkg):
             continue
         checked += 1
         early = [t.strip() for t in ins[:acq[0]] if re.search(r"\bLDG|\bLD\.|UTMALDG|UBLKCP|LDGSTS", t)]
-        allowed = 1 if "dec_kernel" in name else 0
+        # the decode kernel's FAST variants (second template argument true) preload the constant code2 table ahead of the wait:
+        # ceil(256 * 32 / 640 threads) = 13 loads per thread, all of weights; nothing else may sit there
+        allowed = 13 if re.search(r"dec_kernelILi\dELb1E", name) else 0
         assert len(early) <= allowed, f"{name}: loads ahead of the dependency wait: {early}"
     assert checked >= 10, "expected the PDL kernels (route, bucket, permute, GEMV, tcgen05, combine) in the library"
 
