@@ -536,6 +536,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
           if (elect_one()) {
             const uint32_t full = rfull0 + 8u * (uint32_t)sw;
             mbar_expect_tx(full, kDecRawBytes);
+            // (a probe that read every stage as one contiguous 16 KB block instead of 128 row segments 1440 B apart changed
+            // nothing -- 123.9 vs 123.5 us per layer -- so the weights keep bnb's row-major layout)
             tma_load_2d(s_plan.raw[sw], map_w, st * 128, c1, full);
           }
           __syncwarp();
