@@ -598,6 +598,7 @@ def run_ours(args):
     eff_name = {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "gemm_exact", pkg.REGIME_GEMM_FAST: "gemm_fast"}[eff]
     use_tc = eff != pkg.REGIME_GEMV
     dec_kernel = use_tc and (T * TOP_K <= 40 * E or (E <= 8 and T * TOP_K <= 128 * E))   # gemm_tile_tokens == 32
+    act_fused = True   # the bench runs the gpt-oss clamped SwiGLU, which the decode kernel fuses (so w13 and w2 share one launch)
     stack = make_stack(pkg, dev, L, E, code2)
     g = torch.Generator(device=dev).manual_seed(SEED + 1)
     x = torch.randn(T, H, generator=g, device=dev).half()
@@ -728,6 +729,30 @@ def run_ours(args):
         if rep > 0:
             t13.append(a0.elapsed_time(a1) / L)
             t2.append(a1.elapsed_time(a2) / L)
+    # The decode tcgen05 regime serves w13 + SwiGLU and w2 in ONE launch (dec_kernel<2>): that launch is the step's dominant
+    # kernel.  Timed alone the same way; its tile lists (which carry the w13-done counters) are rewritten by an untimed replay of
+    # the bucket kernels before every timed replay.
+    t_both = []
+    if dec_kernel and act_fused:
+        hy = [pkg.ops.expert_w13_w2(xin, w13, w2, b, T, TOP_K, nested=nested, regime=eff) for (w13, w2), (b, xin) in zip(stack, prep)]
+        idss = [pkg.ops.route_topk(logits[l], TOP_K)[0] for l in range(L)]
+        torch.cuda.synchronize()
+        g_reset, g_both = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g_reset, stream=side):
+                for l, (b, _) in enumerate(prep):
+                    pkg.ops.bucket(idss[l], E, want_tiles=True, into=b)
+            with torch.cuda.graph(g_both, stream=side):
+                for (w13, w2), (b, xin), (hb, yb) in zip(stack, prep, hy):
+                    pkg.ops.expert_w13_w2(xin, w13, w2, b, T, TOP_K, nested=nested, regime=eff, h=hb, y=yb)
+        torch.cuda.synchronize()
+        for rep in range(4):
+            g_reset.replay()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(); g_both.replay(); a1.record()
+            torch.cuda.synchronize()
+            if rep > 0:
+                t_both.append(a0.elapsed_time(a1) / L)
     ea = sum(eact) / len(eact)
     b13 = ea * stack[0][0].nbytes(nested) + T * H * 2 + T * TOP_K * I * 2
     b2 = ea * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2
@@ -742,9 +767,29 @@ def run_ours(args):
             traffic, traffic_src = tj[key]["traffic_bytes_per_launch"], tj[key]["source"]
     except Exception:
         pass
+    if t_both:   # the merged launch is what the step runs: report it as the dominant kernel, the split kernels beside it
+        d_both = statistics.mean(t_both) * 1e-3
+        key = "dec2"
+        traffic, traffic_src = None, None
+        try:
+            if T == 64 and E == 32 and nested and key in tj:
+                traffic, traffic_src = tj[key]["traffic_bytes_per_launch"], tj[key]["source"]
+        except Exception:
+            pass
+        roof = {"bound": "hbm", "kernel": "dec_kernel<SIDES=2> (decode-regime tcgen05 kernel: NF4 -> TMEM A operand; w13 + SwiGLU and w2 in one persistent launch)",
+                "achieved": layer_bytes / d_both / 1e9, "peak": peak, "unit": "GB/s", "frac": layer_bytes / d_both / 1e9 / peak,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": layer_bytes,
+                "avg_launch_us": d_both * 1e6, "frac_of_nominal_8TBs": layer_bytes / d_both / 8e12,
+                "split_launches": {"w13": {"achieved": b13 / d13 / 1e9, "frac": b13 / d13 / 1e9 / peak, "avg_launch_us": d13 * 1e6,
+                                           "algorithmic_bytes_per_launch": b13},
+                                   "w2": {"achieved": b2 / d2 / 1e9, "frac": b2 / d2 / 1e9 / peak, "avg_launch_us": d2 * 1e6,
+                                          "algorithmic_bytes_per_launch": b2},
+                                   "note": "the same work as two launches of the same kernel template (SIDES = 0 / 1), for comparison"},
+                "whole_step": {"achieved": layer_bytes * L / (ms_per_step * 1e-3) / 1e9,
+                               "frac": layer_bytes * L / (ms_per_step * 1e-3) / 1e9 / peak, "experts_active_mean": ea}}
     kname = ("dec_kernel<W13> (decode-regime tcgen05 kernel: NF4 -> TMEM A operand, w13 + SwiGLU)" if dec_kernel else
              "gemm_kernel<W13> (tcgen05 grouped GEMM, w13 + SwiGLU)" if use_tc else "gemv_kernel<NT=2,W13> (w13 NF4 GEMV + SwiGLU)")
-    roof = {"bound": "hbm", "kernel": kname, "achieved": b13 / d13 / 1e9, "peak": peak,
+    roof = roof if t_both else {"bound": "hbm", "kernel": kname, "achieved": b13 / d13 / 1e9, "peak": peak,
             "unit": "GB/s", "frac": b13 / d13 / 1e9 / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": b13, "avg_launch_us": d13 * 1e6, "frac_of_nominal_8TBs": b13 / d13 / 8e12,
             "w2_kernel": {"achieved": b2 / d2 / 1e9, "frac": b2 / d2 / 1e9 / peak, "avg_launch_us": d2 * 1e6,

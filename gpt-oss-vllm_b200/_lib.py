@@ -21,7 +21,7 @@ LOGITS_DTYPE = {"float16": 0, "float32": 1, "bfloat16": 2}
 EXPORTED = (
     "nf4moe_version", "nf4moe_auto_regime", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_dequant", "nf4moe_dequant_absmax",
     "nf4moe_quantize", "nf4moe_route_topk", "nf4moe_bucket", "nf4moe_permute_rows", "nf4moe_combine",
-    "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
+    "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_gemm_w13_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
     "nf4moe_last_launch_count", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
     "nf4moe_workspace_status_offset", "nf4moe_expert_rows_bias", "nf4moe_combine_indexed_bias",
     "nf4moe_ep_dispatch_p2p", "nf4moe_ep_return_p2p", "nf4moe_ep_wait",
@@ -71,6 +71,7 @@ def _declare(lib):
     lib.nf4moe_gemv_w2.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, vp, vp]
     lib.nf4moe_gemm_w13_swiglu.argtypes = [vp, qp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]
     lib.nf4moe_gemm_w2.argtypes = [vp, qp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
+    lib.nf4moe_gemm_w13_w2.argtypes = [vp, qp, vp, vp, qp, vp, vp, vp, vp, i32, i32, i32, i32, i32, vp]
     lib.nf4moe_moe_forward.argtypes = [vp, vp, i32, vp, vp, qp, qp, vp, i32, i32, i32, i32, i32, i32, i32, vp, sz, vp,
                                        vp, vp]
     lib.nf4moe_moe_forward_bias.argtypes = [vp, vp, i32, vp, vp, qp, qp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, sz, vp,

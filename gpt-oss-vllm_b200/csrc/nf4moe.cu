@@ -426,6 +426,15 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
   return gemm_w2_any(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, mode, y, stream, nullptr);
 }
 
+int nf4moe_gemm_w13_w2(const void* x_sorted, const nf4moe_qweight* w13, const void* w13_bias, void* h_sorted,
+                       const nf4moe_qweight* w2, void* y, const int32_t* sorted_pairs, const int32_t* meta, int32_t* tile_list,
+                       int T, int k, int E, int act, int mode, void* stream) {
+  g_launches = 0;
+  if (w13_bias && !aligned16(w13_bias)) return fail(NF4MOE_EALIGN, "gemm_w13_w2: w13_bias must be 16-byte aligned");
+  return dec_launch_both(x_sorted, w13, h_sorted, w2, y, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, g_err,
+                         sizeof(g_err), &g_launches, w13_bias, nullptr);
+}
+
 // bucket -> (permute) -> w13 (+activation) -> w2 for the (row, slot) pairs of `ids` [T, k]; y fp16 [T*k, H] in pair order.
 // policy_T: the token count the regime and the token-tile size are chosen for (an expert-parallel owner passes the rows it
 // EXPECTS, not the capacity of its receive buffer); buffers and TMA maps are always sized by T.

@@ -96,13 +96,16 @@ def route_topk(logits: torch.Tensor, k: int) -> tuple[torch.Tensor, torch.Tensor
     return ids, w
 
 
-def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True, tile_rows: int = 0) -> dict[str, torch.Tensor]:
-    """Stable counting sort of the (token,slot) pairs by expert -> offsets / sorted_pairs / active / meta / tiles."""
+def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True, tile_rows: int = 0,
+           into: dict[str, torch.Tensor] | None = None) -> dict[str, torch.Tensor]:
+    """Stable counting sort of the (token,slot) pairs by expert -> offsets / sorted_pairs / active / meta / tiles.
+    `into`: a dict returned by an earlier call of the same shape, rewritten in place (CUDA-graph replays; the merged w13+w2
+    launch needs its tile list rewritten before every call)."""
     _require_cuda(ids, "topk_ids")
     T, k = ids.shape
     dev = ids.device
     n = T * k
-    out = {
+    out = into if into is not None else {
         "expert_offsets": torch.empty(E + 1, dtype=torch.int32, device=dev),
         "sorted_pairs": torch.full(((n + 255) // 256 * 256 + 256,), -1, dtype=torch.int32, device=dev),
         "active_experts": torch.empty(E, dtype=torch.int32, device=dev),
@@ -182,6 +185,26 @@ def expert_w2(h: torch.Tensor, w2: NF4ExpertWeights, b: dict, T: int, k: int, ne
                                           b["sorted_pairs"].data_ptr(), b["active_experts"].data_ptr(),
                                           b["meta"].data_ptr(), T, k, E, y.data_ptr(), _stream_ptr(h.device)))
     return y
+
+
+def expert_w13_w2(xs: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, b: dict, T: int, k: int,
+                  nested: bool | None = None, regime: int = _lib.REGIME_GEMM_FAST, w13_bias: torch.Tensor | None = None,
+                  h: torch.Tensor | None = None, y: torch.Tensor | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """Both expert products in ONE launch of the decode-regime tcgen05 kernel (nf4moe_gemm_w13_w2): h fp16 [T*k, I] in sorted
+    order, y fp16 [T*k, H] in (token, slot) order.  `b` must come fresh from bucket() (tile rows <= 32) for every call."""
+    lib = _lib.load_library()
+    E = w13.num_experts
+    I = w13.rows // 2
+    h = torch.zeros(T * k, I, dtype=torch.float16, device=xs.device) if h is None else h
+    y = torch.zeros(T * k, w2.rows, dtype=torch.float16, device=xs.device) if y is None else y
+    q13, q2 = w13.c_struct(nested), w2.c_struct(nested)
+    mode = _lib.GEMM_FAST if regime == _lib.REGIME_GEMM_FAST else _lib.GEMM_EXACT
+    with torch.cuda.device(xs.device):
+        _lib.check(lib.nf4moe_gemm_w13_w2(xs.data_ptr(), C.byref(q13), None if w13_bias is None else w13_bias.data_ptr(),
+                                          h.data_ptr(), C.byref(q2), y.data_ptr(), b["sorted_pairs"].data_ptr(),
+                                          b["meta"].data_ptr(), b["tile_list"].data_ptr(), T, k, E, _lib.ACT_SWIGLU_OAI, mode,
+                                          _stream_ptr(xs.device)))
+    return h, y
 
 
 def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, top_k: int,

@@ -177,6 +177,17 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
                    const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E,
                    int mode, void* y, void* stream);
 
+/* Decode regime (token tiles of at most 32 rows, i.e. a tile list built with tile_rows <= 32) with the fused gpt-oss activation:
+ * both products in ONE persistent launch -- h_sorted[T*k, I] = SwiGLU(x_sorted W13^T (+ w13_bias)), y = h_sorted W2^T scattered to
+ * (token, slot) rows.  Replaces the same two bnb Linear4bit calls per routed row as nf4moe_gemm_w13_swiglu + nf4moe_gemm_w2
+ * (P/unsloth_to_vllm_converter.py:309-318); nf4moe_moe_forward / nf4moe_expert_rows use it whenever it applies.
+ * `tile_list` is written to: the kernel counts the finished w13 row tiles of token tile t in tile_list[4 t + 3], which
+ * nf4moe_bucket zeroes -- the list must come fresh from nf4moe_bucket for EVERY call.  Status bits as for the other tcgen05
+ * entry points (meta[4]); NF4MOE_STATUS_DEP_TIMEOUT if the grid was not fully resident. */
+int nf4moe_gemm_w13_w2(const void* x_sorted, const nf4moe_qweight* w13, const void* w13_bias, void* h_sorted,
+                       const nf4moe_qweight* w2, void* y, const int32_t* sorted_pairs, const int32_t* meta, int32_t* tile_list,
+                       int T, int k, int E, int act, int mode, void* stream);
+
 /* ---- the whole layer ---------------------------------------------------------------------------------------------- */
 
 /* out[T,H] = MoE(x[T,H]).  Routing is computed from `router_logits` when non-NULL (the north-star / legacy
