@@ -54,11 +54,14 @@ constexpr uint32_t kDecSmemBytes = 232448 - 1024;
 // forever -- so the dequant figure is derived from the budget, and dec_launch() checks the budget against the kernel's
 // real register count (cudaFuncGetAttributes) before the first launch instead of trusting this arithmetic.
 constexpr int kDecRegsLaunch = (65536 / kDecThreads) / 8 * 8 > 255 ? 248 : (65536 / kDecThreads) / 8 * 8;
-constexpr int kDecRegsCtl = 40;
-constexpr int kDecRegsDqBudget = (kDecRegsLaunch * kDecThreads - 128 * kDecRegsLaunch - 128 * kDecRegsCtl) / (32 * kDecDqWarps) / 8 * 8;
+constexpr int kDecRegsCtl = 32;
+// The epilogue warpgroup gives registers away too: it runs once per item (12 stages), so what it spills costs nothing, while
+// the dequant warps need two decoded k-blocks (64 registers) next to the undecoded half of the stage (16) in flight.
+constexpr int kDecRegsEpi = kDecRegsLaunch < 64 ? kDecRegsLaunch : 64;
+constexpr int kDecRegsDqBudget = (kDecRegsLaunch * kDecThreads - 128 * kDecRegsEpi - 128 * kDecRegsCtl) / (32 * kDecDqWarps) / 8 * 8;
 constexpr int kDecRegsDq = kDecRegsDqBudget > 232 ? 232 : kDecRegsDqBudget;
 static_assert(kDecRegsDq >= kDecRegsLaunch, "the dequant warps never give registers away");
-static_assert(32 * kDecDqWarps * kDecRegsDq + 128 * kDecRegsLaunch + 128 * kDecRegsCtl <= kDecRegsLaunch * kDecThreads,
+static_assert(32 * kDecDqWarps * kDecRegsDq + 128 * kDecRegsEpi + 128 * kDecRegsCtl <= kDecRegsLaunch * kDecThreads,
               "setmaxnreg budget: increases must fit in what the decreases release");
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
@@ -266,6 +269,16 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  if (lane == 0 && (warp == kDecWarpProd || warp == kDecWarpAct)) {   // descriptor fetches off the first TMA's critical path
+    auto pf = [](const CUtensorMap* m) { asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory"); };
+    if (warp == kDecWarpProd) {
+      if (SIDES != 1) pf(&map_w13);
+      if (SIDES != 0) pf(&map_w2);
+    } else {
+      if (SIDES != 1) { pf(&map_x16); pf(&map_x32); }
+      if (SIDES != 0) { pf(&map_h16); pf(&map_h32); }
+    }
+  }
   if (tid == 0) stamp(1);
   grid_dep_wait();
   if (tid == 0) stamp(2);
@@ -322,11 +335,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     const uint32_t hole_lane = pin(lut | 128u | ((uint32_t)lane << 2));
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + acol0;
     const uint32_t rfull0 = bar(kDbRFull), rempty0 = bar(kDbREmpty), afull0 = bar(kDbAFull), done0 = bar(kDbDone);
-    // this lane's 16-byte chunks of a raw stage row (128B swizzle: chunk c of row r sits at chunk c ^ (r & 7))
-    const uint32_t row_off = (uint32_t)r * 128u, swz = (uint32_t)(r & 7);
-    uint32_t ch[2 * kDecKpw];
-#pragma unroll
-    for (int j = 0; j < 2 * kDecKpw; ++j) ch[j] = row_off + (((uint32_t)(hh * 2 * kDecKpw + j) ^ swz) << 4);
+    // this lane's 16-byte chunks of a raw stage row (128B swizzle: chunk c of row r sits at chunk c ^ (r & 7)).  Stages are
+    // 1 KB-aligned and a row is 128 B, so chunk j of the stage at `wst` is at (wst + c_row) ^ (j << 4): one add per stage and one
+    // LOP3 with an immediate per chunk (round 2: ptxas rebuilt all eight addresses from %tid every stage, 38 instructions)
+    const uint32_t c_row = pin(((uint32_t)r * 128u) | ((uint32_t)(r & 7) << 4));
     // this warp owns stages cs = pp (mod kDecGroups).  Running ring positions of its NEXT stage: raw stage sw, A slot `slot`,
     // and the Done barrier of stage cs - 3 (index dn, parity pdn; "stage -3 .. -1" = the phase before the first one, which a
     // fresh barrier reports complete)
@@ -344,14 +356,14 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       const int mb = it & 1;
       // nested absmax: code2[u8] * absmax2[blk >> 8] + offset; this row's blocks touch at most two absmax2 entries
       float a2_lo = 0.f, a2_hi = 0.f, off_e = 0.f;
-      long long blk_hi = 0;
+      int blk_hi = 0;                                      // first k-block of this row that belongs to the next absmax2 entry (1..256)
       if (nested) {
         const long long blk0 = (long long)min(n, w.rows - 1) * nkb;
         const long long i2 = blk0 >> 8;
         a2_lo = __ldg(w.absmax2 + (long long)e * w.n2 + i2);
         a2_hi = __ldg(w.absmax2 + (long long)e * w.n2 + min(i2 + 1, w.n2 - 1));
         off_e = __ldg(w.offset + e);
-        blk_hi = ((i2 + 1) << 8) - blk0;
+        blk_hi = (int)(((i2 + 1) << 8) - blk0);
       }
       GEMM_DBG_T0();
       mbar_wait(bar(kDbMFull + mb), (uint32_t)(it >> 1) & 1u);
@@ -363,11 +375,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         mbar_wait(rfull0 + 8u * (uint32_t)sw, phw);
         if (DBG && warp == 0 && it == 0 && st == 0) stamp(4);
         GEMM_DBG_ADD(1);
-        const uint32_t wst = pin(s_plan.raw[sw]);
+        const uint32_t wst = pin(s_plan.raw[sw]) + c_row;
         const int kb0 = st * 4 + hh * kDecKpw;
         uint4 v[2 * kDecKpw];
 #pragma unroll
-        for (int j = 0; j < 2 * kDecKpw; ++j) v[j] = lds128(wst + ch[j]);
+        for (int j = 0; j < 2 * kDecKpw; ++j) v[j] = lds128(wst ^ ((uint32_t)(hh * 2 * kDecKpw + j) << 4));
         float am[kDecKpw];
 #pragma unroll
         for (int u = 0; u < kDecKpw; ++u) {
@@ -385,18 +397,30 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         __syncwarp();
         if (lane == 0) mbar_arrive(rempty0 + 8u * (uint32_t)sw);
         const uint32_t t_st = t_lane + (uint32_t)slot * 128u + (uint32_t)(hh * kDecKpw) * 32u;
-        uint32_t regs[32];
+        // The first kDecPre k-blocks are decoded BEFORE the wait for the A slot (the MMAs of stage cs - 3): in round 2's first
+        // kernel only one was, and the dequant warps spent 12.6 % of their samples (ncu) spinning on Done -- the commit of stage
+        // cs - 3 arrives about one k-block's decode after this warp gets here.  Two register banks, used alternately afterwards.
+        constexpr int kDecPre = kDecKpw >= 2 ? 2 : 1;
+        uint32_t ra[32], rb[32];
+        const bool real0 = kb0 < nkb, real1 = kDecPre > 1 && kb0 + 1 < nkb;
+        if (real0) decode_block<FAST>(v[0], v[1], lut_lane, am[0], ra);
+        if constexpr (kDecPre > 1) {
+          if (real1) decode_block<FAST>(v[2], v[3], lut_lane, am[1], rb);
+        }
+        GEMM_DBG_ADD(2);
+        mbar_wait(done0 + 8u * (uint32_t)dn, pdn);          // the MMAs of stage cs - 3, which read this A slot, are done
+        tc_fence_after();
+        GEMM_DBG_ADD(3);
+        if (real0) tmem_st32(t_st, ra);
+        if constexpr (kDecPre > 1) {
+          if (real1) tmem_st32(t_st + 32u, rb);
+        }
 #pragma unroll
-        for (int u = 0; u < kDecKpw; ++u) {
-          const bool real = kb0 + u < nkb;
-          if (real) decode_block<FAST>(v[2 * u], v[2 * u + 1], lut_lane, am[u], regs);
-          if (u == 0) {
-            GEMM_DBG_ADD(2);
-            mbar_wait(done0 + 8u * (uint32_t)dn, pdn);      // the MMAs of stage cs - 3, which read this A slot, are done
-            tc_fence_after();
-            GEMM_DBG_ADD(3);
+        for (int u = kDecPre; u < kDecKpw; ++u) {
+          if (kb0 + u < nkb) {
+            if (u & 1) { decode_block<FAST>(v[2 * u], v[2 * u + 1], lut_lane, am[u], rb); tmem_st32(t_st + (uint32_t)u * 32u, rb); }
+            else { decode_block<FAST>(v[2 * u], v[2 * u + 1], lut_lane, am[u], ra); tmem_st32(t_st + (uint32_t)u * 32u, ra); }
           }
-          if (real) tmem_st32(t_st + (uint32_t)u * 32u, regs);
         }
         GEMM_DBG_ADD(4);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -415,6 +439,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     if (dbg_on && (warp == 0 || warp == kDecDqWarps - 3)) for (int i = 0; i < 6; ++i) a.dbg[(warp ? 8 : 0) + i] = dbg_acc[i];
   } else if (warp < kDecDqWarps + 4) {
     // =============================== epilogue: TMEM -> registers -> global, overlapped with the next item ===============
+    if constexpr (kDecRegsEpi < kDecRegsLaunch) set_max_regs_dec<kDecRegsEpi>();
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16);
@@ -775,7 +800,7 @@ int dec_launch_sides(const DecHostSide (&hs)[2], const int32_t* sorted_pairs, co
       e = fast ? cudaFuncGetAttributes(&fa, dec_kernel<SIDES, true, false>) : cudaFuncGetAttributes(&fa, dec_kernel<SIDES, false, false>);
       if (e != cudaSuccess) { snprintf(err, err_len, "%s: cudaFuncGetAttributes: %s", name, cudaGetErrorString(e)); return (int)e; }
       const int launched = (fa.numRegs + 7) / 8 * 8;
-      ok = (32 * kDecDqWarps * std::max(kDecRegsDq, launched) + 128 * launched + 128 * std::min(kDecRegsCtl, launched) <= launched * kDecThreads &&
+      ok = (32 * kDecDqWarps * std::max(kDecRegsDq, launched) + 128 * std::min(kDecRegsEpi, launched) + 128 * std::min(kDecRegsCtl, launched) <= launched * kDecThreads &&
             launched <= kDecRegsDq) ? 1 : -1;
       regs_ok[fast].store(ok, std::memory_order_release);
     }
