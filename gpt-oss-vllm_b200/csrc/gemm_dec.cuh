@@ -33,6 +33,13 @@ namespace nf4moe {
 #ifndef NF4MOE_DEC_SPLIT
 #define NF4MOE_DEC_SPLIT 1
 #endif
+#ifndef NF4MOE_DEC_ARITH
+#define NF4MOE_DEC_ARITH 0
+#endif
+#ifndef NF4MOE_DEC_PRE
+#define NF4MOE_DEC_PRE 1
+#endif
+constexpr int kDecArith = NF4MOE_DEC_ARITH;       // packed words (of 8 per k-block and thread) decoded without the shared-memory table
 constexpr int kDecGroups = NF4MOE_DEC_GROUPS;     // dequant groups; stage cs belongs to group cs % kDecGroups
 constexpr int kDecSplit = NF4MOE_DEC_SPLIT;       // warps sharing one (stage, lane quarter): 1 or 2
 constexpr int kDecKpw = 4 / kDecSplit;            // k-blocks a warp decodes per stage
@@ -54,10 +61,16 @@ constexpr uint32_t kDecSmemBytes = 232448 - 1024;
 // forever -- so the dequant figure is derived from the budget, and dec_launch() checks the budget against the kernel's
 // real register count (cudaFuncGetAttributes) before the first launch instead of trusting this arithmetic.
 constexpr int kDecRegsLaunch = (65536 / kDecThreads) / 8 * 8 > 255 ? 248 : (65536 / kDecThreads) / 8 * 8;
-constexpr int kDecRegsCtl = 32;
-// The epilogue warpgroup gives registers away too: it runs once per item (12 stages), so what it spills costs nothing, while
-// the dequant warps need two decoded k-blocks (64 registers) next to the undecoded half of the stage (16) in flight.
-constexpr int kDecRegsEpi = kDecRegsLaunch < 64 ? kDecRegsLaunch : 64;
+#ifndef NF4MOE_DEC_REGS_CTL
+#define NF4MOE_DEC_REGS_CTL 32
+#endif
+#ifndef NF4MOE_DEC_REGS_EPI
+#define NF4MOE_DEC_REGS_EPI 64
+#endif
+constexpr int kDecRegsCtl = NF4MOE_DEC_REGS_CTL;
+// The epilogue warpgroup gives registers away too: it runs once per item (12 stages), so what it spills costs nothing, and the
+// dequant warps at 128 registers keep their addresses and ring state live instead of rebuilding them every stage.
+constexpr int kDecRegsEpi = kDecRegsLaunch < NF4MOE_DEC_REGS_EPI ? kDecRegsLaunch : NF4MOE_DEC_REGS_EPI;
 constexpr int kDecRegsDqBudget = (kDecRegsLaunch * kDecThreads - 128 * kDecRegsEpi - 128 * kDecRegsCtl) / (32 * kDecDqWarps) / 8 * 8;
 constexpr int kDecRegsDq = kDecRegsDqBudget > 232 ? 232 : kDecRegsDqBudget;
 static_assert(kDecRegsDq >= kDecRegsLaunch, "the dequant warps never give registers away");
@@ -397,15 +410,16 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         __syncwarp();
         if (lane == 0) mbar_arrive(rempty0 + 8u * (uint32_t)sw);
         const uint32_t t_st = t_lane + (uint32_t)slot * 128u + (uint32_t)(hh * kDecKpw) * 32u;
-        // The first kDecPre k-blocks are decoded BEFORE the wait for the A slot (the MMAs of stage cs - 3): in round 2's first
-        // kernel only one was, and the dequant warps spent 12.6 % of their samples (ncu) spinning on Done -- the commit of stage
-        // cs - 3 arrives about one k-block's decode after this warp gets here.  Two register banks, used alternately afterwards.
-        constexpr int kDecPre = kDecKpw >= 2 ? 2 : 1;
+        // kDecPre k-blocks are decoded BEFORE the wait for the A slot (the MMAs of stage cs - 3).  Decoding two ahead removes the
+        // wait (ncu: 12.6 % of the dequant warps' samples spin on Done with one) but is 2 % SLOWER end to end (same-box A/B,
+        // profiles/r2_notes.md): the time only moves to the raw-stage wait, the kernel is bound by issue + the shared-memory
+        // pipe, not by this dependency.  What did help (2.6 %) is the register split that came with it: 128 per dequant thread.
+        constexpr int kDecPre = (kDecKpw >= 2 && NF4MOE_DEC_PRE >= 2) ? 2 : 1;
         uint32_t ra[32], rb[32];
         const bool real0 = kb0 < nkb, real1 = kDecPre > 1 && kb0 + 1 < nkb;
-        if (real0) decode_block<FAST>(v[0], v[1], lut_lane, am[0], ra);
+        if (real0) decode_block<FAST, kDecArith>(v[0], v[1], lut_lane, am[0], ra);
         if constexpr (kDecPre > 1) {
-          if (real1) decode_block<FAST>(v[2], v[3], lut_lane, am[1], rb);
+          if (real1) decode_block<FAST, kDecArith>(v[2], v[3], lut_lane, am[1], rb);
         }
         GEMM_DBG_ADD(2);
         mbar_wait(done0 + 8u * (uint32_t)dn, pdn);          // the MMAs of stage cs - 3, which read this A slot, are done
@@ -418,8 +432,8 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 #pragma unroll
         for (int u = kDecPre; u < kDecKpw; ++u) {
           if (kb0 + u < nkb) {
-            if (u & 1) { decode_block<FAST>(v[2 * u], v[2 * u + 1], lut_lane, am[u], rb); tmem_st32(t_st + (uint32_t)u * 32u, rb); }
-            else { decode_block<FAST>(v[2 * u], v[2 * u + 1], lut_lane, am[u], ra); tmem_st32(t_st + (uint32_t)u * 32u, ra); }
+            if (u & 1) { decode_block<FAST, kDecArith>(v[2 * u], v[2 * u + 1], lut_lane, am[u], rb); tmem_st32(t_st + (uint32_t)u * 32u, rb); }
+            else { decode_block<FAST, kDecArith>(v[2 * u], v[2 * u + 1], lut_lane, am[u], ra); tmem_st32(t_st + (uint32_t)u * 32u, ra); }
           }
         }
         GEMM_DBG_ADD(4);

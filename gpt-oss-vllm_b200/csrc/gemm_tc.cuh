@@ -221,13 +221,41 @@ __device__ __forceinline__ uint32_t hmul2_u32(uint32_t a, uint32_t b) {
 //          dequantize_4bit (fp32 multiply, store as half), so the tensor cores see the very matrix the reference multiplies.
 //   FAST : entry = the two codes as half2, scaled by fp16(absmax) with one HMUL2: half the shared-memory wavefronts and
 //          3 instead of 5 instructions per byte; differs from EXACT by fp16 roundings of code and absmax (~2^-11 relative).
-template <bool FAST>
+// NF4 -> fp16 for the 8 nibbles of one packed word WITHOUT shared memory (FAST operand only): the 16 fp16 codes as two byte
+// planes (high bytes, low bytes), each a pair of 8-entry PRMT tables; PRMT takes four 3-bit indices at a time straight from
+// the packed data (selector = data & 0x7777), bit 3 of every nibble picks the table half through a byte mask that a
+// sign-replicating PRMT builds from the data and the data << 4, and two more PRMTs interleave the planes into half2 pairs in
+// the order the look-up table uses (element 2j = high nibble in the low half).  21 ALU instructions per word against 4 PRMT +
+// 4 LDS: the decode kernel is bound by the shared-memory data pipe (profiles/r2_notes.md), so a share of the words is moved
+// here.  Same bits as the table: the tables ARE the fp16 roundings of kNF4 (tests/test_abi_host.py checks the constants).
+constexpr uint32_t kNF4HiA = 0xb6b8b9bcu, kNF4HiB = 0x00adb1b4u, kNF4HiC = 0x3533312du, kNF4HiD = 0x3c393837u;
+constexpr uint32_t kNF4LoA = 0x52339200u, kNF4LoB = 0x00d4ea8du, kNF4LoC = 0x68e02618u, kNF4LoD = 0x00c9800du;
+__device__ __forceinline__ uint32_t sel_bytes(uint32_t a, uint32_t b, uint32_t m) { return (a & ~m) | (b & m); }   // one LOP3
+__device__ __forceinline__ void decode_word_alu(const uint32_t w, const uint32_t am2, uint32_t* out) {
+  const uint32_t s = w & 0x77777777u, w4 = w << 4;
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const uint32_t sel = half ? (s >> 16) : s;
+    const uint32_t m = prmt(w4, w, half ? 0xFBEAu : 0xD9C8u);
+    const uint32_t rh = sel_bytes(prmt(kNF4HiA, kNF4HiB, sel), prmt(kNF4HiC, kNF4HiD, sel), m);
+    const uint32_t rl = sel_bytes(prmt(kNF4LoA, kNF4LoB, sel), prmt(kNF4LoC, kNF4LoD, sel), m);
+    out[2 * half] = hmul2_u32(prmt(rl, rh, 0x4051u), am2);
+    out[2 * half + 1] = hmul2_u32(prmt(rl, rh, 0x6273u), am2);
+  }
+}
+
+// ARITH = how many of the k-block's 8 packed words per thread take the shared-memory-free path (FAST only)
+template <bool FAST, int ARITH = 0>
 __device__ __forceinline__ void decode_block(const uint4 v0, const uint4 v1, const uint32_t lut_lane, const float am,
                                              uint32_t (&regs)[32]) {
   const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
   const uint32_t am2 = FAST ? pack_half2(am, am) : 0u;
 #pragma unroll
-  for (int wi = 0; wi < 8; ++wi)
+  for (int wi = 0; wi < 8; ++wi) {
+    if (FAST && wi >= 8 - ARITH) {
+      decode_word_alu(wd[wi], am2, &regs[wi * 4]);
+      continue;
+    }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const uint32_t addr = prmt(wd[wi], lut_lane, 0x7604u | ((uint32_t)i << 4));
@@ -238,6 +266,7 @@ __device__ __forceinline__ void decode_block(const uint4 v0, const uint4 v1, con
         regs[wi * 4 + i] = pack_half2(__fmul_rn(f.x, am), __fmul_rn(f.y, am));
       }
     }
+  }
 }
 
 // Shared-memory plan around the 64 KB-aligned decode table -- the same function on the host (gemm_launch refuses a shape that
