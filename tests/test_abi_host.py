@@ -176,3 +176,40 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "nf4_oracle" not in src and not re.search(r"^\s*(from|import)\s+oracle", src, re.M), f
+
+
+def test_alu_decode_tables_are_the_fp16_nf4_codes():
+    """csrc/gemm_tc.cuh decode_word_alu (the -DNF4MOE_DEC_ARITH path): its PRMT byte-plane constants and selectors, emulated on
+    the host, give the same half2 per packed byte as the look-up table (element 2j = HIGH nibble in the low half)."""
+    import re
+    import numpy as np
+    from oracle import nf4_oracle as orc
+    src = open(os.path.join(ROOT, "gpt-oss-vllm_b200", "csrc", "gemm_tc.cuh")).read()
+    c = {m.group(1): int(m.group(2), 16) for m in re.finditer(r"(kNF4(?:Hi|Lo)[A-D]) = (0x[0-9a-f]+)u", src)}
+    assert len(c) == 8
+    h16 = np.asarray(orc.NF4_CODE, np.float32).astype(np.float16).view(np.uint16)
+
+    def prmt(a, b, sel):
+        by = [(a >> (8 * i)) & 255 for i in range(4)] + [(b >> (8 * i)) & 255 for i in range(4)]
+        r = 0
+        for i in range(4):
+            s = (sel >> (4 * i)) & 15
+            v = by[s & 7]
+            if s & 8:
+                v = 0xFF if v & 0x80 else 0
+            r |= v << (8 * i)
+        return r
+
+    def decode(w):
+        s, w4, out = w & 0x77777777, (w << 4) & 0xFFFFFFFF, []
+        for msel, sel in ((0xD9C8, s), (0xFBEA, s >> 16)):
+            m = prmt(w4, w, msel)
+            rh = (prmt(c["kNF4HiA"], c["kNF4HiB"], sel) & ~m & 0xFFFFFFFF) | (prmt(c["kNF4HiC"], c["kNF4HiD"], sel) & m)
+            rl = (prmt(c["kNF4LoA"], c["kNF4LoB"], sel) & ~m & 0xFFFFFFFF) | (prmt(c["kNF4LoC"], c["kNF4LoD"], sel) & m)
+            out += [prmt(rl, rh, 0x4051), prmt(rl, rh, 0x6273)]
+        return out
+
+    rng = np.random.default_rng(3)
+    for w in [0, 0xFFFFFFFF, 0x01234567, 0x89ABCDEF, 0xFEDCBA98, 0x76543210] + [int(v) for v in rng.integers(0, 2 ** 32, 4000)]:
+        ref = [int(h16[((w >> (8 * j)) & 255) >> 4]) | (int(h16[(w >> (8 * j)) & 15]) << 16) for j in range(4)]
+        assert decode(w) == ref, hex(w)
