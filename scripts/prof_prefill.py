@@ -19,8 +19,11 @@ p.add_argument("--reps", type=int, default=5)
 p.add_argument("--absmax", default="flat")
 p.add_argument("--check", action="store_true")
 p.add_argument("--regime", default="gemm", choices=["gemm", "gemm_fast"])
+p.add_argument("--lib", default=None)
 a = p.parse_args()
 pkg = importlib.import_module("gpt-oss-vllm_b200")
+if a.lib:
+    pkg.load_library(path=os.path.abspath(a.lib))
 dev = torch.device("cuda:0")
 H = I = 2880
 E, k = a.experts, 4
