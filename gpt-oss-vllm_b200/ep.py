@@ -19,6 +19,8 @@ Two exchange back ends:
     flags; the return path is the mirror image (csrc/ep.cuh).  No collective library on the data path, only rows that exist
     cross the link, so the capacity is the worst case (T*k rows per peer) at no cost and NO pair is ever dropped.
   * `NcclExchange`: fixed-capacity `all_to_all_single` over NCCL (round 1's path; kept as the fallback and for A/B).
+`ReplicatedMoELayer` is the other mode SURVEY 8(e) lists: activations already replicated on every rank, no dispatch, one
+all-reduce of the partial outputs.
 Every arithmetic step is a kernel of libnf4moe.  `device_ops` exists so that the choreography (buffer layout, splits, slot maps) can be exercised on CPU with
 `gloo` by the tests, which inject an oracle-backed implementation; the product default is `CudaEPOps` and nothing here
 falls back to it silently -- CUDA tensors are required unless a `device_ops` object is passed explicitly.
@@ -331,6 +333,52 @@ class EPMoELayer:
             return {"dispatch": int((rows * self.H * 2 + W * self.cap * 4 + W * 8) * off), "combine": int((rows * self.H * 2 + W * 8) * off)}
         n = W * self.cap
         return {"dispatch": int(n * (self.H * 2 + 4) * off), "combine": int(n * self.H * 2 * off)}
+
+
+class ReplicatedMoELayer:
+    """SURVEY 8(e)'s second mode, for callers whose activations are ALREADY replicated on every rank (tensor-parallel attention):
+    no dispatch at all -- every rank routes all T tokens (the router is replicated, so all ranks agree), runs only ITS experts on
+    the pairs routed to them (non-local pairs are masked with -1, which the bucket kernel drops), and the partial [T, H] outputs are
+    summed across ranks with one all-reduce (NCCL; in-switch NVLS reduction where the fabric offers it).  The sum is over fp16
+    partials, so unlike `EPMoELayer` the result is NOT bit-identical to one GPU -- it meets the MoE tolerance (tests).  Wire bytes:
+    T*H*2 per rank each way, against T*k/W rows for the dispatch mode; it pays only when the all-gather it saves the attention side
+    is worth more, which is why it is the fallback and not the default.  `w2_bias`: this rank's slice [E_local, H]."""
+
+    def __init__(self, w13, w2, plan: EPPlan, top_k: int, device, group=None, device_ops=None, nested: bool | None = None,
+                 regime: int | None = None, w13_bias=None, w2_bias=None):
+        self.w13, self.w2, self.plan, self.k, self.group = w13, w2, plan, top_k, group
+        self.device = torch.device(device)
+        if device_ops is None and self.device.type != "cuda":
+            raise RuntimeError("ReplicatedMoELayer needs a CUDA device: there is no CPU fallback on the product path")
+        self.ops, self.nested = device_ops, nested
+        self.regime = regime if regime is not None else _lib.REGIME_AUTO
+        self.w13_bias, self.w2_bias = w13_bias, w2_bias
+
+    def local_ids(self, topk_ids: torch.Tensor) -> torch.Tensor:
+        lo, n = self.plan.local_experts.start, self.plan.experts_per_rank
+        loc = topk_ids.to(torch.int32) - lo
+        return torch.where((loc >= 0) & (loc < n), loc, torch.full_like(loc, -1))
+
+    def partial(self, x, router_logits=None, topk_ids=None, topk_weights=None, out=None):
+        """This rank's share of the layer output (before the all-reduce): fp16 [T, H], zero rows for tokens none of whose experts
+        live here."""
+        if router_logits is not None:
+            topk_ids, topk_weights = (self.ops.route(router_logits, self.k) if self.ops is not None else ops.route_topk(router_logits, self.k))
+        elif topk_ids is None or topk_weights is None:
+            raise ValueError("give router_logits or (topk_ids, topk_weights)")
+        loc = self.local_ids(topk_ids)
+        if self.ops is not None:
+            return self.ops.local_forward(x, loc, topk_weights, out)
+        return ops.moe_forward(x, self.w13, self.w2, self.k, topk_ids=loc, topk_weights=topk_weights, regime=self.regime,
+                               nested=self.nested, out=out, w13_bias=self.w13_bias, w2_bias=self.w2_bias)
+
+    def forward(self, x, router_logits=None, topk_ids=None, topk_weights=None, out=None):
+        part = self.partial(x, router_logits, topk_ids, topk_weights, out)
+        if self.plan.world > 1:
+            dist.all_reduce(part, op=dist.ReduceOp.SUM, group=self.group)
+        return part
+
+    __call__ = forward
 
 
 def make_exchange(plan: EPPlan, top_k: int, hidden_size: int, max_tokens: int, device, group=None, backend: str = "auto",

@@ -66,3 +66,22 @@ class OracleEPOps:
             out.copy_(res)
             return out
         return res
+
+    def local_forward(self, x, local_ids, weights, out):              # nf4moe_moe_forward with masked (-1) non-local pairs
+        T, k = local_ids.shape
+        ids, w, x16 = local_ids.numpy(), weights.numpy(), x.numpy()
+        acc = np.zeros((T, self.w2.shape[1]), dtype=np.float32)
+        for s in range(k):
+            for e in range(self.w13.shape[0]):
+                idx = np.nonzero(ids[:, s] == e)[0]
+                if idx.size == 0:
+                    continue
+                h = orc._mm_f16_f32acc(x16[idx], self.w13[e]).astype(np.float16)
+                a = orc.swiglu_oai(h.astype(np.float32)).astype(np.float16)
+                y = orc._mm_f16_f32acc(a, self.w2[e]).astype(np.float16)
+                acc[idx] += (w[idx, s:s + 1] * y.astype(np.float32)).astype(np.float32)
+        res = torch.from_numpy(acc.astype(np.float16))
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res

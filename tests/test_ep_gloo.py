@@ -73,6 +73,51 @@ def test_ep_world2_matches_single_process_oracle(skew):
         assert cap == T * K and used == (T - rank) * K
 
 
+def _worker_replicated(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ep_oracle_ops import OracleEPOps
+        from oracle import nf4_oracle as orc
+        ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+        rng, d13, d2 = _inputs()
+        x = rng.standard_normal((T, H)).astype(np.float16)            # the SAME tokens on every rank (replicated activations)
+        lg = rng.standard_normal((T, E)).astype(np.float16)
+        plan = ep.EPPlan(rank, world, E)
+        lo, hi = plan.local_experts.start, plan.local_experts.stop
+        layer = ep.ReplicatedMoELayer(None, None, plan, K, "cpu", device_ops=OracleEPOps(d13[lo:hi], d2[lo:hi]))
+        part = layer.partial(torch.from_numpy(x), router_logits=torch.from_numpy(lg)).clone()
+        out = layer.forward(torch.from_numpy(x), router_logits=torch.from_numpy(lg))
+        ref = orc.moe_forward_ref(x, lg, d13, d2, k=K).astype(np.float32)
+        got = out.numpy().astype(np.float32)
+        ids, _ = orc.route_topk(lg, K)
+        has_local = ((ids >= lo) & (ids < hi)).any(axis=1)
+        q.put((rank, float(np.abs(got - ref).max()), float(np.linalg.norm(got - ref) / np.linalg.norm(ref)),
+               bool((part.numpy()[~has_local] == 0).all())))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_replicated_activation_mode_world2():
+    """SURVEY 8(e)'s second mode over gloo: every rank holds all tokens, computes its own experts' share, one all-reduce."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000) + 13
+    procs = [ctx.Process(target=_worker_replicated, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, max_abs, rel, zero_rows_ok in res:
+        assert max_abs <= 1e-2 and rel <= 2e-3, f"rank {rank}: {max_abs} {rel}"       # fp16 sum of two partials: tolerance, not bits
+        assert zero_rows_ok, "tokens with no local expert must contribute exactly zero"
+
+
 def test_plan_partition_and_capacity():
     ep = importlib.import_module("gpt-oss-vllm_b200.ep")
     p = ep.EPPlan(3, 8, 32)

@@ -200,3 +200,28 @@ def test_ep_pack_layout_and_overflow_flag(pkg, cuda_device):
     small.prepare(x, topk_ids=ids, topk_weights=w)
     with pytest.raises(RuntimeError):
         small.check_overflow()
+
+
+@pytest.mark.parametrize("world,T,E", [(2, 24, 32), (8, 64, 32), (4, 5, 32)])
+def test_replicated_activation_mode_virtual_ranks(pkg, cuda_device, world, T, E):
+    """SURVEY 8(e)'s second mode: every (virtual) rank gets ALL tokens, runs only its experts (non-local pairs masked with -1), and
+    the partial outputs are summed -- here in fp32 on one device, the all-reduce of the real thing being NCCL's.  Against the
+    oracle, MoE tolerance; tokens none of whose experts are local contribute exact zeros."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    H, I, k = 192, 128, 4
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 300 + world + T, E, H, I)
+    rng = np.random.default_rng(9)
+    x = torch.from_numpy(rng.standard_normal((T, H)).astype(np.float16)).to(cuda_device)
+    lg = torch.from_numpy(rng.standard_normal((T, E)).astype(np.float16)).to(cuda_device)
+    ids, _ = pkg.ops.route_topk(lg, k)
+    total = torch.zeros(T, H, dtype=torch.float32, device=cuda_device)
+    for r in range(world):
+        plan = ep.EPPlan(r, world, E)
+        layer = ep.ReplicatedMoELayer(ep.shard_experts(w13, plan), ep.shard_experts(w2, plan), plan, k, cuda_device)
+        part = layer.partial(x, router_logits=lg)
+        lo, hi = plan.local_experts.start, plan.local_experts.stop
+        none_local = ~((ids >= lo) & (ids < hi)).any(dim=1)
+        assert bool((part[none_local] == 0).all())
+        total += part.float()
+    ref = orc.moe_forward_from_states(x.cpu().numpy(), lg.cpu().numpy(), st13, st2, k=k)
+    assert_moe_close(total.half().cpu().numpy(), ref)

@@ -135,6 +135,46 @@ def test_prefill_8192_sample_vs_oracle(pkg, cuda_device, full_layer):
     assert_moe_close(out_f[pick].cpu().numpy(), ref)
 
 
+def test_expert_parallel_prefill_regime_full_size_k(pkg, cuda_device, full_layer):
+    """BASELINE.json configs[4]'s prefill leg, the regime it runs in: EPMoELayer with 160-row token tiles at K = 2880 (two virtual
+    ranks, 16 full-size experts each, 400 tokens per rank -> ~100 rows per expert, AUTO resolves to the prefill grouped GEMM
+    with the exact operand).  Bit-identical to the single-GPU layer in the same regime, and a sample against the oracle."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    w13, w2, d13, d2 = full_layer
+    world, T = 2, 400
+    layers, xs, lgs = [], [], []
+    for r in range(world):
+        plan = ep.EPPlan(r, world, E20)
+        layers.append(ep.EPMoELayer(ep.shard_experts(w13, plan), ep.shard_experts(w2, plan), plan, K20, H20, T, cuda_device))
+        assert layers[r].regime_resolved == pkg.REGIME_GEMM, "AUTO must pick the prefill grouped GEMM for ~100 rows per expert"
+        x, lg = _inputs(cuda_device, T - 7 * r, False, 4096 + r)          # ragged token counts per rank
+        xs.append(x); lgs.append(lg)
+    for r in range(world):
+        layers[r].prepare(xs[r], router_logits=lgs[r])
+    cap = layers[0].cap
+
+    def exchange(src_name, dst_name):
+        for dst in range(world):
+            for src in range(world):
+                getattr(layers[dst], dst_name)[src * cap:(src + 1) * cap].copy_(getattr(layers[src], src_name)[dst * cap:(dst + 1) * cap])
+    exchange("send_ids", "recv_ids")
+    exchange("send_rows", "recv_rows")
+    for l in layers:
+        l.compute()
+    exchange("y_rows", "back_rows")
+    for r in range(world):
+        out = layers[r].finish()
+        layers[r].check_overflow()
+        Tr = xs[r].shape[0]
+        ws = pkg.ops.new_workspace(cuda_device, Tr, E20, H20, I20, K20)
+        single = pkg.ops.moe_forward(xs[r], w13, w2, K20, router_logits=lgs[r], regime=pkg.REGIME_GEMM, workspace=ws)
+        assert pkg.ops.workspace_status(ws) == 0
+        assert torch.equal(out, single), f"rank {r}: expert-parallel prefill regime differs from the single-GPU layer"
+        pick = np.linspace(0, Tr - 1, 12).astype(np.int64)
+        ref = orc.moe_forward_ref(xs[r][pick].cpu().numpy(), lgs[r][pick].cpu().numpy(), d13, d2, k=K20)
+        assert_moe_close(out[pick].cpu().numpy(), ref)
+
+
 # ------------------------------------------------------------------------------------------------- golden pins
 def _swap_nibbles(packed: np.ndarray) -> np.ndarray:
     return ((packed >> 4) | ((packed & 0x0F) << 4)).astype(np.uint8)
