@@ -492,7 +492,7 @@ def stack_and_kernel_times(pkg, dev, stack, T, E, regime, nested, seed, reps=6):
     logits = [torch.randn(T, E, generator=g, device=dev).half() for _ in range(L)]
     outs = [torch.empty(T, H, dtype=torch.float16, device=dev) for _ in range(L)]
     ws = pkg.ops.new_workspace(dev, T, E, H, I, TOP_K)
-    eff = pkg.ops.auto_regime(T, TOP_K, E) if regime == pkg.REGIME_AUTO else regime
+    eff = pkg.ops.auto_regime(T, TOP_K, E, nested) if regime == pkg.REGIME_AUTO else regime
     use_tc = eff != pkg.REGIME_GEMV
 
     def fwd():
@@ -541,7 +541,10 @@ def stack_and_kernel_times(pkg, dev, stack, T, E, regime, nested, seed, reps=6):
             "ms_per_step": ms, "per_layer_us": ms * 1e3 / L, "tokens_per_s": T / (ms * 1e-3),
             "w13_us": d13 * 1e6, "w13_gbs": b13 / d13 / 1e9, "w13_frac": b13 / d13 / 1e9 / peak,
             "w2_us": d2 * 1e6, "w2_gbs": b2 / d2 / 1e9, "w2_frac": b2 / d2 / 1e9 / peak,
-            "whole_step_frac": (b13 + b2) * L / (ms * 1e-3) / 1e9 / peak}
+            "whole_step_frac": (b13 + b2) * L / (ms * 1e-3) / 1e9 / peak,
+            "token_tiles": ("whole stack: 64-row token tiles (nested absmax, FAST operand, > 20 rows per expert on average); the w13 / w2 "
+                            "columns time the stand-alone entry points, which keep 32-row tiles"
+                            if nested and eff == pkg.REGIME_GEMM_FAST and T * TOP_K > 20 * E else "32-row token tiles" if use_tc else "gemv")}
 
 
 def oracle_check_of_benched_output(pkg, stack, x, logits0, out0, nested, sample=8):
@@ -594,7 +597,7 @@ def run_ours(args):
         return run_ep(args, pkg, dev, rank, world, code2)
 
     regime = {"auto": pkg.REGIME_AUTO, "gemv": pkg.REGIME_GEMV, "gemm": pkg.REGIME_GEMM, "gemm_fast": pkg.REGIME_GEMM_FAST}[args.regime]
-    eff = pkg.ops.auto_regime(T, TOP_K, E) if regime == pkg.REGIME_AUTO else regime     # what AUTO resolves to
+    eff = pkg.ops.auto_regime(T, TOP_K, E, nested) if regime == pkg.REGIME_AUTO else regime     # what AUTO resolves to
     eff_name = {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "gemm_exact", pkg.REGIME_GEMM_FAST: "gemm_fast"}[eff]
     use_tc = eff != pkg.REGIME_GEMV
     dec_kernel = use_tc and (T * TOP_K <= 40 * E or (E <= 8 and T * TOP_K <= 128 * E))   # gemm_tile_tokens == 32

@@ -19,7 +19,7 @@ LOGITS_DTYPE = {"float16": 0, "float32": 1, "bfloat16": 2}
 
 # every symbol include/nf4moe.h declares (tests check the library exports exactly these)
 EXPORTED = (
-    "nf4moe_version", "nf4moe_auto_regime", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_dequant", "nf4moe_dequant_absmax",
+    "nf4moe_version", "nf4moe_auto_regime", "nf4moe_auto_regime_for", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_dequant", "nf4moe_dequant_absmax",
     "nf4moe_quantize", "nf4moe_route_topk", "nf4moe_bucket", "nf4moe_permute_rows", "nf4moe_combine",
     "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_gemm_w13_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
     "nf4moe_last_launch_count", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
@@ -54,6 +54,8 @@ def _declare(lib):
     lib.nf4moe_version.restype = i32
     lib.nf4moe_auto_regime.restype = i32
     lib.nf4moe_auto_regime.argtypes = [i32] * 3
+    lib.nf4moe_auto_regime_for.restype = i32
+    lib.nf4moe_auto_regime_for.argtypes = [i32] * 4
     lib.nf4moe_last_error.restype = C.c_char_p
     lib.nf4moe_last_launch_count.restype = i32
     lib.nf4moe_workspace_bytes.restype = sz
@@ -86,7 +88,7 @@ def _declare(lib):
     lib.nf4moe_ep_wait.argtypes = [vp, i32, vp, vp, vp]
     for name in EXPORTED:
         fn = getattr(lib, name)
-        if name not in ("nf4moe_version", "nf4moe_auto_regime", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_last_launch_count",
+        if name not in ("nf4moe_version", "nf4moe_auto_regime", "nf4moe_auto_regime_for", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_last_launch_count",
                         "nf4moe_workspace_status_offset"):
             fn.restype = i32
 

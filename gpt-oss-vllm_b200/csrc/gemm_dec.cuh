@@ -52,7 +52,7 @@ constexpr int kDecWarpProd = kDecDqWarps + 4, kDecWarpMma = kDecDqWarps + 5, kDe
 constexpr int kDecMaxRaw = 8;                              // raw-NF4 stages (16 KB each) in the shared-memory ring
 constexpr int kDecMaxB = 6;                                // activation stages (their own ring: they live until the MMAs retire)
 constexpr int kDecSlots = 3;                               // A-operand slots in TMEM: one stage = 4 k-blocks = 128 columns each
-constexpr int kDecAccCols = 32;                            // per accumulator (two of them)
+constexpr int kDecAccCols = 32;                            // per accumulator (two of them); 64 in a launch with 64-row token tiles
 constexpr uint32_t kDecRawBytes = 128 * 128;               // raw NF4 of one stage: 128 rows x 4 k-blocks x 32 B
 constexpr uint32_t kDecSmemBytes = 232448 - 1024;
 // Registers per thread.  The CTA is launched with kDecRegsLaunch per thread (what __launch_bounds__(kDecThreads, 1) lets ptxas
@@ -144,7 +144,7 @@ __host__ __device__ inline bool dec_plan_try(uint32_t base, uint32_t lut, uint32
   return p->n_raw >= kDecGroups;
 }
 
-// bmax = largest MMA N of the launch (16 or 32).  Takes the deepest activation ring that still leaves one raw stage per
+// bmax = largest MMA N of the launch (16, 32 or -- 64-row token tiles, nested absmax only: the flat form does not fit -- 64).  Takes the deepest activation ring that still leaves one raw stage per
 // dequant group (measured, K = 2880 nested, 64 tokens: 3 raw stages 80.4 us vs 6 raw stages 79.7 us per w13 launch, but 3
 // activation stages 91.6 us vs 6 stages 79.7 us: the activation ring is what has to be deep, its slots are only released by
 // retiring MMAs).  The activation ring is never shorter
@@ -154,7 +154,7 @@ __host__ __device__ inline bool dec_plan_try(uint32_t base, uint32_t lut, uint32
 __host__ __device__ inline bool dec_plan(uint32_t base, uint32_t lut, int nkb, bool nested, bool stage_code2, int bmax, DecPlan* p) {
   p->m_bytes = dec_absmax_stage_bytes(nkb, nested, stage_code2, &p->m_code2);
   p->b_stage = 4u * (uint32_t)bmax * 128u;
-  const int want_b = bmax == 16 ? kDecMaxB : 5;
+  const int want_b = bmax == 16 ? kDecMaxB : bmax == 32 ? 5 : 3;
   for (int n_b = want_b; n_b >= (kDecGroups > 3 ? kDecGroups : 3); --n_b) {
     DecPlan t = *p;
     if (!dec_plan_try(base, lut, p->m_bytes, p->b_stage, n_b, &t)) continue;
@@ -193,7 +193,8 @@ struct DecArgs {
   // CTA's window) x the two MMA widths (16 / 32): a lone device thread needs ~1.5 us for dec_plan(), on the critical path of
   // every launch.  The kernel falls back to computing it only if its window starts somewhere else.
   uint32_t plan_base[2];
-  DecPlan plan[4];      // [base index * 2 + (bmax == 32)]
+  DecPlan plan[6];      // [base index * 3 + width class (16 / 32 / 64)]; n_raw == 0: that width does not fit
+  int max_tile;         // token-tile size the tile list was built with (32 or 64)
 };
 
 // barrier slots
@@ -228,7 +229,9 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
                                                             const __grid_constant__ CUtensorMap map_x32,
                                                             const __grid_constant__ CUtensorMap map_w2,
                                                             const __grid_constant__ CUtensorMap map_h16,
-                                                            const __grid_constant__ CUtensorMap map_h32) {
+                                                            const __grid_constant__ CUtensorMap map_h32,
+                                                            const __grid_constant__ CUtensorMap map_x64,
+                                                            const __grid_constant__ CUtensorMap map_h64) {
   extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ __align__(8) uint64_t s_bar[kNumDecBars];
   __shared__ uint32_t s_tmem;
@@ -288,18 +291,20 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       if (SIDES != 1) pf(&map_w13);
       if (SIDES != 0) pf(&map_w2);
     } else {
-      if (SIDES != 1) { pf(&map_x16); pf(&map_x32); }
-      if (SIDES != 0) { pf(&map_h16); pf(&map_h32); }
+      if (SIDES != 1) { pf(&map_x16); pf(&map_x32); pf(&map_x64); }
+      if (SIDES != 0) { pf(&map_h16); pf(&map_h32); pf(&map_h64); }
     }
   }
   if (tid == 0) stamp(1);
   grid_dep_wait();
   if (tid == 0) stamp(2);
-  const int bmax = a.meta[3] <= 16 ? 16 : 32;           // largest MMA N of this launch (meta[3] = largest per-expert count)
+  // largest MMA N of this launch (meta[3] = largest per-expert count; tiles never exceed max_tile rows)
+  const int bmax = a.meta[3] <= 16 ? 16 : (a.meta[3] <= 32 || a.max_tile <= 32) ? 32 : 64;
+  const uint32_t acc_cols = bmax == 64 ? 64u : (uint32_t)kDecAccCols;
   // ---- one-time setup ----
   if (tid == 0) {
     const int bi = base == a.plan_base[0] ? 0 : base == a.plan_base[1] ? 1 : -1;
-    if (bi >= 0) s_plan = a.plan[bi * 2 + (bmax == 32 ? 1 : 0)];
+    if (bi >= 0) s_plan = a.plan[bi * 3 + (bmax == 16 ? 0 : bmax == 32 ? 1 : 2)];
     else dec_plan(base, lut, SIDES == 2 ? max(a.s[0].w.nkb, a.s[1].w.nkb) : a.s[kSide0].w.nkb, nested, !hole, bmax, &s_plan);
     if (s_plan.n_raw == 0 && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
     for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
@@ -335,7 +340,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       rt = item - tile * nrt0;
     }
   };
-  const uint32_t acol0 = 2u * kDecAccCols;   // TMEM: accumulators at columns 0 and 32, A slots after them
+  const uint32_t acol0 = 2u * acc_cols;   // TMEM: two accumulators (32 or 64 columns each), the three 128-column A slots after them
   const bool dbg_on = DBG && a.dbg != nullptr && blockIdx.x == 0 && lane == 0;   // DBG = false: every counter below folds away
   long long dbg_acc[6] = {0, 0, 0, 0, 0, 0};
 
@@ -478,12 +483,18 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       if (DBG && q == 0) stamp(it == 0 ? 6 : 7);          // first / last accumulator finished
       tc_fence_after();
       const bool row_ok = n < w_rows;
+      const int n_chunks = n_tok > 32 ? 2 : 1;              // 64-row token tiles: the accumulator is read 32 columns at a time
+#pragma unroll 1
+      for (int ch = 0; ch < n_chunks; ++ch) {
+      const int c0 = ch * 32;
       uint32_t v[32];
-      tmem_ld32(t_lane + (uint32_t)(db * kDecAccCols), v);
+      tmem_ld32(t_lane + (uint32_t)db * acc_cols + (uint32_t)c0, v);
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(kDbDEmpty + db));   // the accumulator is in registers: hand it back before the stores
+      if (ch == n_chunks - 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(kDbDEmpty + db));   // the accumulator is in registers: hand it back before the stores
+      }
       if (up_side && a.act == NF4MOE_ACT_SWIGLU_OAI) {
         // rows 2j / 2j+1 (gate / up) sit in adjacent lanes; products rounded to fp16 first (the reference stores the GEMM
         // result as fp16 before the activation); even lane takes tokens 0..15, odd lane tokens 16..31 of the tile
@@ -504,7 +515,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 #pragma unroll
           for (int i = 0; i < 8; ++i) { gt[i] = hadd2_u32(gt[i], bg2); up[i] = hadd2_u32(up[i], bu2); }
         }
-        const int t0 = odd ? 16 : 0;
+        const int t0 = c0 + (odd ? 16 : 0);
         __half* dst = h + (long long)(row0 + t0) * I + (n >> 1);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -518,14 +529,15 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         __half* raw = reinterpret_cast<__half*>(out);
 #pragma unroll
         for (int i = 0; i < 32; ++i)
-          if (row_ok && i < n_tok) raw[(long long)(row0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
+          if (row_ok && c0 + i < n_tok) raw[(long long)(row0 + c0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
       } else {
         __half* y = reinterpret_cast<__half*>(out);
 #pragma unroll
         for (int i = 0; i < 32; ++i)
-          if (row_ok && i < n_tok)
-            y[(long long)__ldg(a.sorted_pairs + row0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
+          if (row_ok && c0 + i < n_tok)
+            y[(long long)__ldg(a.sorted_pairs + row0 + c0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
       }
+      }   // chunks
       if (SIDES == 2 && up_side) {
         // publish this row tile of h: every epilogue thread's stores are ordered before the count (fence, then the four warps
         // meet on named barrier 1, then ONE release-increment at GPU scope); the w2 items of this token tile wait for all nrt0
@@ -596,9 +608,10 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         item_of(item, side, tile, rt);
         const int nkb = a.s[side].w.nkb, nst = (nkb + 3) >> 2;
         const int row0 = a.tile_list[4 * tile + 1], n_tok = a.tile_list[4 * tile + 2];
-        const int nb = n_tok <= 16 ? 16 : 32;
+        const int nb = n_tok <= 16 ? 16 : n_tok <= 32 ? 32 : 64;
         const uint32_t b_tile = (uint32_t)nb * 128u;
-        const CUtensorMap* map_x = side == 0 ? (nb == 16 ? &map_x16 : &map_x32) : (nb == 16 ? &map_h16 : &map_h32);
+        const CUtensorMap* map_x = side == 0 ? (nb == 16 ? &map_x16 : nb == 32 ? &map_x32 : &map_x64)
+                                             : (nb == 16 ? &map_h16 : nb == 32 ? &map_h32 : &map_h64);
         if (SIDES == 2 && side == 1) {
           // the tile's h rows come from the w13 items of this very launch: wait until all nrt0 of them are counted, then order
           // the (generic-proxy) acquire before the TMA (async-proxy) reads that follow
@@ -660,11 +673,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
         item_of(item, side, tile, rt);
         const int nkb = a.s[side].w.nkb, nst = (nkb + 3) >> 2;
         const int n_tok = a.tile_list[4 * tile + 2];
-        const int nb = n_tok <= 16 ? 16 : 32;
-        const uint32_t idesc = make_idesc(nb);
+        const int nb = n_tok <= 16 ? 16 : n_tok <= 32 ? 32 : 64;   // rows of the activation box (the tile's stride in shared memory)
+        const uint32_t idesc = make_idesc((n_tok + 15) & ~15);     // MMA N: the token count in 16s (48 of a 64-row box is fine)
         const uint32_t blo_step = ((uint32_t)nb * 128u) >> 4;
         const int db = it & 1;
-        const uint32_t d_t = tmem + (uint32_t)(db * kDecAccCols);
+        const uint32_t d_t = tmem + (uint32_t)db * acc_cols;
         GEMM_DBG_T0();
         mbar_wait(bar(kDbDEmpty + db), (((uint32_t)(it >> 1)) & 1u) ^ 1u);   // the epilogue has drained this accumulator
         GEMM_DBG_ADD(0);
@@ -704,9 +717,11 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 }
 
 // ---- host side ------------------------------------------------------------------------------------------------------
-// True when the decode-regime tcgen05 kernel serves this call: token tiles of at most 32 rows (either operand mode).
-inline bool dec_serves(int T, int k, int E, int mode) {
-  return (mode == NF4MOE_GEMM_FAST || mode == NF4MOE_GEMM_EXACT) && gemm_tile_tokens(T, k, E) <= 32;
+// True when the decode-regime tcgen05 kernel serves this call: token tiles of at most 64 rows (either operand mode; 64-row tiles
+// exist for nested absmax only, see gemm_tile_tokens).
+constexpr int kDecMaxTile = 64;
+inline bool dec_serves(int T, int k, int E, int mode, bool wide = false) {
+  return (mode == NF4MOE_GEMM_FAST || mode == NF4MOE_GEMM_EXACT) && gemm_tile_tokens(T, k, E, wide && mode == NF4MOE_GEMM_FAST) <= kDecMaxTile;
 }
 
 struct DecHostSide {
@@ -719,7 +734,7 @@ struct DecHostSide {
 template <int SIDES>
 int dec_launch_sides(const DecHostSide (&hs)[2], const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T,
                      int k, int E, int act, int mode, void* stream, char* err, size_t err_len, int* launches, const void* bias,
-                     int32_t* status) {
+                     int32_t* status, int tile_rows = 32) {
   const char* name = SIDES == 0 ? "gemm_w13(decode)" : SIDES == 1 ? "gemm_w2(decode)" : "gemm_w13_w2(decode)";
   auto fail = [&](int code, const char* msg) { snprintf(err, err_len, "%s: %s", name, msg); return code; };
   constexpr int s_lo = SIDES == 1 ? 1 : 0, s_hi = SIDES == 0 ? 0 : 1;
@@ -772,29 +787,36 @@ int dec_launch_sides(const DecHostSide (&hs)[2], const int32_t* sorted_pairs, co
   a.status = status ? status : const_cast<int32_t*>(meta) + 4;
   a.dbg = gemm_debug_buffer();
   a.hole_code2 = hole;
+  if (tile_rows != 16 && tile_rows != 32 && tile_rows != 64) return fail(NF4MOE_EINVAL, "the decode-regime kernel takes token tiles of 16, 32 or 64 rows");
+  a.max_tile = tile_rows;
   for (int bi = 0; bi < 2; ++bi) {
     a.plan_base[bi] = bi ? 2048u : 1024u;
-    for (int wide = 0; wide < 2; ++wide)
-      if (!dec_plan(a.plan_base[bi], kGemmLutBytes, nkb_max, nested, nested && !hole, wide ? 32 : 16, &a.plan[bi * 2 + wide]))
-        return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form");
+    for (int wide = 0; wide < 3; ++wide) {
+      const bool fits = dec_plan(a.plan_base[bi], kGemmLutBytes, nkb_max, nested, nested && !hole, 16 << wide, &a.plan[bi * 3 + wide]);
+      if (!fits && (16 << wide) <= std::max(tile_rows, 32))   // (a 64-wide plan is only needed when the tile list has 64-row tiles)
+        return fail(NF4MOE_EINVAL, "K is too large for the decode pipeline's shared-memory plan with this absmax form and token-tile size");
+    }
   }
 #ifdef NF4MOE_EXPERIMENTS
-  for (int i = 0; i < 4; ++i) {   // shallower rings for pipeline-depth measurements
+  for (int i = 0; i < 6; ++i) {   // shallower rings for pipeline-depth measurements
+    if (a.plan[i].n_raw == 0) continue;
     a.plan[i].n_raw = std::max(kDecGroups, std::min(a.plan[i].n_raw, experiment_env("NF4MOE_DEC_MAXRAW", kDecMaxRaw)) / kDecGroups * kDecGroups);
     a.plan[i].n_b = std::max(std::max(3, kDecGroups), std::min(a.plan[i].n_b, experiment_env("NF4MOE_DEC_MAXB", kDecMaxB)));
   }
 #endif
-  CUtensorMap map_w[2], map_a16[2], map_a32[2];
-  memset(map_w, 0, sizeof(map_w)); memset(map_a16, 0, sizeof(map_a16)); memset(map_a32, 0, sizeof(map_a32));
+  CUtensorMap map_w[2], map_a16[2], map_a32[2], map_a64[2];
+  memset(map_w, 0, sizeof(map_w)); memset(map_a16, 0, sizeof(map_a16)); memset(map_a32, 0, sizeof(map_a32)); memset(map_a64, 0, sizeof(map_a64));
   a.b3d = 1;
   for (int pass = 0; pass < 2; ++pass) {   // pass 0 tries the 3-D activation maps for every side, pass 1 falls back to 2-D for all
     bool ok = true;
     for (int sd = s_lo; sd <= s_hi && ok; ++sd) {
       const nf4moe_qweight* w = hs[sd].w;
       if (pass == 0) ok = make_map_x3d(&map_a16[sd], hs[sd].act_in, (uint64_t)w->cols, (uint64_t)T * k, 16) &&
-                          make_map_x3d(&map_a32[sd], hs[sd].act_in, (uint64_t)w->cols, (uint64_t)T * k, 32);
+                          make_map_x3d(&map_a32[sd], hs[sd].act_in, (uint64_t)w->cols, (uint64_t)T * k, 32) &&
+                          make_map_x3d(&map_a64[sd], hs[sd].act_in, (uint64_t)w->cols, (uint64_t)T * k, 64);
       else ok = make_map_2d(&map_a16[sd], hs[sd].act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 16) &&
-                make_map_2d(&map_a32[sd], hs[sd].act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32);
+                make_map_2d(&map_a32[sd], hs[sd].act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 32) &&
+                make_map_2d(&map_a64[sd], hs[sd].act_in, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (uint64_t)w->cols, (uint64_t)T * k, kBlock, 64);
     }
     if (ok) break;
     if (pass == 1) return fail(NF4MOE_EINVAL, "cuTensorMapEncodeTiled failed for the activations");
@@ -825,15 +847,15 @@ int dec_launch_sides(const DecHostSide (&hs)[2], const int32_t* sorted_pairs, co
 #ifdef NF4MOE_EXPERIMENTS
   if (SIDES == 0 && fast && a.dbg != nullptr) {   // the cycle-counter build exists for FAST w13 only (scripts/dec_roles.py)
     e = ensure_dyn_smem<dec_kernel<0, true, true>>((int)kDecSmemBytes);
-    if (e == cudaSuccess) e = launch_pdl(dec_kernel<0, true, true>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1]);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<0, true, true>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1], map_a64[0], map_a64[1]);
   } else
 #endif
   if (fast) {
     e = ensure_dyn_smem<dec_kernel<SIDES, true, false>>((int)kDecSmemBytes);
-    if (e == cudaSuccess) e = launch_pdl(dec_kernel<SIDES, true, false>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1]);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<SIDES, true, false>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1], map_a64[0], map_a64[1]);
   } else {
     e = ensure_dyn_smem<dec_kernel<SIDES, false, false>>((int)kDecSmemBytes);
-    if (e == cudaSuccess) e = launch_pdl(dec_kernel<SIDES, false, false>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1]);
+    if (e == cudaSuccess) e = launch_pdl(dec_kernel<SIDES, false, false>, grid, block, kDecSmemBytes, st, a, map_w[0], map_a16[0], map_a32[0], map_w[1], map_a16[1], map_a32[1], map_a64[0], map_a64[1]);
   }
   ++*launches;
   if (e == cudaSuccess) e = cudaGetLastError();
@@ -844,18 +866,20 @@ int dec_launch_sides(const DecHostSide (&hs)[2], const int32_t* sorted_pairs, co
 template <bool W13>
 int dec_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sorted_pairs, const int32_t* meta,
                const int32_t* tile_list, int T, int k, int E, int act, int mode, void* out, void* stream, char* err, size_t err_len,
-               int* launches, const void* bias = nullptr, int32_t* status = nullptr) {
+               int* launches, const void* bias = nullptr, int32_t* status = nullptr, int tile_rows = 32) {
   DecHostSide hs[2] = {{nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr}};
   hs[W13 ? 0 : 1] = DecHostSide{w, act_in, out};
-  return dec_launch_sides<W13 ? 0 : 1>(hs, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, err, err_len, launches, bias, status);
+  return dec_launch_sides<W13 ? 0 : 1>(hs, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, err, err_len, launches, bias, status,
+                                       tile_rows);
 }
 
 // w13 + SwiGLU and w2 in ONE launch: x_sorted [T k, H] -> h [T k, I] -> y [(token, slot) rows, H]
 inline int dec_launch_both(const void* x_sorted, const nf4moe_qweight* w13, void* h, const nf4moe_qweight* w2, void* y,
                            const int32_t* sorted_pairs, const int32_t* meta, const int32_t* tile_list, int T, int k, int E, int act,
-                           int mode, void* stream, char* err, size_t err_len, int* launches, const void* bias, int32_t* status) {
+                           int mode, void* stream, char* err, size_t err_len, int* launches, const void* bias, int32_t* status,
+                           int tile_rows = 32) {
   const DecHostSide hs[2] = {{w13, x_sorted, h}, {w2, h, y}};
-  return dec_launch_sides<2>(hs, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, err, err_len, launches, bias, status);
+  return dec_launch_sides<2>(hs, sorted_pairs, meta, tile_list, T, k, E, act, mode, stream, err, err_len, launches, bias, status, tile_rows);
 }
 
 }  // namespace nf4moe

@@ -35,6 +35,8 @@
 
 namespace nf4moe {
 
+constexpr int kDec64MinMeanRows = 20;   // nested absmax: mean rows per expert from which the decode kernel uses 64-row token tiles ...
+constexpr int kDec64MaxMeanRows = 80;   // ... and up to which it does (above: the prefill grouped GEMM, 160-row tiles)
 constexpr int kDecMaxMeanRows = 40;     // mean routed rows per expert up to which token tiles are 32 rows (decode tcgen05 kernel)
 constexpr int kDecAutoMinTokens = 8;    // tokens; up to this nf4moe_moe_forward(AUTO) uses the GEMV, above it a tcgen05 kernel
 constexpr int kDqGroups = 3;            // dequant warpgroups; k-block c of a CTA belongs to group c % 3
@@ -797,16 +799,23 @@ inline long long*& gemm_debug_buffer() {
 // Token-tile size (multiple of 32).  Small batches: 32-token tiles (4 KB activation stages, three 4-k-block slots in TMEM).
 // Otherwise 160: two 160-column accumulators leave 192 TMEM columns = three 2-k-block slots, and four 20 KB activation
 // stages fit beside the 64 KB decode table and two 23 KB flat-absmax stages.
-inline int gemm_tile_tokens(int T, int k, int E, bool nested = false) {
-  (void)nested;
+// wide: 64-row token tiles may be used (the caller knows it runs the decode kernel with the FAST operand on nested absmax: what
+// fits that kernel's shared memory).  Without it: round 1's 32 / 160 split, which suits either absmax form.
+inline int gemm_tile_tokens(int T, int k, int E, bool wide = false) {
   const int tile_env = experiment_env("NF4MOE_TILE", 0);   // crossover measurements (NF4MOE_EXPERIMENTS builds only)
-  if (tile_env == 32 || tile_env == 160) return tile_env;
+  if (tile_env == 32 || tile_env == 160 || (tile_env == 64 && wide)) return tile_env;
   // 32-row tiles (decode tcgen05 kernel; an expert with more rows gets several tiles and its weights are decoded once per tile)
   // while the mean routed rows per expert stay <= 40 (measured crossover with the 160-row prefill pipeline: 48 rows per expert at
   // E = 32), or <= 128 with at most 8 experts (an expert-parallel rank: few experts, so the extra tiles are what fills 148 SMs;
   // E = 4..8 measured equal or faster up to 128 rows per expert)
   const long long pairs = (long long)T * k;
-  if (pairs <= (long long)kDecMaxMeanRows * E || (E <= 8 && pairs <= 128ll * E)) return 32;
+  const bool small = pairs <= (long long)kDecMaxMeanRows * E || (E <= 8 && pairs <= 128ll * E);
+  if (!wide) return small ? 32 : 160;
+  // nested absmax (12 KB of absmax stages instead of 46 KB) leaves room for 64-row token tiles in the decode kernel: from a mean
+  // of kDec64MinMeanRows rows per expert a good share of the experts would otherwise need two 32-row tiles, i.e. decode their
+  // weights twice (round 2, T = 256 at E = 32: 183 us per layer with 32-row tiles)
+  if (pairs <= (long long)kDec64MinMeanRows * E) return 32;
+  if (pairs <= (long long)kDec64MaxMeanRows * E || (E <= 8 && pairs <= 160ll * E)) return 64;
   return 160;
 }
 
@@ -841,7 +850,7 @@ int gemm_launch(const void* act_in, const nf4moe_qweight* w, const int32_t* sort
   a.meta = meta;
   a.tile_list = tile_list;
   a.act = act;
-  a.tile_tokens = tile_rows > 0 ? tile_rows : gemm_tile_tokens(T, k, E, w->absmax_f32 == nullptr);
+  a.tile_tokens = tile_rows > 0 ? tile_rows : gemm_tile_tokens(T, k, E);   // stand-alone entry points: the size nf4moe_bucket(tile_rows = 0) used
   a.kps = a.tile_tokens <= 32 ? 4 : 2;
   a.n_a = std::min(kMaxAStages, (512 - 2 * a.tile_tokens) / (32 * a.kps));
   a.want_b = a.tile_tokens <= 32 ? 12 : 4;

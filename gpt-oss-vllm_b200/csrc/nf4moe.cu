@@ -170,13 +170,20 @@ constexpr long long kBucketClusterMinPairs = 2048;   // pairs from which the 8-C
 //   T <= 8                       mma.sync GEMV (few active experts, 3.3-3.5 TB/s; the tcgen05 pipeline's fill costs more)
 //   token tiles of <= 32 rows    decode-regime tcgen05 kernel (gemm_dec.cuh; FAST operand), 3.1-3.3 TB/s vs the GEMV's 2.4-2.9
 //   larger                       prefill tcgen05 grouped GEMM with the EXACT (bit-identical dequant) operand
-int nf4moe_auto_regime(int T, int k, int E) {
+int nf4moe_auto_regime(int T, int k, int E) { return nf4moe_auto_regime_for(T, k, E, 0); }
+// nested_absmax != 0: both weight sets carry the nested (double-quant) absmax, so the decode kernel may use 64-row token tiles and
+// its regime (FAST operand) extends to a mean of kDec64MaxMeanRows routed rows per expert (measured, E = 32: 156 us per layer at
+// T = 384 and 204 us at T = 512 against 240 / 250 us through the prefill grouped GEMM)
+int nf4moe_auto_regime_for(int T, int k, int E, int nested_absmax) {
   if (T <= kDecAutoMinTokens) return NF4MOE_REGIME_GEMV;
-  if (dec_serves(T, k, E, NF4MOE_GEMM_FAST)) return NF4MOE_REGIME_GEMM_FAST;
+  if (dec_serves(T, k, E, NF4MOE_GEMM_FAST, nested_absmax != 0)) return NF4MOE_REGIME_GEMM_FAST;
   return NF4MOE_REGIME_GEMM;
 }
 // profiling hook (not part of the public header): 64 int64 cycle counters written by CTA 0 of the tcgen05 kernels
 void nf4moe_debug_set_gemm_counters(long long* dev_ptr) { gemm_debug_buffer() = dev_ptr; }
+#ifdef NF4MOE_EXPERIMENTS
+extern "C" int nf4moe_debug_bucket_stamps(long long* out8) { return (int)cudaMemcpyFromSymbol(out8, g_bucket_stamps, 8 * sizeof(long long)); }
+#endif
 const char* nf4moe_last_error(void) { return g_err; }
 int nf4moe_last_launch_count(void) { return g_launches; }
 
@@ -394,9 +401,9 @@ int nf4moe_gemv_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
 static int gemm_w13_any(const void* x_sorted, const nf4moe_qweight* w13, const int32_t* meta, const int32_t* tile_list, int T,
                         int k, int E, int act, int mode, void* h_sorted, void* stream, const void* bias, int32_t* status,
                         int tile_rows = 0) {
-  if (tile_rows > 0 ? tile_rows <= 32 : dec_serves(T, k, E, mode))
+  if (tile_rows > 0 ? tile_rows <= kDecMaxTile : dec_serves(T, k, E, mode))
     return dec_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err, sizeof(g_err),
-                            &g_launches, bias, status);
+                            &g_launches, bias, status, tile_rows > 0 ? tile_rows : 32);
   if (bias) return fail(NF4MOE_EINVAL, "gemm_w13: the fused bias exists in the decode-regime kernel only");
   return gemm_launch<true>(x_sorted, w13, nullptr, meta, tile_list, T, k, E, act, mode, h_sorted, stream, g_err, sizeof(g_err),
                            &g_launches, status, tile_rows);
@@ -405,9 +412,9 @@ static int gemm_w13_any(const void* x_sorted, const nf4moe_qweight* w13, const i
 static int gemm_w2_any(const void* h_sorted, const nf4moe_qweight* w2, const int32_t* sorted_pairs, const int32_t* meta,
                        const int32_t* tile_list, int T, int k, int E, int mode, void* y, void* stream, int32_t* status,
                        int tile_rows = 0) {
-  if (tile_rows > 0 ? tile_rows <= 32 : dec_serves(T, k, E, mode))
+  if (tile_rows > 0 ? tile_rows <= kDecMaxTile : dec_serves(T, k, E, mode))
     return dec_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, g_err, sizeof(g_err),
-                             &g_launches, nullptr, status);
+                             &g_launches, nullptr, status, tile_rows > 0 ? tile_rows : 32);
   return gemm_launch<false>(h_sorted, w2, sorted_pairs, meta, tile_list, T, k, E, 0, mode, y, stream, g_err, sizeof(g_err),
                             &g_launches, status, tile_rows);
 }
@@ -447,18 +454,23 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     // the tcgen05 kernels need 16-row / 64-column granularity and K <= 4096; other shapes stay on the GEMV
     const bool tc_ok = w13->rows % 16 == 0 && w2->rows % 16 == 0 && w13->cols % kBlock == 0 && w2->cols % kBlock == 0 &&
                        w13->cols <= 4096 && w2->cols <= 4096;
-    regime = tc_ok ? nf4moe_auto_regime(policy_T, k, E) : NF4MOE_REGIME_GEMV;
+    regime = tc_ok ? nf4moe_auto_regime_for(policy_T, k, E, w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr && act == NF4MOE_ACT_SWIGLU_OAI)
+                   : NF4MOE_REGIME_GEMV;
   }
   if (regime != NF4MOE_REGIME_GEMV && regime != NF4MOE_REGIME_GEMM && regime != NF4MOE_REGIME_GEMM_FAST)
     return fail(NF4MOE_EINVAL, "unknown regime %d", regime);
   const bool gemm = regime != NF4MOE_REGIME_GEMV;
   const int mode = regime == NF4MOE_REGIME_GEMM_FAST ? NF4MOE_GEMM_FAST : NF4MOE_GEMM_EXACT;
-  const int tile_rows = gemm ? gemm_tile_tokens(policy_T, k, E, w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr) : 0;
+  // 64-row token tiles: decode kernel, FAST operand, nested absmax on both sides (what fits its shared memory); the EXACT regime keeps
+  // round 1's 32 / 160 split, and so do the stand-alone nf4moe_bucket / nf4moe_gemm_* entry points (they cannot know the absmax form)
+  const bool wide_ok = regime == NF4MOE_REGIME_GEMM_FAST && w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr &&
+                       act == NF4MOE_ACT_SWIGLU_OAI;
+  const int tile_rows = gemm ? gemm_tile_tokens(policy_T, k, E, wide_ok) : 0;
   if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
   *launches += g_launches; g_launches = 0;
   // with an up-projection bias the w13 kernels store their raw products and bias_act_kernel applies bias + activation
   // (the decode tcgen05 kernel adds the bias inside its fused SwiGLU epilogue instead)
-  const bool bias_fused = w13_bias && gemm && act == NF4MOE_ACT_SWIGLU_OAI && tile_rows <= 32;
+  const bool bias_fused = w13_bias && gemm && act == NF4MOE_ACT_SWIGLU_OAI && tile_rows <= kDecMaxTile;
   const bool bias_split = w13_bias && !bias_fused;
   const int act_k = bias_split ? NF4MOE_ACT_CHUNK_SILU : act;   // CHUNK_SILU = "store raw [rows, 2I]" for the w13 kernels
   __half* h_dst = act_k == NF4MOE_ACT_CHUNK_SILU ? ws.raw : ws.h;
@@ -466,10 +478,10 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     if (int rc = nf4moe_permute_rows(x, ws.sorted, ws.meta, T, k, H, ws.xs, stream)) return rc;
     *launches += g_launches; g_launches = 0;
     // decode regime with the fused activation: w13 and w2 in ONE persistent launch (gemm_dec.cuh, DecSide)
-    if (tile_rows <= 32 && act == NF4MOE_ACT_SWIGLU_OAI && !bias_split && (w13->absmax_f32 == nullptr) == (w2->absmax_f32 == nullptr) &&
+    if (tile_rows <= kDecMaxTile && act == NF4MOE_ACT_SWIGLU_OAI && !bias_split && (w13->absmax_f32 == nullptr) == (w2->absmax_f32 == nullptr) &&
         experiment_env("NF4MOE_DEC_MERGED", 1) != 0) {
       if (int rc = dec_launch_both(ws.xs, w13, ws.h, w2, y, ws.sorted, ws.meta, ws.tiles, T, k, E, act, mode, stream, g_err, sizeof(g_err),
-                                   &g_launches, bias_fused ? w13_bias : nullptr, ws.status)) return rc;
+                                   &g_launches, bias_fused ? w13_bias : nullptr, ws.status, tile_rows)) return rc;
       *launches += g_launches; g_launches = 0;
       return 0;
     }

@@ -65,61 +65,67 @@ __global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict_
   }
 }
 
-// Warp 0 of the bucket kernels: exclusive scan of the per-expert counts (E <= 256, 8 experts per lane) into s_off, and -- in
-// the same pass -- the compacted list of active experts, the token-tile list of the grouped GEMM and meta[0..3].  (Round 1 did
-// the compaction serially on one thread: ~5 us of the 11.8 us a 256-pair bucket launch took.)
+// Warp 0 of the bucket kernels: exclusive scan of the per-expert counts (E <= 256) into s_off, and -- in the same pass -- the
+// compacted list of active experts, the token-tile list of the grouped GEMM and meta[0..3].  One expert per LANE per pass of 32
+// experts (E = 32: a single pass).  Round 2 measured the earlier form -- 8 consecutive experts per lane, fully unrolled, three
+// integer divisions each -- at 5.4 us (T = 1) to 8.9 us (T = 256) of a lone warp's dependent instructions, most of the bucket
+// kernel and ~7 % of a decode layer (scripts/bucket_stamps.py); round 1's serial compaction on one thread was slower still.
 // Token tiles: an expert's c rows split into ceil(c / tile_rows) near-equal tiles (multiples of 16 rows).
 __device__ __forceinline__ void bucket_scan_and_lists(const int* s_count, int* s_off, int E, int lane, int32_t* expert_offsets,
                                                       int32_t* active_experts, int32_t* meta, int32_t* tile_list, int tile_rows,
                                                       bool write_global) {
-  int cnt[8], loc[8], tsz[8], run = 0, act = 0, tiles = 0, mx = 0;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int e = lane * 8 + j;
+  int run_base = 0, act_base = 0, tile_base = 0, mx = 0;
+  const int n_pass = (E + 31) >> 5;
+#pragma unroll 1
+  for (int j = 0; j < n_pass; ++j) {
+    const int e = j * 32 + lane;
     const int c = e < E ? s_count[e] : 0;
-    cnt[j] = c;
-    loc[j] = run;
-    run += c;
-    tsz[j] = 0;
+    int tsz = 0, nt = 0;
     if (c > 0) {
-      ++act;
-      mx = max(mx, c);
-      const int ntl = (c + tile_rows - 1) / tile_rows;
-      tsz[j] = (((c + ntl - 1) / ntl) + 15) & ~15;
-      tiles += (c + tsz[j] - 1) / tsz[j];
+      // ceil(a / b) for 0 < a, b < 2^20 through one reciprocal and a +-1 correction: the integer-division sequences were most of
+      // this function's code, and a lone warp running cold straight-line code pays an instruction-cache miss per 8 instructions
+      auto cdiv = [](int a, int b) {
+        int q = __float2int_rz(__fdividef((float)a, (float)b));
+        q += (q + 1) * b <= a ? 1 : 0;
+        q -= q * b > a ? 1 : 0;
+        return q + (q * b < a ? 1 : 0);
+      };
+      const int ntl = cdiv(c, tile_rows);
+      tsz = (cdiv(c, ntl) + 15) & ~15;
+      nt = cdiv(c, tsz);
     }
-  }
-  int inc = run, inc_a = act, inc_t = tiles;
+    mx = max(mx, c);
+    int inc = c, inc_a = c > 0 ? 1 : 0, inc_t = nt;
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int n = __shfl_up_sync(0xffffffffu, inc, o), na = __shfl_up_sync(0xffffffffu, inc_a, o), nt = __shfl_up_sync(0xffffffffu, inc_t, o);
-    if (lane >= o) { inc += n; inc_a += na; inc_t += nt; }
+    for (int o = 1; o < 32; o <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, inc, o), na = __shfl_up_sync(0xffffffffu, inc_a, o), nn = __shfl_up_sync(0xffffffffu, inc_t, o);
+      if (lane >= o) { inc += n; inc_a += na; inc_t += nn; }
+    }
+    const int off = run_base + inc - c;
+    s_off[e] = off;                      // e <= 255
+    if (write_global) {
+      if (e < E) expert_offsets[e] = off;
+      if (c > 0) {
+        active_experts[act_base + inc_a - 1] = e;
+        if (tile_list) {
+          int t = tile_base + inc_t - nt;
+#pragma unroll 1
+          for (int r = 0; r < c; r += tsz, ++t) *reinterpret_cast<int4*>(tile_list + 4 * t) = make_int4(e, off + r, min(tsz, c - r), 0);
+        }
+      }
+    }
+    run_base += __shfl_sync(0xffffffffu, inc, 31);
+    act_base += __shfl_sync(0xffffffffu, inc_a, 31);
+    tile_base += __shfl_sync(0xffffffffu, inc_t, 31);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-  const int base = inc - run;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) s_off[lane * 8 + j] = base + loc[j];
-  if (lane == 31) s_off[256] = inc;
+  if (lane == 0) s_off[256] = run_base;
   if (!write_global) return;
-  const int total = __shfl_sync(0xffffffffu, inc, 31), n_act = __shfl_sync(0xffffffffu, inc_a, 31), n_tiles = __shfl_sync(0xffffffffu, inc_t, 31);
-  int ia = inc_a - act, it = inc_t - tiles;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const int e = lane * 8 + j, c = cnt[j];
-    if (e <= E) expert_offsets[e] = e < E ? base + loc[j] : total;
-    if (c > 0) {
-      active_experts[ia++] = e;
-      if (tile_list)
-        for (int r = 0; r < c; r += tsz[j]) {
-          *reinterpret_cast<int4*>(tile_list + 4 * it) = make_int4(e, base + loc[j] + r, min(tsz[j], c - r), 0);
-          ++it;
-        }
-    }
-  }
-  if (E == 256 && lane == 31) expert_offsets[256] = total;
-  for (int i = n_act + lane; i < E; i += 32) active_experts[i] = -1;
-  if (lane == 0) { meta[0] = n_act; meta[1] = total; meta[2] = n_tiles; meta[3] = mx; }
+  if (lane == 0) expert_offsets[E] = run_base;
+#pragma unroll 1
+  for (int i = act_base + lane; i < E; i += 32) active_experts[i] = -1;   // (unrolled 16x this was a fifth of the function's code)
+  if (lane == 0) { meta[0] = act_base; meta[1] = run_base; meta[2] = tile_base; meta[3] = mx; }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -129,6 +135,12 @@ __device__ __forceinline__ void bucket_scan_and_lists(const int* s_count, int* s
 // P/unsloth_to_vllm_converter.py:298-305.
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kBucketThreads = 1024;
+#ifdef NF4MOE_EXPERIMENTS
+__device__ long long g_bucket_stamps[8];
+#define BUCKET_STAMP(i) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_bucket_stamps[i] = (long long)t_; } } while (0)
+#else
+#define BUCKET_STAMP(i) do { } while (0)
+#endif
 
 __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* __restrict__ ids, int n_pairs, int E,
                                                                 int32_t* __restrict__ expert_offsets,
@@ -140,8 +152,10 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
   __shared__ int s_count[256];
   __shared__ int s_off[257];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  BUCKET_STAMP(0);
   grid_dep_launch();
   grid_dep_wait();
+  BUCKET_STAMP(1);
   const int n_pad = (n_pairs + 127) & ~127;
   for (int i = tid; i < n_pad; i += kBucketThreads) {
     int e = i < n_pairs ? ids[i] : -1;
@@ -149,6 +163,7 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
   }
   if (tid < 256) s_count[tid] = 0;
   __syncthreads();
+  BUCKET_STAMP(2);
   // ids are read four at a time (one 32-bit shared-memory load per lane = 128 pairs per warp iteration); n_pad128 rounds
   // the scan up to whole iterations, the tail is 0xFF (never matches)
   const int n_pad128 = (n_pairs + 127) & ~127;
@@ -165,8 +180,10 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
     if (lane == 0) s_count[e] = c;
   }
   __syncthreads();
+  BUCKET_STAMP(3);
   if (warp == 0) bucket_scan_and_lists(s_count, s_off, E, lane, expert_offsets, active_experts, meta, tile_list, tile_rows, true);
   __syncthreads();
+  BUCKET_STAMP(4);
   for (int e = warp; e < E; e += 32) {
     const uint32_t pat = 0x01010101u * (uint32_t)e;
     int run = s_off[e];
@@ -186,6 +203,7 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
       run += __shfl_sync(0xffffffffu, inc, 31);
     }
   }
+  BUCKET_STAMP(5);
 }
 
 // Prefill-sized batches: the same stable counting sort by ONE thread-block cluster of kBucketCluster CTAs (the single CTA takes

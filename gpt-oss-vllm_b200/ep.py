@@ -255,7 +255,10 @@ class EPMoELayer:
         self.regime = regime if regime is not None else _lib.REGIME_AUTO
         self.regime_resolved = self.regime
         if self.regime == _lib.REGIME_AUTO and self.device.type == "cuda" and w13 is not None:
-            self.regime_resolved = int(_lib.load_library().nf4moe_auto_regime(self.rows_hint, 1, w13.num_experts))
+            nested = getattr(device_ops, "nested", None)
+            nested_both = all((nested if nested is not None else w.absmax is None) for w in (w13, w2))
+            fused_act = getattr(device_ops, "act", _lib.ACT_SWIGLU_OAI) == _lib.ACT_SWIGLU_OAI
+            self.regime_resolved = ops.auto_regime(self.rows_hint, 1, w13.num_experts, nested_both and fused_act)
         self.pair_slot = torch.full((max_tokens * top_k,), -1, dtype=torch.int32, device=self.device)
         self.status = getattr(exchange, "status", None)
         if self.status is None:

@@ -120,9 +120,10 @@ def bucket(ids: torch.Tensor, E: int, want_tiles: bool = True, tile_rows: int = 
     return out
 
 
-def auto_regime(T: int, k: int, E: int) -> int:
-    """The regime REGIME_AUTO resolves to (nf4moe_auto_regime)."""
-    return int(_lib.load_library().nf4moe_auto_regime(T, k, E))
+def auto_regime(T: int, k: int, E: int, nested_absmax: bool = False) -> int:
+    """The regime REGIME_AUTO resolves to (nf4moe_auto_regime[_for]).  nested_absmax: both weight sets are passed with the nested
+    absmax and the activation is the fused gpt-oss one (the decode kernel then has 64-row token tiles and a wider regime)."""
+    return int(_lib.load_library().nf4moe_auto_regime_for(T, k, E, 1 if nested_absmax else 0))
 
 
 def permute_rows(x: torch.Tensor, b: dict, k: int) -> torch.Tensor:

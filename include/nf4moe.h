@@ -91,6 +91,10 @@ int nf4moe_version(void);
 /* The regime NF4MOE_REGIME_AUTO resolves to for T tokens, top-k k, E experts (pure function of its arguments; replaces the
  * reference's absence of any regime choice: its forward is a per-(token, slot) Python loop, P/unsloth_to_vllm_converter.py:298-323). */
 int nf4moe_auto_regime(int T, int k, int E);
+/* The same for a layer whose w13 AND w2 carry the nested absmax (nested_absmax != 0) and the fused gpt-oss activation: the decode-regime
+ * kernel then takes 64-row token tiles and serves up to a mean of 80 routed rows per expert.  nf4moe_moe_forward / nf4moe_expert_rows
+ * with NF4MOE_REGIME_AUTO resolve through this function. */
+int nf4moe_auto_regime_for(int T, int k, int E, int nested_absmax);
 const char* nf4moe_last_error(void);
 
 /* Scratch the fused forward needs for T tokens (bytes).  Layout is private to the library. */

@@ -276,6 +276,47 @@ def test_decode_kernel_exact_vs_fast_vs_oracle(pkg, cuda_device, T, E, H, I, k):
     pkg.ops.check_status()
 
 
+@pytest.mark.parametrize("T,E,H,I,k,skew", [(256, 32, 320, 128, 4, False), (200, 8, 256, 192, 4, False), (160, 4, 192, 128, 2, True),
+                                            (192, 32, 2880, 128, 4, True)])
+def test_decode_kernel_64_row_token_tiles(pkg, cuda_device, T, E, H, I, k, skew):
+    """Round 2: with nested absmax (and the FAST operand) the decode-regime kernel takes token tiles of up to 64 rows (64-column
+    accumulators, 64-row activation boxes, the epilogue reads the accumulator 32 columns at a time), so an expert with 33..64 routed
+    rows is decoded once instead of twice.  Shapes with tiles of 33..48 and 49..64 rows, experts that need several 64-row tiles,
+    K = 2880 (45 k-blocks, 3-stage activation ring), with and without the fused up-projection bias; against the oracle and
+    against the GEMV regime.  AUTO resolves to this path for these shapes."""
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 640 + T, E, H, I, 0.02 if H > 1000 else 0.05)
+    rng = np.random.default_rng(T + 3 * E)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    if skew:
+        lg[np.arange(T), np.arange(T) % 2] += 3.0        # two hot experts: > 64 rows each, the rest ragged
+    xd, lgd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(lg).to(cuda_device)
+    assert pkg.ops.auto_regime(T, k, E, True) == pkg.REGIME_GEMM_FAST
+    ids, _ = orc.route_topk(lg, k)
+    counts = np.bincount(ids.reshape(-1), minlength=E)
+    assert counts.max() > 32, "the case must need tiles wider than 32 rows"
+    ws = pkg.ops.new_workspace(cuda_device, T, E, H, I, k)
+    out = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, nested=True, workspace=ws)           # AUTO
+    assert pkg.ops.workspace_status(ws) == 0
+    ref = orc.moe_forward_from_states(x, lg, st13, st2, k=k)
+    assert_moe_close(out.cpu().numpy(), ref)
+    out_f = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, nested=True, regime=pkg.REGIME_GEMM_FAST, workspace=ws)
+    assert torch.equal(out, out_f)
+    out_v = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, nested=True, regime=pkg.REGIME_GEMV)
+    assert_moe_close(out.cpu().numpy(), out_v.cpu().numpy())
+    # flat absmax keeps 32-row tiles (the 64-row plan does not fit next to 46 KB of absmax stages): same operand, same arithmetic
+    # per (row, token) -> bit-identical
+    out_flat = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, nested=False, regime=pkg.REGIME_GEMM_FAST)
+    assert torch.equal(out, out_flat)
+    # fused up-projection bias in the 64-column epilogue
+    b13 = (rng.standard_normal((E, 2 * I)) * 0.5).astype(np.float16)
+    b2 = (rng.standard_normal((E, H)) * 0.5).astype(np.float16)
+    out_b = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, nested=True, w13_bias=torch.from_numpy(b13).to(cuda_device),
+                                w2_bias=torch.from_numpy(b2).to(cuda_device), workspace=ws)
+    assert pkg.ops.workspace_status(ws) == 0
+    assert_moe_close(out_b.cpu().numpy(), orc.moe_forward_from_states(x, lg, st13, st2, k=k, b13=b13, b2=b2))
+
+
 def test_per_expert_code2_tables(pkg, cuda_device):
     """code2_stride = 256 (one double-quant table per expert): the decode kernel then stages the expert's table per item
     instead of using the per-lane copy in the decode table's holes; results must not change."""
