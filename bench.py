@@ -465,7 +465,7 @@ def run_ep(args, pkg, dev, rank, world, code2):
                 "ep_matches_single_gpu": ep_matches, "ep_vs_single_gpu_max_abs_diff": ep_maxdiff,
                 "e2e": {"value": T_all / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2 + hlg.numel() * 2,
                         "d2h_bytes_per_step": hout.numel() * 2, "ms_per_step": e2e_ms, "api": e2e_api},
-                "gpu_launches": (pkg.ops.last_launch_count() + (7 if exchange.kind == "p2p" else 5)) * L * K,
+                "gpu_launches": (pkg.ops.last_launch_count() + 5) * L * K,
                 "collectives_per_layer": exchange.collectives_per_layer, "wire_bytes_per_rank_per_layer": wire,
                 "roofline": {"bound": "hbm", "kernel": "expert_rows chain (bucket + permute + w13 + w2) on this rank's experts",
                              "achieved": wbytes / d / 1e9, "peak": peak, "unit": "GB/s", "frac": wbytes / d / 1e9 / peak,

@@ -83,8 +83,8 @@ def _declare(lib):
     lib.nf4moe_combine_indexed.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]
     lib.nf4moe_expert_rows_bias.argtypes = [vp, vp, qp, qp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, sz, vp]
     lib.nf4moe_combine_indexed_bias.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, vp]
-    lib.nf4moe_ep_dispatch_p2p.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
-    lib.nf4moe_ep_return_p2p.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, vp, vp]
+    lib.nf4moe_ep_dispatch_p2p.argtypes = [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.nf4moe_ep_return_p2p.argtypes = [vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     lib.nf4moe_ep_wait.argtypes = [vp, i32, vp, vp, vp]
     for name in EXPORTED:
         fn = getattr(lib, name)

@@ -120,7 +120,13 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned 
 
 // Last-CTA-done: every CTA fences its (peer) stores at system scope and takes a ticket; the CTA that draws the last one
 // bumps the epoch and publishes it to all peers.  ctr[0] = ticket, ctr[1] = epoch (reset / advanced here).
-__device__ __forceinline__ void ep_publish_epoch(unsigned int* ctr, const EpPeers& peers, int world, int rank) {
+// wait_flags / wait_ctr (optional): after publishing, the same last CTA also WAITS until every peer's flag for this rank has reached
+// this rank's next wait epoch (wait_ctr[0], advanced here), so the kernel completes only when all peers' rows have landed and no
+// separate one-warp wait launch sits between it and its consumer.  Only for one process per GPU: with several virtual ranks on one
+// stream the peers' kernels are queued BEHIND this one and the wait would never end (the tests use the separate wait kernel).
+__device__ __forceinline__ void ep_publish_epoch(unsigned int* ctr, const EpPeers& peers, int world, int rank,
+                                                 const unsigned long long* wait_flags = nullptr, unsigned int* wait_ctr = nullptr,
+                                                 int32_t* status = nullptr) {
   __shared__ unsigned int s_last;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -129,14 +135,27 @@ __device__ __forceinline__ void ep_publish_epoch(unsigned int* ctr, const EpPeer
   }
   __syncthreads();
   if (s_last) {
+    __shared__ unsigned int s_wait_epoch;
     if (threadIdx.x == 0) {
       __threadfence_system();
       ctr[0] = 0u;
       ctr[1] += 1u;
+      if (wait_flags != nullptr) { s_wait_epoch = wait_ctr[0] + 1u; wait_ctr[0] = s_wait_epoch; }
     }
     __syncthreads();
     const unsigned long long epoch = ctr[1];
     if ((int)threadIdx.x < world) st_release_sys_u64(peers.flags[threadIdx.x] + rank, epoch);
+    if (wait_flags != nullptr) {
+      if ((int)threadIdx.x < world) {
+        const unsigned long long want = s_wait_epoch;
+        unsigned long long spins = 0;
+        while (ld_acquire_sys_u64(wait_flags + threadIdx.x) < want) {
+          if (++spins > (1ull << 27)) { if (status) atomicOr(status, 8); break; }   // a peer died or never launched
+          __nanosleep(64);
+        }
+      }
+      __threadfence_system();
+    }
   }
 }
 
@@ -145,17 +164,27 @@ __global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* __restri
                                                           const int32_t* __restrict__ expert_offsets,
                                                           const int32_t* __restrict__ sorted_pairs, int k, int H, int world, int rank,
                                                           int e_local, int cap, const EpPeers peers, int32_t* __restrict__ pair_slot,
-                                                          unsigned int* __restrict__ ctr, int32_t* __restrict__ status) {
+                                                          unsigned int* __restrict__ ctr, int32_t* __restrict__ status, int n_pairs,
+                                                          const unsigned long long* wait_flags, unsigned int* wait_ctr) {
   grid_dep_launch();
   grid_dep_wait();
   const int lane = threadIdx.x & 31;
   const int n_slots = world * cap;
   const int vec = H / 8;
+  // pairs whose expert id is outside [0, E) are not in the sorted list: mark them "not dispatched" here (every other pair gets its
+  // slot below, a different word), instead of a memset node in front of every dispatch
+  for (int pr = blockIdx.x * blockDim.x + threadIdx.x; pr < n_pairs; pr += gridDim.x * blockDim.x) {
+    const int id = ids[pr];
+    if (id < 0 || id >= world * e_local) pair_slot[pr] = -1;
+  }
   for (int slot = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; slot < n_slots; slot += (gridDim.x * blockDim.x) >> 5) {
     const int p = slot / cap, j = slot - p * cap;
     const int start = expert_offsets[p * e_local];
     const int cnt = expert_offsets[(p + 1) * e_local] - start;
-    if (j == 0 && lane == 0 && cnt > cap) atomicOr(status, 1);
+    if (j == 0 && cnt > cap) {   // capacity below the worst case: the pairs past it are dropped (flagged) and marked
+      if (lane == 0) atomicOr(status, 1);
+      for (int jj = cap + lane; jj < cnt; jj += 32) pair_slot[sorted_pairs[start + jj]] = -1;
+    }
     const long long dst_slot = (long long)rank * cap + j;
     if (j < cnt) {
       const int pair = sorted_pairs[start + j];
@@ -176,13 +205,14 @@ __global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* __restri
       peers.ids[p][dst_slot] = -1;
     }
   }
-  ep_publish_epoch(ctr, peers, world, rank);
+  ep_publish_epoch(ctr, peers, world, rank, wait_flags, wait_ctr, status);
 }
 
 // Return: row (q, j) of this rank's expert outputs (valid where recv_ids >= 0) -> home rank q's back_rows chunk `rank`.
 __global__ void __launch_bounds__(256) ep_return_kernel(const __half* __restrict__ y_rows, const int32_t* __restrict__ recv_ids, int H,
                                                         int world, int rank, int cap, const EpPeers peers,
-                                                        unsigned int* __restrict__ ctr) {
+                                                        unsigned int* __restrict__ ctr, const unsigned long long* wait_flags,
+                                                        unsigned int* wait_ctr, int32_t* status) {
   grid_dep_launch();
   grid_dep_wait();
   const int lane = threadIdx.x & 31;
@@ -201,7 +231,7 @@ __global__ void __launch_bounds__(256) ep_return_kernel(const __half* __restrict
       for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) dst[i] = v[u]; }
     }
   }
-  ep_publish_epoch(ctr, peers, world, rank);
+  ep_publish_epoch(ctr, peers, world, rank, wait_flags, wait_ctr, status);
 }
 
 // One warp: advance this rank's wait epoch (ctr[0]) and spin until every peer's flag has reached it.  A peer that never

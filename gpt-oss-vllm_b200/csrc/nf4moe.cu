@@ -648,7 +648,9 @@ static int fill_peers(EpPeers* peers, void* const* rows, void* const* ids, void*
 
 int nf4moe_ep_dispatch_p2p(const void* x, const int32_t* ids, const int32_t* expert_offsets, const int32_t* sorted_pairs, int T, int k,
                            int E, int H, int world, int rank, int cap, void* const* peer_recv_rows, void* const* peer_recv_ids,
-                           void* const* peer_flags, int32_t* pair_slot, uint32_t* ctr, int32_t* status, void* stream) {
+                           void* const* peer_flags, int32_t* pair_slot, uint32_t* ctr, int32_t* status, const void* wait_flags,
+                           uint32_t* wait_ctr, void* stream) {
+  if ((wait_flags != nullptr) != (wait_ctr != nullptr)) return fail(NF4MOE_EINVAL, "ep_dispatch_p2p: give wait_flags and wait_ctr together");
   if (!x || !ids || !expert_offsets || !sorted_pairs || !pair_slot || !ctr || !status || T < 0 || k <= 0 || E <= 0 || H <= 0 || H % 8 ||
       cap <= 0 || rank < 0 || rank >= world || E % world)
     return fail(NF4MOE_EINVAL, "ep_dispatch_p2p: bad arguments (E must be a multiple of world, H of 8)");
@@ -658,18 +660,20 @@ int nf4moe_ep_dispatch_p2p(const void* x, const int32_t* ids, const int32_t* exp
   DevInfo di;
   if (int rc = device_info(&di)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(pair_slot, 0xFF, (size_t)T * k * 4, st);   // -1: not dispatched
-  if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(pair_slot)");
   const long long slots = (long long)world * cap;
   const int grid = (int)std::min<long long>((slots + 7) / 8, (long long)di.sms * 4);
+  // (plain launches: these kernels read the router's and the bucket kernel's outputs through const __restrict__ pointers)
   ep_dispatch_kernel<<<grid, 256, 0, st>>>((const __half*)x, ids, expert_offsets, sorted_pairs, k, H, world, rank, E / world, cap, peers,
-                                          pair_slot, ctr, status);
+                                          pair_slot, (unsigned int*)ctr, status, T * k, (const unsigned long long*)wait_flags,
+                                          (unsigned int*)wait_ctr);
   CHECK_LAUNCH("ep_dispatch_kernel");
   return 0;
 }
 
 int nf4moe_ep_return_p2p(const void* y_rows, const int32_t* recv_ids, int H, int world, int rank, int cap, void* const* peer_back_rows,
-                         void* const* peer_flags, uint32_t* ctr, void* stream) {
+                         void* const* peer_flags, uint32_t* ctr, const void* wait_flags, uint32_t* wait_ctr, int32_t* status,
+                         void* stream) {
+  if ((wait_flags != nullptr) != (wait_ctr != nullptr)) return fail(NF4MOE_EINVAL, "ep_return_p2p: give wait_flags and wait_ctr together");
   if (!y_rows || !recv_ids || !ctr || H <= 0 || H % 8 || cap <= 0 || rank < 0 || rank >= world)
     return fail(NF4MOE_EINVAL, "ep_return_p2p: bad arguments");
   if (!aligned16(y_rows)) return fail(NF4MOE_EALIGN, "ep_return_p2p: y_rows must be 16-byte aligned");
@@ -679,7 +683,8 @@ int nf4moe_ep_return_p2p(const void* y_rows, const int32_t* recv_ids, int H, int
   if (int rc = device_info(&di)) return rc;
   const long long slots = (long long)world * cap;
   const int grid = (int)std::min<long long>((slots + 7) / 8, (long long)di.sms * 4);
-  ep_return_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y_rows, recv_ids, H, world, rank, cap, peers, ctr);
+  ep_return_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __half*)y_rows, recv_ids, H, world, rank, cap, peers, (unsigned int*)ctr,
+                                                          (const unsigned long long*)wait_flags, (unsigned int*)wait_ctr, status);
   CHECK_LAUNCH("ep_return_kernel");
   return 0;
 }

@@ -163,6 +163,7 @@ class PeerExchange:
         self.flags.zero_()
         self._tables = None
         self._keep = None
+        self.fused_wait = False   # one process per GPU (symmetric()): the dispatch / return kernels wait for the peers themselves
 
     @staticmethod
     def layout(W: int, cap: int, H: int) -> dict:
@@ -195,6 +196,7 @@ class PeerExchange:
         hdl = symm_mem.rendezvous(storage, grp)
         self = cls(plan, cap, hidden_size, device, storage)
         self._keep = hdl
+        self.fused_wait = True
         torch.cuda.synchronize(device)
         dist.barrier(group=group)          # every rank has zeroed its flags before anyone writes one
         self._set_tables([int(p) for p in hdl.buffer_ptrs])
@@ -216,17 +218,21 @@ class PeerExchange:
     # the two halves of each direction are separate calls so that tests can interleave virtual ranks
     def dispatch_from(self, x, ids, b, E, k, pair_slot):
         ops.ep_dispatch_p2p(x, ids, b, E, self.plan.world, self.plan.rank, self.cap, self._tables["recv_rows"], self._tables["recv_ids"],
-                            self._tables["flags_dispatch"], pair_slot, self.ctr[0:2], self.status)
+                            self._tables["flags_dispatch"], pair_slot, self.ctr[0:2], self.status,
+                            *((self.flags[0], self.ctr[4:6]) if self.fused_wait else ()))
 
     def wait_dispatch(self):
-        ops.ep_wait(self.flags[0], self.plan.world, self.ctr[4:6], self.status)
+        if not self.fused_wait:
+            ops.ep_wait(self.flags[0], self.plan.world, self.ctr[4:6], self.status)
 
     def ret(self):
         ops.ep_return_p2p(self.y_rows, self.recv_ids, self.plan.world, self.plan.rank, self.cap, self._tables["back_rows"],
-                          self._tables["flags_return"], self.ctr[2:4])
+                          self._tables["flags_return"], self.ctr[2:4],
+                          *((self.flags[1], self.ctr[6:8], self.status) if self.fused_wait else ()))
 
     def wait_return(self):
-        ops.ep_wait(self.flags[1], self.plan.world, self.ctr[6:8], self.status)
+        if not self.fused_wait:
+            ops.ep_wait(self.flags[1], self.plan.world, self.ctr[6:8], self.status)
 
 
 class EPMoELayer:

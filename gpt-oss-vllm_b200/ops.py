@@ -325,8 +325,10 @@ def combine_indexed(y: torch.Tensor, weights: torch.Tensor, pair_slot: torch.Ten
 
 # ---- peer-memory exchange (nf4moe_ep_dispatch_p2p / nf4moe_ep_wait / nf4moe_ep_return_p2p) ---------------------------------
 def ep_dispatch_p2p(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: int, rank: int, cap: int, peer_recv_rows,
-                    peer_recv_ids, peer_flags, pair_slot: torch.Tensor, ctr: torch.Tensor, status: torch.Tensor) -> None:
-    """Store this rank's routed rows straight into their owners' receive buffers (peer_* are ctypes arrays of device pointers)."""
+                    peer_recv_ids, peer_flags, pair_slot: torch.Tensor, ctr: torch.Tensor, status: torch.Tensor,
+                    wait_flags: torch.Tensor | None = None, wait_ctr: torch.Tensor | None = None) -> None:
+    """Store this rank's routed rows straight into their owners' receive buffers (peer_* are ctypes arrays of device pointers).
+    wait_flags / wait_ctr: also wait, in the same launch, for every peer's rows to land here (one process per GPU only)."""
     _require_cuda(x, "x")
     T, H = x.shape
     k = ids.shape[1]
@@ -334,16 +336,19 @@ def ep_dispatch_p2p(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: 
         _lib.check(_lib.load_library().nf4moe_ep_dispatch_p2p(
             x.data_ptr(), ids.data_ptr(), b["expert_offsets"].data_ptr(), b["sorted_pairs"].data_ptr(), T, k, E, H, world, rank, cap,
             C.cast(peer_recv_rows, C.c_void_p), C.cast(peer_recv_ids, C.c_void_p), C.cast(peer_flags, C.c_void_p),
-            pair_slot.data_ptr(), ctr.data_ptr(), status.data_ptr(), _stream_ptr(x.device)))
+            pair_slot.data_ptr(), ctr.data_ptr(), status.data_ptr(), None if wait_flags is None else wait_flags.data_ptr(),
+            None if wait_ctr is None else wait_ctr.data_ptr(), _stream_ptr(x.device)))
 
 
 def ep_return_p2p(y_rows: torch.Tensor, recv_ids: torch.Tensor, world: int, rank: int, cap: int, peer_back_rows, peer_flags,
-                  ctr: torch.Tensor) -> None:
+                  ctr: torch.Tensor, wait_flags: torch.Tensor | None = None, wait_ctr: torch.Tensor | None = None,
+                  status: torch.Tensor | None = None) -> None:
     H = y_rows.shape[-1]
     with torch.cuda.device(y_rows.device):
         _lib.check(_lib.load_library().nf4moe_ep_return_p2p(
             y_rows.data_ptr(), recv_ids.data_ptr(), H, world, rank, cap, C.cast(peer_back_rows, C.c_void_p),
-            C.cast(peer_flags, C.c_void_p), ctr.data_ptr(), _stream_ptr(y_rows.device)))
+            C.cast(peer_flags, C.c_void_p), ctr.data_ptr(), None if wait_flags is None else wait_flags.data_ptr(),
+            None if wait_ctr is None else wait_ctr.data_ptr(), None if status is None else status.data_ptr(), _stream_ptr(y_rows.device)))
 
 
 def ep_wait(flags: torch.Tensor, world: int, ctr: torch.Tensor, status: torch.Tensor) -> None:

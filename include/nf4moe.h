@@ -261,14 +261,19 @@ int nf4moe_combine_indexed_bias(const void* y, const float* weights, const int32
  *                            status |= NF4MOE_STATUS_EP_TIMEOUT if a peer never arrives.
  *   nf4moe_ep_return_p2p     owner rank: stores y_rows[q*cap + j] (where recv_ids >= 0) into home rank q's back_rows[rank, j] and
  *                            publishes to flags[1][rank] of every peer; nf4moe_combine_indexed[_bias] then reads back_rows.
+ * wait_flags / wait_ctr (both or neither; one process per GPU only): the dispatch / return kernel itself then waits, after publishing,
+ * for THIS rank's flag row (flags[0] resp. flags[1]) to reach its next epoch -- the call returns a stream on which the peers' rows
+ * have landed and the separate nf4moe_ep_wait launch is not needed.
  * Epochs live in device memory and advance once per launch, so a layer built from these calls replays from a CUDA graph.  Every
  * rank must issue the same sequence of calls (SPMD).  Replaces nothing in the reference (single GPU, P/gpt_oss_server.py:25). */
 #define NF4MOE_STATUS_EP_TIMEOUT 8
 int nf4moe_ep_dispatch_p2p(const void* x, const int32_t* ids, const int32_t* expert_offsets, const int32_t* sorted_pairs, int T, int k,
                            int E, int H, int world, int rank, int cap, void* const* peer_recv_rows, void* const* peer_recv_ids,
-                           void* const* peer_flags, int32_t* pair_slot, uint32_t* ctr, int32_t* status, void* stream);
+                           void* const* peer_flags, int32_t* pair_slot, uint32_t* ctr, int32_t* status, const void* wait_flags,
+                           uint32_t* wait_ctr, void* stream);
 int nf4moe_ep_return_p2p(const void* y_rows, const int32_t* recv_ids, int H, int world, int rank, int cap, void* const* peer_back_rows,
-                         void* const* peer_flags, uint32_t* ctr, void* stream);
+                         void* const* peer_flags, uint32_t* ctr, const void* wait_flags, uint32_t* wait_ctr, int32_t* status,
+                         void* stream);
 int nf4moe_ep_wait(const void* flags, int world, uint32_t* ctr, int32_t* status, void* stream);
 
 /* Number of kernels the last nf4moe_moe_forward / nf4moe_expert_rows on this thread launched (bench.py's gpu_launches). */
