@@ -57,7 +57,7 @@ def parse():
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-prefill", action="store_true", help="skip the extra 8192-token prefill measurement")
     p.add_argument("--prefill-tokens", type=int, default=8192)
-    p.add_argument("--cpu-tokens", type=int, default=16)
+    p.add_argument("--cpu-tokens", type=int, default=None, help="tokens of the CPU arm's layer sample (default: --tokens, the GPU arm's batch)")
     return p.parse_args()
 
 
@@ -156,7 +156,7 @@ def run_reference(args):
     rng = np.random.default_rng(SEED)
     st13, st2 = cpu_states(rng, E, 2 * I, H), cpu_states(rng, E, H, I)
     steps, warm = max(1, min(args.steps, 6)), max(0, min(args.warmup, 1))
-    T = args.cpu_tokens
+    T = args.cpu_tokens or args.tokens           # the same batch as the GPU arm
     times = cpu_layer_seconds(st13, st2, T, E, steps, warm)
     sec = sum(times) / len(times)
     val = T / (sec * args.layers)
@@ -837,7 +837,7 @@ def run_ours(args):
     if not args.no_cpu_baseline:
         st13 = [state_to_cpu(stack[0][0], e) for e in range(E)]
         st2 = [state_to_cpu(stack[0][1], e) for e in range(E)]
-        Tc = args.cpu_tokens
+        Tc = args.cpu_tokens or T                # the same batch as the timed GPU step
         times = cpu_layer_seconds(st13, st2, Tc, E, reps=2, warm=0)
         sec = min(times)
         line["cpu_baseline"] = {"value": Tc / (sec * L), "unit": "tokens/s", "cores": os.cpu_count(), "kind": "port",
