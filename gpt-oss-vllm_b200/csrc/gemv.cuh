@@ -146,6 +146,12 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a)
     uint32_t* virt = const_cast<uint32_t*>(s_virt);
     const int n_act = a.meta[0];
     int total = 0;
+    if (a.meta[3] <= 8 * NT) {
+      // no expert has more rows than one chunk holds (always so under AUTO, which sends at most 8 tokens here): the virtual experts ARE
+      // the active experts -- one parallel load instead of the dependent active_experts -> expert_offsets round trips below
+      for (int ai = lane; ai < n_act && ai < kMaxVirt; ai += 32) virt[ai] = (uint32_t)a.active_experts[ai];
+      total = n_act;
+    } else
     for (int a0 = 0; a0 < n_act; a0 += 32) {
       const int ai = a0 + lane;
       const int e = ai < n_act ? a.active_experts[ai] : 0;

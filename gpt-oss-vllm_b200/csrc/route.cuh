@@ -181,12 +181,81 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
   }
   __syncthreads();
   BUCKET_STAMP(3);
-  if (warp == 0) bucket_scan_and_lists(s_count, s_off, E, lane, expert_offsets, active_experts, meta, tile_list, tile_rows, true);
-  __syncthreads();
+  // Every warp scans the counts itself (one expert per lane and pass: 5 shuffles) and goes straight on to place its own experts'
+  // pairs -- no second block barrier, no shared offsets.  The lists the later kernels read are written on the side by three
+  // different warps (tile list + meta[2] by warp 0, active experts + meta[0] by warp 1, offsets + meta[1], meta[3] by warp 2), each
+  // running only its own short piece of code: one warp doing all of it was 3.8 us of cold, dependent instructions on the critical
+  // path of every layer (scripts/bucket_stamps.py).
+  (void)s_off;
+  int my_off[8];                       // offsets of this warp's experts e = warp + 32 j
+  {
+    int run_base = 0, act_base = 0, tile_base = 0, mx = 0;
+    const int n_pass = (E + 31) >> 5;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      my_off[j] = 0;
+      if (j < n_pass) {
+        const int e = j * 32 + lane;
+        const int c = e < E ? s_count[e] : 0;
+        int inc = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int n = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += n;
+        }
+        const int off = run_base + inc - c;
+        my_off[j] = __shfl_sync(0xffffffffu, off, warp);
+        if (warp == 0) {                 // token tiles: an expert's c rows split into near-equal tiles, multiples of 16 rows
+          int tsz = 0, nt = 0;
+          if (c > 0) {
+            const int ntl = (c + tile_rows - 1) / tile_rows;
+            tsz = (((c + ntl - 1) / ntl) + 15) & ~15;
+            nt = (c + tsz - 1) / tsz;
+          }
+          int inc_t = nt;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, inc_t, o);
+            if (lane >= o) inc_t += n;
+          }
+          if (tile_list != nullptr && c > 0) {
+            int t = tile_base + inc_t - nt;
+#pragma unroll 1
+            for (int r = 0; r < c; r += tsz, ++t) *reinterpret_cast<int4*>(tile_list + 4 * t) = make_int4(e, off + r, min(tsz, c - r), 0);
+          }
+          tile_base += __shfl_sync(0xffffffffu, inc_t, 31);
+        } else if (warp == 1) {          // active experts, ascending
+          int inc_a = c > 0 ? 1 : 0;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const int n = __shfl_up_sync(0xffffffffu, inc_a, o);
+            if (lane >= o) inc_a += n;
+          }
+          if (c > 0) active_experts[act_base + inc_a - 1] = e;
+          act_base += __shfl_sync(0xffffffffu, inc_a, 31);
+        } else if (warp == 2) {          // offsets and the largest count
+          if (e < E) expert_offsets[e] = off;
+          mx = max(mx, c);
+        }
+        run_base += __shfl_sync(0xffffffffu, inc, 31);
+      }
+    }
+    if (warp == 0) {
+      if (lane == 0) meta[2] = tile_base;
+    } else if (warp == 1) {
+#pragma unroll 1
+      for (int i = act_base + lane; i < E; i += 32) active_experts[i] = -1;
+      if (lane == 0) meta[0] = act_base;
+    } else if (warp == 2) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      if (lane == 0) { expert_offsets[E] = run_base; meta[1] = run_base; meta[3] = mx; }
+    }
+  }
   BUCKET_STAMP(4);
-  for (int e = warp; e < E; e += 32) {
+  for (int e = warp, j = 0; e < E; e += 32, ++j) {
     const uint32_t pat = 0x01010101u * (uint32_t)e;
-    int run = s_off[e];
+    int run = my_off[j];
     for (int i = lane * 4; i < n_pad128; i += 128) {
       const uint32_t z = __vcmpeq4(*reinterpret_cast<const uint32_t*>(s_ids + i) ^ pat, 0u);
       const int mine = __popc(z) >> 3;                      // matches among this lane's four pairs
@@ -198,8 +267,8 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
       }
       int pos = run + inc - mine;
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if ((z >> (8 * j)) & 1u) sorted_pairs[pos++] = i + j;
+      for (int jj = 0; jj < 4; ++jj)
+        if ((z >> (8 * jj)) & 1u) sorted_pairs[pos++] = i + jj;
       run += __shfl_sync(0xffffffffu, inc, 31);
     }
   }
