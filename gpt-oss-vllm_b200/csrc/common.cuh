@@ -140,6 +140,11 @@ __device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol
 // grid_dep_wait() -- it did, for the bucket metadata in permute_rows_kernel (round 2: LDG.E.CONSTANT ahead of ACQBULK in the
 // SASS, stale routing under back-to-back launches).  This form stays where it is written; tests/test_abi_host.py scans the
 // built library's SASS for global loads ahead of the wait.
+__device__ __forceinline__ uint4 ld_dep_u4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ int ld_dep_s32(const int32_t* p) {
   int v;
   asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

@@ -1,5 +1,6 @@
 // NF4 dequantise / quantise kernels (HBM-bound elementwise work; CUDA cores, 128-bit accesses).
 #pragma once
+#include <cuda_bf16.h>
 #include "common.cuh"
 
 namespace nf4moe {
@@ -127,6 +128,36 @@ __global__ void __launch_bounds__(256) quantize_nested_kernel(const float* __res
   if (tid == 0) {
     absmax2[blk] = m;
     if (j == 0) offset[e] = off;
+  }
+}
+
+// fp16 <-> bf16 (elementwise).  bf16 -> fp16 is EXACT for every finite value inside the fp16 range (bf16 carries 8 significand
+// bits, fp16 11) and saturates at +-65504 outside it; fp16 -> bf16 rounds to nearest even.  This is how bf16 callers are served:
+// the kernels of this library take fp16 operands (the reference serves --dtype float16, P/gpt_oss_server.py:41; its config also
+// lists bf16, P/bnb_moe_4bit.py:35-37), so a bf16 activation tensor is widened exactly, the layer runs as for fp16 (fp32
+// accumulation) and the result is rounded to bf16 once at the end.
+__global__ void __launch_bounds__(256) cast_f16_bf16_kernel(const uint16_t* __restrict__ src, uint16_t* __restrict__ dst, long long n,
+                                                            int to_bf16) {
+  grid_dep_launch();
+  grid_dep_wait();
+  auto one = [&](uint16_t v) -> uint16_t {
+    if (to_bf16) return __bfloat16_as_ushort(__float2bfloat16_rn(__half2float(__ushort_as_half(v))));
+    const float f0 = __bfloat162float(__ushort_as_bfloat16(v));
+    const float f = f0 != f0 ? f0 : fminf(fmaxf(f0, -65504.f), 65504.f);   // NaN stays NaN (fmaxf / fminf would drop it)
+    return __half_as_ushort(__float2half_rn(f));
+  };
+  const long long nv = n >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+    uint4 v = ld_dep_u4(reinterpret_cast<const uint4*>(src) + i);
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) w[j] = (uint32_t)one((uint16_t)(w[j] & 0xFFFFu)) | ((uint32_t)one((uint16_t)(w[j] >> 16)) << 16);
+    reinterpret_cast<uint4*>(dst)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  for (long long i = (nv << 3) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    uint16_t v;
+    asm volatile("ld.global.u16 %0, [%1];" : "=h"(v) : "l"(src + i) : "memory");
+    dst[i] = one(v);
   }
 }
 

@@ -249,6 +249,18 @@ int nf4moe_quantize(const void* w_f16, int E, int rows, int cols, uint8_t* packe
   return 0;
 }
 
+int nf4moe_cast_f16_bf16(const void* src, void* dst, long long n, int to_bf16, void* stream) {
+  if (!src || !dst || n < 0) return fail(NF4MOE_EINVAL, "cast_f16_bf16: bad arguments");
+  if (!aligned16(src) || !aligned16(dst)) return fail(NF4MOE_EALIGN, "cast_f16_bf16: src and dst must be 16-byte aligned");
+  if (n == 0) return 0;
+  DevInfo di;
+  if (int rc = device_info(&di)) return rc;
+  const int grid = (int)std::min<long long>((n / 8 + 255) / 256 + 1, (long long)di.sms * 8);
+  launch_pdl(cast_f16_bf16_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const uint16_t*)src, (uint16_t*)dst, n, to_bf16 ? 1 : 0);
+  CHECK_LAUNCH("cast_f16_bf16_kernel");
+  return 0;
+}
+
 int nf4moe_route_topk(const void* logits, int dtype, int T, int E, int k, int32_t* ids, float* weights, void* stream) {
   if (!logits || !ids || !weights || T < 0 || k <= 0 || k > 32 || k > E || dtype < 0 || dtype > 2)
     return fail(NF4MOE_EINVAL, "route_topk: bad arguments");

@@ -35,8 +35,8 @@ class B200NF4MoEConfig:
     def get_name(self) -> str:  # P/bnb_moe_4bit.py:33
         return "bnb_moe_4bit"
 
-    def get_supported_act_dtypes(self):  # :37 lists fp16/bf16; the kernels here are fp16 (the reference serves fp16)
-        return [torch.float16]
+    def get_supported_act_dtypes(self):  # :37 lists fp16/bf16; the kernels take fp16 operands, bf16 is widened exactly (ops.moe_forward)
+        return [torch.float16, torch.bfloat16]
 
     @classmethod
     def get_min_capability(cls) -> int:  # :54-56 says 70; this build is sm_100a only

@@ -208,6 +208,20 @@ def expert_w13_w2(xs: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights,
     return h, y
 
 
+def cast_f16_bf16(src: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """fp16 -> bf16 (round to nearest even) or bf16 -> fp16 (exact inside the fp16 range, saturating outside): nf4moe_cast_f16_bf16."""
+    _require_cuda(src, "src")
+    if src.dtype not in (torch.float16, torch.bfloat16) or not src.is_contiguous():
+        raise TypeError("cast_f16_bf16 takes a contiguous fp16 or bf16 tensor")
+    to_bf16 = src.dtype == torch.float16
+    if out is None:
+        out = torch.empty_like(src, dtype=torch.bfloat16 if to_bf16 else torch.float16)
+    with torch.cuda.device(src.device):
+        _lib.check(_lib.load_library().nf4moe_cast_f16_bf16(src.data_ptr(), out.data_ptr(), src.numel(), 1 if to_bf16 else 0,
+                                                            _stream_ptr(src.device)))
+    return out
+
+
 def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, top_k: int,
                 router_logits: torch.Tensor | None = None, topk_ids: torch.Tensor | None = None,
                 topk_weights: torch.Tensor | None = None, act: int = _lib.ACT_SWIGLU_OAI,
@@ -217,8 +231,19 @@ def moe_forward(x: torch.Tensor, w13: NF4ExpertWeights, w2: NF4ExpertWeights, to
     """The whole layer (nf4moe_moe_forward[_bias]): x fp16 [T,H] -> fp16 [T,H].  w13_bias fp16 [E, 2I] / w2_bias fp16 [E, H]
     (optional) are gpt-oss's expert biases."""
     _require_cuda(x, "hidden_states")
+    if x.dtype == torch.bfloat16:
+        # bf16 callers (P/bnb_moe_4bit.py:35-37 lists bf16 beside fp16): widened exactly to fp16, computed as for fp16 (fp32 accumulation),
+        # rounded to bf16 once at the end -- two elementwise kernels of this library around the same launch chain
+        if out is not None and out.dtype != torch.bfloat16:
+            raise TypeError("out must be bf16 for bf16 hidden_states")
+        res = moe_forward(cast_f16_bf16(x.contiguous()), w13, w2, top_k, router_logits=router_logits, topk_ids=topk_ids,
+                          topk_weights=topk_weights, act=act, regime=regime, nested=nested, workspace=workspace,
+                          return_routing=return_routing, w13_bias=w13_bias, w2_bias=w2_bias)
+        o16 = res[0] if return_routing else res
+        out = cast_f16_bf16(o16, out)
+        return (out, res[1], res[2]) if return_routing else out
     if x.dtype != torch.float16:
-        raise TypeError("hidden_states must be fp16 (the reference serves with --dtype float16)")
+        raise TypeError("hidden_states must be fp16 or bf16 (the reference serves with --dtype float16)")
     lib = _lib.load_library()
     T, H = x.shape
     E, I = w13.num_experts, w13.rows // 2

@@ -96,7 +96,7 @@ def build_config_class():
             return NAME
 
         def get_supported_act_dtypes(self):
-            return [torch.float16]
+            return [torch.float16, torch.bfloat16]
 
         @classmethod
         def get_min_capability(cls) -> int:

@@ -133,6 +133,12 @@ int nf4moe_quantize(const void* w_f16, int E, int rows, int cols, uint8_t* packe
 int nf4moe_route_topk(const void* logits, int logits_dtype, int T, int E, int k, int32_t* ids, float* weights,
                       void* stream);
 
+/* fp16 <-> bf16, elementwise, n elements (to_bf16 != 0: src fp16 -> dst bf16, round to nearest even; else src bf16 -> dst fp16, exact
+ * inside the fp16 range, saturating at +-65504).  How a bf16 caller is served (the reference's config lists bf16 beside fp16,
+ * P/bnb_moe_4bit.py:35-37): activations are widened exactly, the layer runs with fp16 operands and fp32 accumulation, the output
+ * is rounded to bf16 once. */
+int nf4moe_cast_f16_bf16(const void* src, void* dst, long long n, int to_bf16, void* stream);
+
 /* Stable counting sort of the T*k (token,slot) pairs by expert.  ids outside [0,E) are dropped (expert-parallel
  * callers mask non-local experts with -1).  Outputs (all int32):
  *   expert_offsets[E+1]  exclusive prefix of per-expert pair counts

@@ -317,6 +317,36 @@ def test_decode_kernel_64_row_token_tiles(pkg, cuda_device, T, E, H, I, k, skew)
     assert_moe_close(out_b.cpu().numpy(), orc.moe_forward_from_states(x, lg, st13, st2, k=k, b13=b13, b2=b2))
 
 
+def test_bf16_activations_are_widened_exactly(pkg, cuda_device):
+    """P/bnb_moe_4bit.py:35-37 lists bf16 beside fp16.  nf4moe_cast_f16_bf16: bf16 -> fp16 exact inside the fp16 range (saturating
+    outside, NaN kept), fp16 -> bf16 round-to-nearest-even -- against torch's own conversions bit for bit; a bf16 layer call equals
+    the fp16 call on the widened input, rounded once, and meets the MoE tolerance against the oracle on the widened input."""
+    g = torch.Generator(device=cuda_device).manual_seed(5)
+    v = (torch.randn(100003, generator=g, device=cuda_device) * 40).to(torch.bfloat16)
+    v[:6] = torch.tensor([0.0, -0.0, 70000.0, -1e30, float("inf"), 3e-6], device=cuda_device).to(torch.bfloat16)
+    h = pkg.ops.cast_f16_bf16(v)
+    ref = v.float().clamp(-65504.0, 65504.0).to(torch.float16)
+    assert h.dtype == torch.float16 and torch.equal(h.view(torch.int16), ref.view(torch.int16))
+    nan = pkg.ops.cast_f16_bf16(torch.full((8,), float("nan"), device=cuda_device, dtype=torch.bfloat16))
+    assert bool(torch.isnan(nan).all())
+    f = (torch.randn(4099, generator=g, device=cuda_device) * 100).half()
+    b = pkg.ops.cast_f16_bf16(f)
+    assert b.dtype == torch.bfloat16 and torch.equal(b.view(torch.int16), f.to(torch.bfloat16).view(torch.int16))
+    # the layer
+    T, E, H, I, k = 40, 8, 256, 192, 4
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 77, E, H, I)
+    rng = np.random.default_rng(17)
+    xb = torch.from_numpy(rng.standard_normal((T, H)).astype(np.float32)).to(cuda_device).to(torch.bfloat16)
+    lg = torch.from_numpy(rng.standard_normal((T, E)).astype(np.float16)).to(cuda_device)
+    out_b = pkg.ops.moe_forward(xb, w13, w2, k, router_logits=lg)
+    x16 = xb.to(torch.float16)                         # exact: |x| < 65504
+    out_h = pkg.ops.moe_forward(x16, w13, w2, k, router_logits=lg)
+    assert out_b.dtype == torch.bfloat16 and torch.equal(out_b.view(torch.int16), out_h.to(torch.bfloat16).view(torch.int16))
+    ref = orc.moe_forward_from_states(x16.cpu().numpy(), lg.cpu().numpy(), st13, st2, k=k)
+    got = out_b.float().cpu().numpy()
+    assert np.abs(got - ref.astype(np.float32)).max() <= 1e-2 + 2.0 ** -8 * np.abs(ref.astype(np.float32)).max()   # + one bf16 rounding
+
+
 def test_per_expert_code2_tables(pkg, cuda_device):
     """code2_stride = 256 (one double-quant table per expert): the decode kernel then stages the expert's table per item
     instead of using the per-lane copy in the decode table's holes; results must not change."""

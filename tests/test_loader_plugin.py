@@ -78,7 +78,7 @@ def test_vllm_plugin_registers_config():
     from vllm.model_executor.layers.quantization import get_quantization_config
     assert get_quantization_config(plug.NAME) is cls and plug.register() is cls
     cfg = cls.from_config({"top_k": 4})
-    assert cfg.get_name() == plug.NAME and cfg.get_min_capability() == 100 and cfg.get_supported_act_dtypes() == [torch.float16]
+    assert cfg.get_name() == plug.NAME and cfg.get_min_capability() == 100 and cfg.get_supported_act_dtypes() == [torch.float16, torch.bfloat16]
     assert cfg.operand_mode == "fast" and cls.from_config({"operand_mode": "exact"}).operand_mode == "exact"
     with pytest.raises(ValueError):
         cls.from_config({"operand_mode": "sloppy"})
