@@ -459,7 +459,7 @@ int nf4moe_gemm_w13_w2(const void* x_sorted, const nf4moe_qweight* w13, const vo
 // EXPECTS, not the capacity of its receive buffer); buffers and TMA maps are always sized by T.
 static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* w13, const nf4moe_qweight* w2, void* y, int T,
                        int E, int H, int I, int k, int act, int regime, const Workspace& ws, void* stream, int* launches,
-                       const void* w13_bias = nullptr, int policy_T = 0) {
+                       const void* w13_bias = nullptr, int policy_T = 0, bool prebucketed = false) {
   cudaStream_t st = (cudaStream_t)stream;
   if (policy_T <= 0 || policy_T > T) policy_T = T;
   if (regime == NF4MOE_REGIME_AUTO) {
@@ -478,8 +478,12 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
   const bool wide_ok = regime == NF4MOE_REGIME_GEMM_FAST && w13->absmax_f32 == nullptr && w2->absmax_f32 == nullptr &&
                        act == NF4MOE_ACT_SWIGLU_OAI;
   const int tile_rows = gemm ? gemm_tile_tokens(policy_T, k, E, wide_ok) : 0;
-  if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
-  *launches += g_launches; g_launches = 0;
+  if (prebucketed) {   // route_bucket_small_kernel already sorted the pairs (GEMV regime only: it writes no tile list)
+    if (gemm) return fail(NF4MOE_EINVAL, "run_experts: the fused router + bucket launch serves the GEMV regime only");
+  } else {
+    if (int rc = nf4moe_bucket(ids, T, k, E, ws.offsets, ws.sorted, ws.active, ws.meta, gemm ? ws.tiles : nullptr, tile_rows, stream)) return rc;
+    *launches += g_launches; g_launches = 0;
+  }
   // with an up-projection bias the w13 kernels store their raw products and bias_act_kernel applies bias + activation
   // (the decode tcgen05 kernel adds the bias inside its fused SwiGLU epilogue instead)
   const bool bias_fused = w13_bias && gemm && act == NF4MOE_ACT_SWIGLU_OAI && tile_rows <= kDecMaxTile;
@@ -560,15 +564,35 @@ int nf4moe_moe_forward_bias(const void* x, const void* router_logits, int logits
   int launches = 0;
   const int32_t* ids = topk_ids;
   const float* wts = topk_weights;
+  bool prebucketed = false;
   if (router_logits) {
     int32_t* ids_w = topk_ids_out ? topk_ids_out : ws.ids;
     float* wts_w = topk_weights_out ? topk_weights_out : ws.weights;
-    if (int rc = nf4moe_route_topk(router_logits, logits_dtype, T, E, k, ids_w, wts_w, stream)) return rc;
+    // batch-1..8 decode (always the GEMV regime under AUTO): router and bucketing in ONE single-CTA launch
+    const bool tiny = T <= 8 && T * k <= 32 && k <= 32 && E <= 255 && (regime == NF4MOE_REGIME_AUTO || regime == NF4MOE_REGIME_GEMV) &&
+                      logits_dtype >= 0 && logits_dtype <= 2 && experiment_env("NF4MOE_ROUTE_BUCKET", 1) != 0;
+    if (tiny) {
+      cudaStream_t st = (cudaStream_t)stream;
+      const int per_lane = (E + 31) / 32;
+#define NF4MOE_RB(P) launch_pdl(route_bucket_small_kernel<P>, dim3(1), dim3(256), 0, st, router_logits, logits_dtype, T, E, k, ids_w, wts_w, \
+                                ws.offsets, ws.sorted, ws.active, ws.meta)
+      switch (per_lane <= 2 ? per_lane : per_lane <= 4 ? 4 : 8) {
+        case 1: NF4MOE_RB(1); break;
+        case 2: NF4MOE_RB(2); break;
+        case 4: NF4MOE_RB(4); break;
+        default: NF4MOE_RB(8); break;
+      }
+#undef NF4MOE_RB
+      CHECK_LAUNCH("route_bucket_small_kernel");
+      prebucketed = true;
+    } else {
+      if (int rc = nf4moe_route_topk(router_logits, logits_dtype, T, E, k, ids_w, wts_w, stream)) return rc;
+    }
     launches += g_launches; g_launches = 0;
     ids = ids_w;
     wts = wts_w;
   }
-  if (int rc = run_experts(x, ids, w13, w2, ws.y, T, E, H, I, k, act, regime, ws, stream, &launches, w13_bias)) return rc;
+  if (int rc = run_experts(x, ids, w13, w2, ws.y, T, E, H, I, k, act, regime, ws, stream, &launches, w13_bias, 0, prebucketed)) return rc;
   if (int rc = combine_impl(ws.y, wts, ids, E, T, k, H, out, w2_bias, stream)) return rc;
   g_launches += launches;
   return 0;

@@ -347,6 +347,30 @@ def test_bf16_activations_are_widened_exactly(pkg, cuda_device):
     assert np.abs(got - ref.astype(np.float32)).max() <= 1e-2 + 2.0 ** -8 * np.abs(ref.astype(np.float32)).max()   # + one bf16 rounding
 
 
+@pytest.mark.parametrize("T,E,k", [(1, 32, 4), (2, 32, 4), (5, 32, 4), (8, 32, 4), (8, 128, 4), (3, 8, 2), (8, 255, 4), (6, 40, 5)])
+def test_router_and_bucket_in_one_launch_for_tiny_batches(pkg, cuda_device, T, E, k):
+    """Batch-1..8 decode: nf4moe_moe_forward routes and buckets in ONE single-CTA launch (route_bucket_small_kernel).  The routing it
+    returns is bit-identical to the stand-alone router (ties included), the layer output is bit-identical to the same layer driven
+    with that routing through the ordinary bucket kernel, and it meets the tolerance against the oracle."""
+    H, I = 128, 64
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 900 + E + T, E, H, I)
+    rng = np.random.default_rng(T * 1000 + E)
+    x = rng.standard_normal((T, H)).astype(np.float16)
+    lg = rng.standard_normal((T, E)).astype(np.float16)
+    lg[0, : min(E, 6)] = lg[0, 0]                       # ties: the lowest expert index wins
+    xd, lgd = torch.from_numpy(x).to(cuda_device), torch.from_numpy(lg).to(cuda_device)
+    out, ids, wts = pkg.ops.moe_forward(xd, w13, w2, k, router_logits=lgd, return_routing=True)
+    launches = pkg.ops.last_launch_count()
+    rid, rw = pkg.ops.route_topk(lgd, k)
+    assert torch.equal(ids, rid) and torch.equal(wts, rw)
+    oid, _ = orc.route_topk(lg, k)
+    assert np.array_equal(ids.cpu().numpy(), oid)
+    out2 = pkg.ops.moe_forward(xd, w13, w2, k, topk_ids=rid, topk_weights=rw)      # ordinary bucket kernel
+    assert torch.equal(out, out2)
+    assert launches == pkg.ops.last_launch_count(), "one launch for router + bucket = as many launches as the pre-routed call"
+    assert_moe_close(out.cpu().numpy(), orc.moe_forward_from_states(x, lg, st13, st2, k=k))
+
+
 def test_per_expert_code2_tables(pkg, cuda_device):
     """code2_stride = 256 (one double-quant table per expert): the decode kernel then stages the expert's table per item
     instead of using the per-lane copy in the decode table's holes; results must not change."""
