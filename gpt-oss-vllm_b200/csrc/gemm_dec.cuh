@@ -295,6 +295,16 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
       if (SIDES != 0) { pf(&map_h16); pf(&map_h32); pf(&map_h64); }
     }
   }
+  if (tid == kDecThreads - 1) {   // the barriers depend on nothing either (the idle control warp's lane: off everybody's path)
+    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
+    for (int i = 0; i < kDecMaxB; ++i) { mbar_init(bar(kDbDone + i), 1); mbar_init(bar(kDbBFull + i), 1); }
+    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecStageWarps);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(kDbDFull + i), 1); mbar_init(bar(kDbDEmpty + i), 4);
+      mbar_init(bar(kDbMFull + i), 1); mbar_init(bar(kDbMEmpty + i), kDecDqWarps);
+    }
+    fence_barrier_init();
+  }
   if (tid == 0) stamp(1);
   grid_dep_wait();
   if (tid == 0) stamp(2);
@@ -307,14 +317,6 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     if (bi >= 0) s_plan = a.plan[bi * 3 + (bmax == 16 ? 0 : bmax == 32 ? 1 : 2)];
     else dec_plan(base, lut, SIDES == 2 ? max(a.s[0].w.nkb, a.s[1].w.nkb) : a.s[kSide0].w.nkb, nested, !hole, bmax, &s_plan);
     if (s_plan.n_raw == 0 && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
-    for (int i = 0; i < kDecMaxRaw; ++i) { mbar_init(bar(kDbRFull + i), 1); mbar_init(bar(kDbREmpty + i), kDecStageWarps); }
-    for (int i = 0; i < kDecMaxB; ++i) { mbar_init(bar(kDbDone + i), 1); mbar_init(bar(kDbBFull + i), 1); }
-    for (int i = 0; i < kDecSlots; ++i) mbar_init(bar(kDbAFull + i), kDecStageWarps);
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(bar(kDbDFull + i), 1); mbar_init(bar(kDbDEmpty + i), 4);
-      mbar_init(bar(kDbMFull + i), 1); mbar_init(bar(kDbMEmpty + i), kDecDqWarps);
-    }
-    fence_barrier_init();
   }
   tc_fence_before();
   __syncthreads();
