@@ -20,7 +20,7 @@ LOGITS_DTYPE = {"float16": 0, "float32": 1, "bfloat16": 2}
 # every symbol include/nf4moe.h declares (tests check the library exports exactly these)
 EXPORTED = (
     "nf4moe_version", "nf4moe_auto_regime", "nf4moe_auto_regime_for", "nf4moe_cast_f16_bf16", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_dequant", "nf4moe_dequant_absmax",
-    "nf4moe_quantize", "nf4moe_route_topk", "nf4moe_bucket", "nf4moe_permute_rows", "nf4moe_combine",
+    "nf4moe_quantize", "nf4moe_quantize_static", "nf4moe_route_topk", "nf4moe_bucket", "nf4moe_permute_rows", "nf4moe_combine",
     "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_gemm_w13_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
     "nf4moe_last_launch_count", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
     "nf4moe_workspace_status_offset", "nf4moe_expert_rows_bias", "nf4moe_combine_indexed_bias",
@@ -66,6 +66,7 @@ def _declare(lib):
     lib.nf4moe_dequant.argtypes = [qp, i32, i32, vp, vp]
     lib.nf4moe_dequant_absmax.argtypes = [qp, i32, vp, vp]
     lib.nf4moe_quantize.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.nf4moe_quantize_static.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     lib.nf4moe_route_topk.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp]
     lib.nf4moe_bucket.argtypes = [vp, i32, i32, i32, vp, vp, vp, vp, vp, i32, vp]
     lib.nf4moe_permute_rows.argtypes = [vp, vp, vp, i32, i32, i32, vp, vp]

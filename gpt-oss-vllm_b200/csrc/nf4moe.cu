@@ -1,4 +1,5 @@
 // libnf4moe.so -- C ABI over the sm_100a kernels (single translation unit).  See include/nf4moe.h for the contract.
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -733,3 +734,51 @@ int nf4moe_ep_wait(const void* flags, int world, uint32_t* ctr, int32_t* status,
 }
 
 }  // extern "C"
+
+// ---- nf4moe_quantize_static: the quantiser for hosts that cannot allocate device memory --------------------------------------
+// The quantiser's two passes talk through scratch (the per-expert fp64 absmax sums and the fp32 absmax of every block).  Here that
+// scratch is a fixed array inside the library image instead of a caller buffer: each GPU that loads libnf4moe.so carries these
+// NF4MOE_STATIC_SCRATCH_BYTES of HBM until the process exits, whether or not this entry point is ever called.
+namespace {
+
+__device__ __align__(256) unsigned char g_quant_scratch[NF4MOE_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+std::atomic<void*> g_quant_scratch_ptr[kMaxDevices];   // per device: where g_quant_scratch lives in THAT device's memory
+
+// `g_quant_scratch` in host code is only the handle the runtime registered the array under, not somewhere a kernel can write: the
+// device address has to be asked for, separately on every device (each holds its own copy), with that device current.
+int quant_scratch_for_current_device(void** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+  if (dev < 0 || dev >= kMaxDevices) return fail(NF4MOE_EINVAL, "quantize_static: device ordinal %d is past %d", dev, kMaxDevices - 1);
+  void* p = g_quant_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    e = cudaGetSymbolAddress(&p, g_quant_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_quant_scratch)");
+    if (!p) return fail(NF4MOE_EINVAL, "quantize_static: the runtime returned no address for the scratch array");
+    g_quant_scratch_ptr[dev].store(p, std::memory_order_release);   // two threads racing here store the same address
+  }
+  *out = p;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int nf4moe_quantize_static(const void* w_f16, int E, int rows, int cols, uint8_t* packed, uint8_t* absmax_u8, float* absmax2,
+                                      const float* code2, float* offset, float* absmax_f32_out, void* stream) {
+  if (E <= 0 || rows <= 0 || cols <= 0 || cols % kBlock) return fail(NF4MOE_EINVAL, "quantize_static: bad arguments");
+  const unsigned long long nb = (unsigned long long)rows * (unsigned long long)(cols / kBlock);
+  const unsigned long long need = align_up((size_t)E * 8, 256) + (unsigned long long)E * nb * 4ull;   // nf4moe_quantize's layout
+  if (need > (unsigned long long)NF4MOE_STATIC_SCRATCH_BYTES)
+    return fail(NF4MOE_EINVAL,
+                "quantize_static: E=%d experts of %d x %d need %llu bytes of scratch, the built-in array holds %llu; quantise fewer "
+                "experts per call or use nf4moe_quantize with a scratch buffer of your own",
+                E, rows, cols, need, (unsigned long long)NF4MOE_STATIC_SCRATCH_BYTES);
+  void* scratch = nullptr;
+  if (int rc = quant_scratch_for_current_device(&scratch)) return rc;
+  // nf4moe_quantize zeroes the sums on `stream` before its first pass and overwrites every absmax word it later reads, so what the
+  // previous call left in the array is never seen
+  return nf4moe_quantize(w_f16, E, rows, cols, packed, absmax_u8, absmax2, code2, offset, absmax_f32_out, scratch, stream);
+}

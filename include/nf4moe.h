@@ -24,7 +24,8 @@
  *                             BitsAndBytesMoEMethod.apply (V/.../quantization/bitsandbytes.py:478-506)
  *
  * Conventions
- *   - every pointer is a DEVICE pointer owned by the caller; the library allocates nothing and keeps no device state;
+ *   - every pointer is a DEVICE pointer owned by the caller; the library allocates nothing and keeps no device state -- with one
+ *     stated exception: the fixed NF4MOE_STATIC_SCRATCH_BYTES array behind nf4moe_quantize_static (see its comment);
  *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), does no host<->device sync and is
  *     CUDA-graph capturable;
  *   - return value: 0 on success, a negative NF4MOE_E* code on a usage error, or a positive cudaError_t passed through;
@@ -125,6 +126,30 @@ int nf4moe_dequant_absmax(const nf4moe_qweight* w, int E, float* absmax_f32_out,
  * `code2` (256 sorted fp32) is an INPUT.  Two passes on `stream`; `scratch` needs E*(rows*cols/64)*4 + E*8 + 512 bytes. */
 int nf4moe_quantize(const void* w_f16, int E, int rows, int cols, uint8_t* packed, uint8_t* absmax_u8, float* absmax2,
                     const float* code2, float* offset, float* absmax_f32_out, void* scratch, void* stream);
+
+/* nf4moe_quantize for a host that must not, or cannot, allocate device memory.  It has no counterpart in the reference (which
+ * quantises through bitsandbytes and lets torch's allocator find the temporaries); it exists for two kinds of caller of THIS library:
+ *   - a weight loader running inside a serving process whose memory is already spoken for: once an engine such as vLLM has sized
+ *     its KV-cache pool to the configured share of HBM, a cudaMalloc (or a torch.empty that misses torch's cache) for the
+ *     quantiser's temporaries can fail with out-of-memory although the layer itself fits;
+ *   - a C / ctypes / cgo host that binds this ABI without an allocator of its own, or that may not call cudaMalloc / cudaFree at
+ *     that point because both can synchronise the whole device and stall the streams that are serving requests.
+ * Same arguments, arithmetic and results as nf4moe_quantize, minus `scratch`: the two passes share a 256-byte-aligned array of
+ * NF4MOE_STATIC_SCRATCH_BYTES that is part of the library image.  What that costs and implies:
+ *   - every GPU on which the process loads libnf4moe.so gives up that much memory until the process exits, used or not;
+ *   - limit: align256(E*8) + E*(rows*cols/64)*4 <= NF4MOE_STATIC_SCRATCH_BYTES, i.e. up to 4 gate/up matrices [5760, 2880] or 8 down
+ *     matrices [2880, 2880] of gpt-oss per call; anything larger returns NF4MOE_EINVAL with the two sizes in nf4moe_last_error()
+ *     and launches nothing -- quantise fewer experts per call (the results per expert do not depend on E);
+ *   - the call itself allocates and frees nothing (no cudaMalloc / cudaFree, no library routine that would);
+ *   - the first call on each device looks up where the array lives on THAT device (cudaGetSymbolAddress, with the caller's current
+ *     device; the answer is kept per device).  Make that first call while no stream capture is in progress;
+ *   - there is one array per device, shared by every caller and left holding the last call's temporaries.  The entry point clears
+ *     the part that has to start at zero on `stream` itself, so back-to-back calls on one stream are fine; two calls that can run
+ *     on the GPU at the same time (different streams, different host threads) overwrite each other's temporaries and both results
+ *     are garbage -- serialise them, or give the concurrent ones nf4moe_quantize and their own buffers. */
+#define NF4MOE_STATIC_SCRATCH_BYTES 4194304 /* 4 MiB */
+int nf4moe_quantize_static(const void* w_f16, int E, int rows, int cols, uint8_t* packed, uint8_t* absmax_u8, float* absmax2,
+                           const float* code2, float* offset, float* absmax_f32_out, void* stream);
 
 /* ---- routing --------------------------------------------------------------------------------------------------- */
 
