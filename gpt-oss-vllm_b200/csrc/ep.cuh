@@ -150,7 +150,9 @@ __device__ __forceinline__ void ep_publish_epoch(unsigned int* ctr, const EpPeer
         const unsigned long long want = s_wait_epoch;
         unsigned long long spins = 0;
         while (ld_acquire_sys_u64(wait_flags + threadIdx.x) < want) {
-          if (++spins > (1ull << 27)) { if (status) atomicOr(status, 8); break; }   // a peer died or never launched
+          // a peer died or never launched: its rows will never land, so nothing downstream may run on them -- leave the bit for
+          // post-mortems and kill the launch; the host's next synchronisation fails (as an NCCL abort would)
+          if (++spins > (1ull << 27)) { if (status) atomicOr(status, 8); __threadfence_system(); __trap(); }
           __nanosleep(64);
         }
       }
@@ -235,7 +237,8 @@ __global__ void __launch_bounds__(256) ep_return_kernel(const __half* __restrict
 }
 
 // One warp: advance this rank's wait epoch (ctr[0]) and spin until every peer's flag has reached it.  A peer that never
-// arrives (a crashed rank) raises NF4MOE_STATUS_EP_TIMEOUT after 2^27 polls (about half a minute) instead of hanging the GPU for ever.
+// arrives (a crashed rank) raises NF4MOE_STATUS_EP_TIMEOUT after 2^27 polls (about half a minute) and traps -- the stream's next
+// synchronisation reports a launch failure -- instead of hanging the GPU for ever or letting the layer run on stale rows.
 __global__ void __launch_bounds__(32) ep_wait_kernel(const unsigned long long* __restrict__ flags, int world, unsigned int* __restrict__ ctr,
                                                      int32_t* __restrict__ status) {
   grid_dep_launch();
@@ -252,7 +255,11 @@ __global__ void __launch_bounds__(32) ep_wait_kernel(const unsigned long long* _
       __nanosleep(64);
     }
   }
-  if (!ok) atomicOr(status, 8);
+  if (!ok) {
+    atomicOr(status, 8);
+    __threadfence_system();
+    __trap();
+  }
   __threadfence_system();
 }
 

@@ -625,8 +625,13 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
             if (seen < nrt0) {
               __nanosleep(100);
               // every CTA is resident and w13 items wait for nothing, so this ends within microseconds; if the grid was NOT
-              // fully resident (SMs held by something that itself waits for this stream) give up loudly rather than hang
-              if (++polls > (1u << 26)) { if (lane == 0 && a.status) atomicOr(a.status, 16); break; }
+              // fully resident (SMs held by something that itself waits for this stream) give up loudly rather than hang or
+              // multiply garbage: set the bit and trap, so the host's next synchronisation fails
+              if (++polls > (1u << 26)) {
+                if (lane == 0 && a.status) atomicOr(a.status, 16);
+                __threadfence();
+                __trap();
+              }
             }
           } while (seen < nrt0);
           asm volatile("fence.proxy.async;" ::: "memory");

@@ -112,7 +112,10 @@ size_t nf4moe_workspace_status_offset(int T, int E, int H, int I, int k);
 #define NF4MOE_STATUS_DEC_NOFIT 2    /* decode tcgen05 kernel: shared-memory plan did not fit */
 #define NF4MOE_STATUS_GEMM_NOFIT 4   /* prefill tcgen05 kernel: shared-memory plan did not fit */
 #define NF4MOE_STATUS_DEP_TIMEOUT 16 /* merged w13+w2 decode launch: a w2 tile waited > 2^26 polls for its w13 row tiles (the
-                                        grid was not fully resident); EP_TIMEOUT = 8 is defined with nf4moe_ep_wait below */
+                                        grid was not fully resident); EP_TIMEOUT = 8 is defined with nf4moe_ep_wait below.
+                                        The two TIMEOUT conditions are fatal: the kernel sets the bit and then TRAPS, so the
+                                        caller's next synchronisation returns a launch failure and the context is lost -- a layer
+                                        never continues on rows that did not arrive (what NCCL's abort does for a dead peer) */
 
 /* ---- NF4 (de)quantisation ------------------------------------------------------------------------------------ */
 
@@ -289,7 +292,8 @@ int nf4moe_combine_indexed_bias(const void* y, const float* weights, const int32
  *                            new epoch to flags[0][rank] of every peer.  Only rows that exist cross the link, so cap = T*k (which
  *                            can never overflow) costs nothing: the exchange is drop-free.
  *   nf4moe_ep_wait           spins (system-scope acquire) until all `world` entries of one flag row carry this rank's next epoch;
- *                            status |= NF4MOE_STATUS_EP_TIMEOUT if a peer never arrives.
+ *                            if a peer never arrives (2^27 polls, roughly half a minute): status |= NF4MOE_STATUS_EP_TIMEOUT and the
+ *                            kernel traps -- the next synchronisation fails; the same holds for the waits inside dispatch / return.
  *   nf4moe_ep_return_p2p     owner rank: stores y_rows[q*cap + j] (where recv_ids >= 0) into home rank q's back_rows[rank, j] and
  *                            publishes to flags[1][rank] of every peer; nf4moe_combine_indexed[_bias] then reads back_rows.
  * wait_flags / wait_ctr (both or neither; one process per GPU only): the dispatch / return kernel itself then waits, after publishing,
