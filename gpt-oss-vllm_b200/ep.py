@@ -69,6 +69,23 @@ class EPPlan:
         mean = -(-worst // self.world)
         return min(worst, max(16, int(factor * mean + 15) // 16 * 16))
 
+    # nf4moe_bucket sorts at most this many (row, expert) pairs per call (csrc/nf4moe.cu: the pair list must fit shared memory)
+    MAX_OWNER_SLOTS = 204800
+
+    def check_owner_slots(self, cap: int, hidden_size: int = 0) -> int:
+        """An owner runs its experts over ALL world * cap receive slots (most of them empty), so that product -- not the token
+        count -- is what the bucket kernel's pair limit and the owner's scratch (recv / back / y rows and the expert workspace,
+        O(world * cap * hidden_size)) scale with.  Raises when the slots exceed what nf4moe_bucket takes: 8 ranks at the
+        worst-case capacity stop at 6,400 tokens per rank, so prefill-sized chunks need a capacity_factor.  Returns the slots."""
+        slots = self.world * cap
+        if slots > self.MAX_OWNER_SLOTS:
+            gb = f" (and about {slots * hidden_size * 2 * 6 / 2**30:.1f} GiB of owner-side buffers)" if hidden_size else ""
+            raise ValueError(
+                f"expert parallel: {self.world} ranks x capacity {cap} = {slots} receive slots per owner exceed the "
+                f"{self.MAX_OWNER_SLOTS} pairs nf4moe_bucket sorts{gb}; pass capacity_factor (e.g. 2.0 = twice the mean load; an "
+                f"overflow is detected, never silent) or feed fewer tokens per call")
+        return slots
+
 
 _COALESCE_DISPATCH = True
 
@@ -255,6 +272,7 @@ class EPMoELayer:
             exchange = NcclExchange(plan, plan.capacity(max_tokens, top_k, capacity_factor), hidden_size, self.device, group)
         self.x = exchange
         self.cap = exchange.cap
+        plan.check_owner_slots(self.cap, hidden_size)
         # The owner's kernels are chosen for the rows it EXPECTS (every rank sends about T*k/W rows to each peer, so T*k arrive),
         # not for the W*cap slots of its receive buffer, which is mostly empty
         self.rows_hint = min(plan.world * self.cap, max_tokens * top_k)
@@ -392,15 +410,21 @@ class ReplicatedMoELayer:
 
 def make_exchange(plan: EPPlan, top_k: int, hidden_size: int, max_tokens: int, device, group=None, backend: str = "auto",
                   capacity_factor: float | None = None):
-    """The exchange a stack of EP layers shares.  backend: "p2p" (peer memory; capacity = worst case, drop-free), "nccl", or
-    "auto" = p2p when torch symmetric memory can be set up on every rank, else nccl.  Returns (exchange, note)."""
+    """The exchange a stack of EP layers shares.  backend: "p2p" (peer memory), "nccl", or "auto" = p2p when torch symmetric
+    memory can be set up on every rank, else nccl.  Returns (exchange, note).
+    capacity_factor applies to BOTH backends.  None = the worst case max_tokens * top_k rows per peer: drop-free, and over peer
+    memory free on the wire (only rows that exist cross the link) -- but every owner then buckets and runs world * max_tokens * top_k
+    slots and holds O(that * hidden_size) bytes of buffers, which is fine at decode sizes and not at prefill sizes (see
+    EPPlan.check_owner_slots).  A factor bounds both at factor * mean load; pairs past it are dropped AND flagged
+    (NF4MOE_STATUS_EP_OVERFLOW -> EPMoELayer.check_overflow raises)."""
     if backend not in ("auto", "p2p", "nccl"):
         raise ValueError("backend must be auto, p2p or nccl")
+    plan.check_owner_slots(plan.capacity(max_tokens, top_k, capacity_factor), hidden_size)
     note = ""
     if backend in ("auto", "p2p") and torch.device(device).type == "cuda":
         ok = 1
         try:
-            ex = PeerExchange.symmetric(plan, plan.capacity(max_tokens, top_k), hidden_size, device, group)
+            ex = PeerExchange.symmetric(plan, plan.capacity(max_tokens, top_k, capacity_factor), hidden_size, device, group)
         except Exception as exc:   # noqa: BLE001 -- any failure to set up peer memory selects the collective path, loudly
             ok, note = 0, f"peer memory unavailable ({type(exc).__name__}: {exc})"
             if backend == "p2p":
@@ -408,7 +432,8 @@ def make_exchange(plan: EPPlan, top_k: int, hidden_size: int, max_tokens: int, d
         flag = torch.tensor([ok], device=device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
         if int(flag.item()) == 1:
-            return ex, "peer memory (torch symmetric memory over NVLink)"
+            return ex, "peer memory (torch symmetric memory over NVLink)" + (
+                f"; capacity {ex.cap} rows per peer (factor {capacity_factor})" if capacity_factor is not None else "")
         note = note or "peer memory unavailable on another rank"
     return NcclExchange(plan, plan.capacity(max_tokens, top_k, capacity_factor), hidden_size, device, group), ("nccl all-to-all" + (f"; {note}" if note else ""))
 

@@ -129,3 +129,22 @@ def test_plan_partition_and_capacity():
         ep.EPPlan(0, 3, 32)
     with pytest.raises(RuntimeError):                     # no CPU fallback unless a device_ops object is injected
         ep.EPMoELayer(None, None, p, 4, 64, 8, "cpu")
+
+
+def test_owner_slot_limit_is_checked_before_any_kernel_runs():
+    """Every owner buckets world * capacity receive slots, and nf4moe_bucket takes 204,800 pairs: at the worst-case capacity
+    8 ranks stop at 6,400 tokens per rank (an 8,192-token prefill chunk used to fail inside the first forward with EINVAL).  The
+    plan refuses at construction and says what to do; a capacity factor brings the same chunk well inside the limit."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    p = ep.EPPlan(0, 8, 32)
+    assert p.check_owner_slots(p.capacity(6400, 4)) == 204800
+    with pytest.raises(ValueError, match="capacity_factor"):
+        p.check_owner_slots(p.capacity(8192, 4), 2880)
+    cap = p.capacity(8192, 4, factor=2.0)
+    assert cap == 8192 and p.check_owner_slots(cap, 2880) == 65536
+    with pytest.raises(ValueError, match="receive slots"):          # make_exchange checks before it touches any device
+        ep.make_exchange(p, 4, 2880, 8192, "cpu")
+    with pytest.raises(ValueError, match="receive slots"):          # ... and so does the layer, whoever built the exchange
+        class _Ex:
+            cap, kind = 8192 * 4, "p2p"
+        ep.EPMoELayer(None, None, p, 4, 2880, 8192, "cpu", device_ops=object(), exchange=_Ex())

@@ -225,3 +225,57 @@ def test_replicated_activation_mode_virtual_ranks(pkg, cuda_device, world, T, E)
         total += part.float()
     ref = orc.moe_forward_from_states(x.cpu().numpy(), lg.cpu().numpy(), st13, st2, k=k)
     assert_moe_close(total.half().cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("world,T", [(4, 48), (8, 64)])
+def test_peer_memory_exchange_honours_capacity_factor(pkg, cuda_device, world, T):
+    """Peer-memory exchange with a per-peer capacity BELOW the worst case (2 x the mean load), which is what bounds the owner's
+    world * capacity slots at prefill sizes.  Near-uniform routing: nothing is dropped and every rank matches the oracle.  Then one
+    rank routes nearly everything to rank 0: the dispatch kernel drops the excess and raises the overflow bit, which
+    check_overflow turns into an error -- never a silent wrong answer."""
+    ep = importlib.import_module("gpt-oss-vllm_b200.ep")
+    E, H, I, k = 32, 192, 128, 4
+    st13, st2, w13, w2 = make_layer(pkg, cuda_device, 700 + world + T, E, H, I)
+    rng = np.random.default_rng(23)
+    plans = [ep.EPPlan(r, world, E) for r in range(world)]
+    cap = plans[0].capacity(T, k, 2.0)
+    assert cap < T * k
+    exs = [ep.PeerExchange.local(pl, cap, H, cuda_device) for pl in plans]
+    for ex in exs:
+        ex.connect(exs)
+    layers = [ep.EPMoELayer(ep.shard_experts(w13, pl), ep.shard_experts(w2, pl), pl, k, H, T, cuda_device, exchange=exs[r])
+              for r, pl in enumerate(plans)]
+    assert all(l.cap == cap for l in layers)
+
+    def run(skew_rank):
+        xs, lgs = [], []
+        for r in range(world):
+            xs.append(torch.from_numpy(rng.standard_normal((T, H)).astype(np.float16)).to(cuda_device))
+            lg = rng.standard_normal((T, E)).astype(np.float16)
+            if r == skew_rank:
+                lg[:, :4] += 8          # all four slots of every token go to rank 0's experts: T*k pairs for one peer
+            lgs.append(torch.from_numpy(lg).to(cuda_device))
+        for r in range(world):
+            layers[r].prepare(xs[r], router_logits=lgs[r])
+        for l in layers:
+            l.dispatch()
+            l.compute()
+        for l in layers:
+            l.x.ret()
+        outs = []
+        for r in range(world):
+            layers[r].x.wait_return()
+            outs.append(layers[r].finish())
+        return xs, lgs, outs
+
+    xs, lgs, outs = run(skew_rank=-1)
+    for r in range(world):
+        layers[r].check_overflow()
+        ref = orc.moe_forward_from_states(xs[r].cpu().numpy(), lgs[r].cpu().numpy(), st13, st2, k=k)
+        assert_moe_close(outs[r].cpu().numpy(), ref)
+    run(skew_rank=1)
+    with pytest.raises(RuntimeError, match="overflowed"):
+        layers[1].check_overflow()
+    for r in range(world):
+        if r != 1:
+            layers[r].check_overflow()
