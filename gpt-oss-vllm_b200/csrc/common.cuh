@@ -138,8 +138,12 @@ __device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol
 // A load of something the PREVIOUS kernel wrote, for kernels launched with launch_pdl().  Through a `const T* __restrict__`
 // parameter (or __ldg) the compiler treats the location as invariant for the whole kernel and may hoist the load ABOVE
 // grid_dep_wait() -- it did, for the bucket metadata in permute_rows_kernel (round 2: LDG.E.CONSTANT ahead of ACQBULK in the
-// SASS, stale routing under back-to-back launches).  This form stays where it is written; tests/test_abi_host.py scans the
-// built library's SASS for global loads ahead of the wait.
+// SASS, stale routing under back-to-back launches).  This form stays where it is written.
+// RULE for every kernel in this library: a pointer to anything an earlier kernel of the stream may have written -- activations,
+// logits, ids, offsets, sorted pairs, meta, tile lists, h, y -- is a plain `const T*` (no __restrict__) and is read with ordinary
+// loads (no __ldg), which the "memory" clobber of grid_dep_wait() keeps behind the wait; `const T* __restrict__` / __ldg are for
+// weights, absmax, code tables and biases only (written before any launch).  tests/test_abi_host.py scans the built library's
+// SASS for global loads ahead of the wait as a second line of defence.
 __device__ __forceinline__ uint4 ld_dep_u4(const uint4* p) {
   uint4 v;
   asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");

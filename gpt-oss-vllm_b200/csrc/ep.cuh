@@ -13,9 +13,9 @@ namespace nf4moe {
 //   send_rows[p * cap + j, :] = x[pair / k, :]      send_ids[p * cap + j] = local expert id (or -1 for an unused slot)
 //   pair_slot[pair]           = p * cap + j          (the row the combine reads after the return all-to-all)
 // Pairs past the capacity are dropped and flagged in status[0] (cannot happen with cap = T * k, the default).
-__global__ void __launch_bounds__(256) ep_pack_kernel(const __half* __restrict__ x, const int32_t* __restrict__ ids,
-                                                      const int32_t* __restrict__ expert_offsets,
-                                                      const int32_t* __restrict__ sorted_pairs, int k, int H, int world,
+__global__ void __launch_bounds__(256) ep_pack_kernel(const __half* x, const int32_t* ids,
+                                                      const int32_t* expert_offsets,
+                                                      const int32_t* sorted_pairs, int k, int H, int world,
                                                       int e_local, int cap, __half* __restrict__ send_rows,
                                                       int32_t* __restrict__ send_ids, int32_t* __restrict__ pair_slot,
                                                       int32_t* __restrict__ status) {
@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) ep_pack_kernel(const __half* __restrict__
       const int pair = sorted_pairs[start + j];
       const uint4* src = reinterpret_cast<const uint4*>(x + (long long)(pair / k) * H);
       uint4* dst = reinterpret_cast<uint4*>(send_rows + (long long)slot * H);
-      for (int i = lane; i < vec; i += 32) dst[i] = __ldg(src + i);
+      for (int i = lane; i < vec; i += 32) dst[i] = src[i];
       if (lane == 0) {
         send_ids[slot] = ids[pair] - p * e_local;
         pair_slot[pair] = slot;
@@ -46,8 +46,8 @@ __global__ void __launch_bounds__(256) ep_pack_kernel(const __half* __restrict__
 // arithmetic and order as combine_kernel, reading the rows where the return all-to-all left them.  pair_slot < 0: pair dropped.
 // bias (optional): the FULL down-projection bias table fp16 [E, H] (replicated on every rank: 184 KB for gpt-oss-20b), indexed by
 // the home rank's GLOBAL expert ids -- added at home, in fp32, so the expert-parallel sum equals the single-GPU one bit for bit.
-__global__ void __launch_bounds__(256) combine_indexed_kernel(const __half* __restrict__ y, const float* __restrict__ w,
-                                                              const int32_t* __restrict__ pair_slot, const int32_t* __restrict__ ids,
+__global__ void __launch_bounds__(256) combine_indexed_kernel(const __half* y, const float* w,
+                                                              const int32_t* pair_slot, const int32_t* ids,
                                                               const __half* __restrict__ bias, int E, int T, int k, int H,
                                                               __half* __restrict__ out) {
   const int vec = H / 8;
@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(256) combine_indexed_kernel(const __half* __re
       const int row = pair_slot[(long long)t * k + s];
       if (row < 0) continue;
       const float ws = w[(long long)t * k + s];
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(y + (long long)row * H) + c);
+      const uint4 v = reinterpret_cast<const uint4*>(y + (long long)row * H)[c];
       const __half2* h = reinterpret_cast<const __half2*>(&v);
       uint4 bv = make_uint4(0u, 0u, 0u, 0u);
       if (bias) {
@@ -162,9 +162,9 @@ __device__ __forceinline__ void ep_publish_epoch(unsigned int* ctr, const EpPeer
 }
 
 // Dispatch: slot (p, j) of this rank's pair list (sorted by global expert id, so grouped by owner) -> owner p's chunk `rank`.
-__global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* __restrict__ x, const int32_t* __restrict__ ids,
-                                                          const int32_t* __restrict__ expert_offsets,
-                                                          const int32_t* __restrict__ sorted_pairs, int k, int H, int world, int rank,
+__global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* x, const int32_t* ids,
+                                                          const int32_t* expert_offsets,
+                                                          const int32_t* sorted_pairs, int k, int H, int world, int rank,
                                                           int e_local, int cap, const EpPeers peers, int32_t* __restrict__ pair_slot,
                                                           unsigned int* __restrict__ ctr, int32_t* __restrict__ status, int n_pairs,
                                                           const unsigned long long* wait_flags, unsigned int* wait_ctr) {
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* __restri
       for (int i0 = 0; i0 < vec; i0 += 128) {     // 4 chunks per lane in flight
         uint4 v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) v[u] = __ldg(src + i); }
+        for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) v[u] = src[i]; }
 #pragma unroll
         for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) dst[i] = v[u]; }
       }
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(256) ep_dispatch_kernel(const __half* __restri
 }
 
 // Return: row (q, j) of this rank's expert outputs (valid where recv_ids >= 0) -> home rank q's back_rows chunk `rank`.
-__global__ void __launch_bounds__(256) ep_return_kernel(const __half* __restrict__ y_rows, const int32_t* __restrict__ recv_ids, int H,
+__global__ void __launch_bounds__(256) ep_return_kernel(const __half* y_rows, const int32_t* recv_ids, int H,
                                                         int world, int rank, int cap, const EpPeers peers,
                                                         unsigned int* __restrict__ ctr, const unsigned long long* wait_flags,
                                                         unsigned int* wait_ctr, int32_t* status) {
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(256) ep_return_kernel(const __half* __restrict
     for (int i0 = 0; i0 < vec; i0 += 128) {
       uint4 v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) v[u] = __ldg(src + i); }
+      for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) v[u] = src[i]; }
 #pragma unroll
       for (int u = 0; u < 4; ++u) { const int i = i0 + u * 32 + lane; if (i < vec) dst[i] = v[u]; }
     }

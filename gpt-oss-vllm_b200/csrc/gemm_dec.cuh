@@ -316,6 +316,9 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
     const int bi = base == a.plan_base[0] ? 0 : base == a.plan_base[1] ? 1 : -1;
     if (bi >= 0) s_plan = a.plan[bi * 3 + (bmax == 16 ? 0 : bmax == 32 ? 1 : 2)];
     else dec_plan(base, lut, SIDES == 2 ? max(a.s[0].w.nkb, a.s[1].w.nkb) : a.s[kSide0].w.nkb, nested, !hole, bmax, &s_plan);
+    // the tile list was built (nf4moe_bucket records it in meta[5]) for larger token tiles than this launch was planned for: refuse
+    // the whole launch -- an MMA N clamped to max_tile would silently drop the tiles' remaining rows
+    if (a.meta[5] > a.max_tile) s_plan.n_raw = 0;
     if (s_plan.n_raw == 0 && a.meta[2] > 0 && a.status) atomicOr(a.status, 2);
   }
   tc_fence_before();
@@ -537,7 +540,7 @@ __global__ void __launch_bounds__(kDecThreads, 1) dec_kernel(const DecArgs a, co
 #pragma unroll
         for (int i = 0; i < 32; ++i)
           if (row_ok && c0 + i < n_tok)
-            y[(long long)__ldg(a.sorted_pairs + row0 + c0 + i) * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
+            y[(long long)a.sorted_pairs[row0 + c0 + i] * w_rows + n] = __float2half_rn(__uint_as_float(v[i]));
       }
       }   // chunks
       if (SIDES == 2 && up_side) {

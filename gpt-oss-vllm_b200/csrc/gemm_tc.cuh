@@ -740,7 +740,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_kernel(const GemmArgs a,
 #pragma unroll
           for (int i = 0; i < 32; ++i)
             if (row_ok && c0 + i < n_tok)
-              y[(long long)__ldg(a.sorted_pairs + row0 + c0 + i) * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
+              y[(long long)a.sorted_pairs[row0 + c0 + i] * a.w.rows + n] = __float2half_rn(__uint_as_float(v[i]));
         }
       }
       tc_fence_before();

@@ -274,8 +274,8 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a)
         uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
         if (valid && j < nkb_w) {
           const uint4* p = reinterpret_cast<const uint4*>(a.x + src_row * (nkb * kBlock) + (kb0 + j) * kBlock + 16 * t);
-          v0 = __ldg(p);
-          v1 = __ldg(p + 1);
+          v0 = p[0];
+          v1 = p[1];
         }
         breg[nt][j][0] = v0.x; breg[nt][j][1] = v0.y; breg[nt][j][2] = v0.z; breg[nt][j][3] = v0.w;
         breg[nt][j][4] = v1.x; breg[nt][j][5] = v1.y; breg[nt][j][6] = v1.z; breg[nt][j][7] = v1.w;
@@ -406,7 +406,7 @@ __global__ void __launch_bounds__(kGemvThreads, 1) gemv_kernel(const GemvArgs a)
 }
 
 // reference-variant activation on a raw [n, 2I] buffer: silu(h[:, :I]) * h[:, I:]  (P/unsloth_to_vllm_converter.py:312-315)
-__global__ void __launch_bounds__(256) chunk_silu_kernel(const __half* __restrict__ raw, const int32_t* __restrict__ meta,
+__global__ void __launch_bounds__(256) chunk_silu_kernel(const __half* raw, const int32_t* meta,
                                                          int I, __half* __restrict__ h) {
   const long long total = (long long)ld_dep_s32(meta + 1) * I;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -419,9 +419,9 @@ __global__ void __launch_bounds__(256) chunk_silu_kernel(const __half* __restric
 // Biased up-projection: raw [rows, 2I] (fp16 products of the w13 kernel) + w13_bias[e] -> activation -> h [rows, I].  The row's
 // expert is ids[sorted_pairs[row]].  Replaces the bias add of gpt-oss's expert MLP (V/model_executor/models/gpt_oss.py:199),
 // which neither the reference nor vLLM's bnb method has.  act: interleaved clamped SwiGLU or chunk + SiLU.
-__global__ void __launch_bounds__(256) bias_act_kernel(const __half* __restrict__ raw, const __half* __restrict__ bias,
-                                                       const int32_t* __restrict__ ids, const int32_t* __restrict__ sorted_pairs,
-                                                       const int32_t* __restrict__ meta, int I, int act, __half* __restrict__ h) {
+__global__ void __launch_bounds__(256) bias_act_kernel(const __half* raw, const __half* __restrict__ bias,
+                                                       const int32_t* ids, const int32_t* sorted_pairs,
+                                                       const int32_t* meta, int I, int act, __half* __restrict__ h) {
   grid_dep_launch();
   grid_dep_wait();
   const long long total = (long long)ld_dep_s32(meta + 1) * I;

@@ -13,7 +13,7 @@ namespace nf4moe {
 // ---------------------------------------------------------------------------------------------------------------
 // One warp routes token t: lane j < k returns the j-th selected expert and its weight.
 template <int kPerLane>
-__device__ __forceinline__ void route_one_token(const void* __restrict__ logits, int dtype, int t, int E, int k, int lane, int& sel_i,
+__device__ __forceinline__ void route_one_token(const void* logits, int dtype, int t, int E, int k, int lane, int& sel_i,
                                                 float& weight) {
   float v[kPerLane];
 #pragma unroll
@@ -59,7 +59,7 @@ __device__ __forceinline__ void route_one_token(const void* __restrict__ logits,
 }
 
 template <int kPerLane>
-__global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict__ logits, int dtype, int T, int E, int k,
+__global__ void __launch_bounds__(256) route_topk_kernel(const void* logits, int dtype, int T, int E, int k,
                                                          int32_t* __restrict__ ids, float* __restrict__ weights) {
   grid_dep_launch();
   grid_dep_wait();   // launched with launch_pdl(): the logits (and a previous layer's readers of ids/weights) are done past here
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(256) route_topk_kernel(const void* __restrict_
 // inside its expert = the matching lanes below it: ascending pair index, as in bucket_kernel) and scans the per-expert counts.  One
 // dependent launch instead of two (~3.5 us of a 31 us layer at one token).  No token-tile list: this serves the GEMV regime only.
 template <int kPerLane>
-__global__ void __launch_bounds__(256) route_bucket_small_kernel(const void* __restrict__ logits, int dtype, int T, int E, int k,
+__global__ void __launch_bounds__(256) route_bucket_small_kernel(const void* logits, int dtype, int T, int E, int k,
                                                                  int32_t* __restrict__ ids, float* __restrict__ weights,
                                                                  int32_t* __restrict__ expert_offsets, int32_t* __restrict__ sorted_pairs,
                                                                  int32_t* __restrict__ active_experts, int32_t* __restrict__ meta) {
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(256) route_bucket_small_kernel(const void* __r
   if (valid) sorted_pairs[s_off[id] + rank] = lane;
 #pragma unroll 1
   for (int i = act_base + lane; i < E; i += 32) active_experts[i] = -1;
-  if (lane == 0) { expert_offsets[E] = run_base; meta[0] = act_base; meta[1] = run_base; meta[2] = 0; meta[3] = mx; }
+  if (lane == 0) { expert_offsets[E] = run_base; meta[0] = act_base; meta[1] = run_base; meta[2] = 0; meta[3] = mx; meta[5] = 0; }
 }
 
 // Warp 0 of the bucket kernels: exclusive scan of the per-expert counts (E <= 256) into s_off, and -- in the same pass -- the
@@ -199,7 +199,7 @@ __device__ __forceinline__ void bucket_scan_and_lists(const int* s_count, int* s
   if (lane == 0) expert_offsets[E] = run_base;
 #pragma unroll 1
   for (int i = act_base + lane; i < E; i += 32) active_experts[i] = -1;   // (unrolled 16x this was a fifth of the function's code)
-  if (lane == 0) { meta[0] = act_base; meta[1] = run_base; meta[2] = tile_base; meta[3] = mx; }
+  if (lane == 0) { meta[0] = act_base; meta[1] = run_base; meta[2] = tile_base; meta[3] = mx; meta[5] = tile_list ? tile_rows : 0; }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -216,7 +216,7 @@ __device__ long long g_bucket_stamps[8];
 #define BUCKET_STAMP(i) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* __restrict__ ids, int n_pairs, int E,
+__global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* ids, int n_pairs, int E,
                                                                 int32_t* __restrict__ expert_offsets,
                                                                 int32_t* __restrict__ sorted_pairs,
                                                                 int32_t* __restrict__ active_experts,
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
       }
     }
     if (warp == 0) {
-      if (lane == 0) meta[2] = tile_base;
+      if (lane == 0) { meta[2] = tile_base; meta[5] = tile_list ? tile_rows : 0; }   // [5]: no tile has more rows than this
     } else if (warp == 1) {
 #pragma unroll 1
       for (int i = act_base + lane; i < E; i += 32) active_experts[i] = -1;
@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_kernel(const int32_t* _
 // counts of all CTAs are exchanged through distributed shared memory, so a pair's position is
 // offset[e] + (matches in lower chunks) + (rank inside its chunk): the order inside an expert stays ascending pair index.
 constexpr int kBucketCluster = 8;
-__global__ void __launch_bounds__(kBucketThreads) bucket_cluster_kernel(const int32_t* __restrict__ ids, int n_pairs, int E,
+__global__ void __launch_bounds__(kBucketThreads) bucket_cluster_kernel(const int32_t* ids, int n_pairs, int E,
                                                                         int32_t* __restrict__ expert_offsets,
                                                                         int32_t* __restrict__ sorted_pairs,
                                                                         int32_t* __restrict__ active_experts,
@@ -431,9 +431,9 @@ __global__ void __launch_bounds__(kBucketThreads) bucket_cluster_kernel(const in
 // x_sorted[s,:] = x[sorted_pairs[s]/k,:]; one CTA of 128 threads per row pass (a 2880-wide row = 360 16-byte chunks = three per
 // thread, all in flight at once: round 1 walked a row with one warp, twelve dependent round trips, 5.8 us for 256 rows).
 // Rows past meta[1] are zeroed so the grouped GEMM's last tile reads defined data.
-__global__ void __launch_bounds__(128) permute_rows_kernel(const __half* __restrict__ x,
-                                                           const int32_t* __restrict__ sorted_pairs,
-                                                           const int32_t* __restrict__ meta, int n_rows, int k, int H,
+__global__ void __launch_bounds__(128) permute_rows_kernel(const __half* x,
+                                                           const int32_t* sorted_pairs,
+                                                           const int32_t* meta, int n_rows, int k, int H,
                                                            __half* __restrict__ xs) {
   grid_dep_launch();
   grid_dep_wait();
@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(128) permute_rows_kernel(const __half* __restr
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int i = i0 + u * 128 + (int)threadIdx.x;
-          if (i < vec) v[u] = __ldg(src + i);
+          if (i < vec) v[u] = src[i];
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -467,8 +467,8 @@ __global__ void __launch_bounds__(128) permute_rows_kernel(const __half* __restr
 
 // (5) out[t,:] = fp16( sum_slot w[t,slot] * y[t*k+slot,:] ), fp32, slot ascending
 // (P/unsloth_to_vllm_converter.py:321-323).  One thread = 8 columns.
-__global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__ y, const float* __restrict__ w,
-                                                      const int32_t* __restrict__ ids, int E, int T, int k, int H,
+__global__ void __launch_bounds__(256) combine_kernel(const __half* y, const float* w,
+                                                      const int32_t* ids, int E, int T, int k, int H,
                                                       __half* __restrict__ out, const __half* __restrict__ bias) {
   // bias (optional, needs ids): fp16 [E, H], the down-projection bias of the slot's expert, added to y in fp32 before weighting
   // (gpt-oss `w2_bias`, V/model_executor/models/gpt_oss.py:199)
@@ -501,7 +501,7 @@ __global__ void __launch_bounds__(256) combine_kernel(const __half* __restrict__
         if (!ok) e[u] = -1;
         v[u] = bv[u] = make_uint4(0u, 0u, 0u, 0u);
         if (ok) {
-          v[u] = __ldg(reinterpret_cast<const uint4*>(y + ((long long)t * k + s0 + u) * H) + c);
+          v[u] = reinterpret_cast<const uint4*>(y + ((long long)t * k + s0 + u) * H)[c];
           if (bias) bv[u] = __ldg(reinterpret_cast<const uint4*>(bias + (long long)e[u] * H) + c);
         }
       }

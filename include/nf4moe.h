@@ -44,7 +44,9 @@
 extern "C" {
 #endif
 
-#define NF4MOE_VERSION 100 /* 0.1.0 */
+#define NF4MOE_VERSION 101 /* 0.1.1.  ABI notes: since 101 `meta` (nf4moe_bucket and every entry point that takes it) is 16 int32, not 4 --
+                              [4] is the status word kernels OR into, [5] the token-tile size of the list; a caller that allocated 4
+                              words for version 100's first drafts must allocate 16.  nf4moe_quantize_static is new in 101. */
 
 #define NF4MOE_OK 0
 #define NF4MOE_EINVAL (-1)      /* bad shape / null pointer / unsupported size */
@@ -174,7 +176,8 @@ int nf4moe_cast_f16_bf16(const void* src, void* dst, long long n, int to_bf16, v
  *   active_experts[E]    experts with >=1 pair, ascending;  meta[0] = how many, meta[1] = total kept pairs,
  *                        meta[2] = number of token tiles, meta[3] = largest per-expert count; meta has 16 entries:
  *                        meta[4] is the status word the nf4moe_gemm_* kernels OR NF4MOE_STATUS_* bits into (never written
- *                        here: zero it once), the rest is reserved
+ *                        here: zero it once), meta[5] = the tile_rows this list was built with (0 without a tile list; no
+ *                        tile has more rows), the rest is reserved
  *   tile_list[4*(T*k/16+E+2)]  (expert, first sorted row, rows, 0) per token tile of the grouped GEMM: an expert with c
  *                        rows gets ceil(c/tile_rows) near-equal tiles, each a multiple of 16 rows except the last.
  *                        tile_rows: multiple of 16 in 16..256, or 0 = what nf4moe_gemm_* expect for this (T, k, E).
@@ -221,7 +224,8 @@ int nf4moe_gemm_w2(const void* h_sorted, const nf4moe_qweight* w2, const int32_t
  * (P/unsloth_to_vllm_converter.py:309-318); nf4moe_moe_forward / nf4moe_expert_rows use it whenever it applies.
  * `tile_list` is written to: the kernel counts the finished w13 row tiles of token tile t in tile_list[4 t + 3], which
  * nf4moe_bucket zeroes -- the list must come fresh from nf4moe_bucket for EVERY call.  Status bits as for the other tcgen05
- * entry points (meta[4]); NF4MOE_STATUS_DEP_TIMEOUT if the grid was not fully resident. */
+ * entry points (meta[4]); NF4MOE_STATUS_DEP_TIMEOUT if the grid was not fully resident.  A tile list built for larger tiles (meta[5] >
+ * 32, e.g. nf4moe_bucket(tile_rows = 0) at prefill sizes) is refused as a whole: NF4MOE_STATUS_DEC_NOFIT is raised, h and y stay untouched. */
 int nf4moe_gemm_w13_w2(const void* x_sorted, const nf4moe_qweight* w13, const void* w13_bias, void* h_sorted,
                        const nf4moe_qweight* w2, void* y, const int32_t* sorted_pairs, const int32_t* meta, int32_t* tile_list,
                        int T, int k, int E, int act, int mode, void* stream);

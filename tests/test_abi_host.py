@@ -20,8 +20,8 @@ def test_library_exports_header_symbols(pkg):
     assert declared == set(pkg._lib.EXPORTED)
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.nf4moe_version() == 100
-    assert int(re.search(r"#define NF4MOE_VERSION (\d+)", header).group(1)) == 100
+    assert lib.nf4moe_version() == 101
+    assert int(re.search(r"#define NF4MOE_VERSION (\d+)", header).group(1)) == 101
 
 
 def test_qweight_struct_layout_matches_header(pkg):
@@ -100,7 +100,10 @@ def test_no_global_load_ahead_of_the_grid_dependency_wait(pkg):
     import subprocess
     cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
     if not os.path.exists(cuobjdump):
-        pytest.skip("cuobjdump not available")
+        # the source-level rule (common.cuh: no __restrict__ / __ldg on anything an earlier kernel writes) is the first line of
+        # defence; this scan is the second, and it must not vanish quietly where the kernels actually run
+        assert not torch.cuda.is_available(), "cuobjdump is missing on a GPU box: the PDL load-order scan cannot run"
+        pytest.skip("cuobjdump not available (no GPU here either)")
     lib = os.path.join(os.path.dirname(pkg.__file__), "libnf4moe.so")
     sass = subprocess.run([cuobjdump, "-sass", lib], capture_output=True, text=True, check=True).stdout
     checked = 0
@@ -117,6 +120,25 @@ def test_no_global_load_ahead_of_the_grid_dependency_wait(pkg):
         allowed = 13 if re.search(r"dec_kernelILi\dELb1E", name) else 0
         assert len(early) <= allowed, f"{name}: loads ahead of the dependency wait: {early}"
     assert checked >= 10, "expected the PDL kernels (route, bucket, permute, GEMV, tcgen05, combine) in the library"
+
+
+def test_no_restrict_or_ldg_on_buffers_an_earlier_kernel_writes():
+    """Source-level form of the same rule: in the kernels' parameter lists, `const ... __restrict__` may only name weights, absmax,
+    code tables and biases, and __ldg only reads those; everything a preceding kernel may have produced is a plain pointer."""
+    csrc = os.path.join(ROOT, "gpt-oss-vllm_b200", "csrc")
+    produced = r"\b(x|xs|y|y_rows|h|raw|logits|ids|recv_ids|w|weights|expert_offsets|sorted_pairs|active_experts|meta|tile_list|pair_slot|src)\b"
+    for f in sorted(os.listdir(csrc)):
+        text = open(os.path.join(csrc, f)).read()
+        for m in re.finditer(r"const\s+[\w:]+\s*\*\s*__restrict__\s+(\w+)", text):
+            name = m.group(1)
+            if f == "dequant.cuh" and name in ("w", "src"):     # the quantiser / cast kernels: `w` is the fp16 weight input of plain
+                line = text[:m.start()].count("\n") + 1         # (non-PDL) launches; the cast kernel reads src through ld_dep_u4
+                assert "quantize_blocks_kernel" in text.splitlines()[line - 1] or "cast_f16_bf16_kernel" in text.splitlines()[line - 1]
+                continue
+            assert not re.fullmatch(produced, name), f"{f}: `{name}` is written by earlier kernels but is const __restrict__"
+        for m in re.finditer(r"__ldg\(([^;]*);", text):
+            arg = m.group(1)
+            assert re.search(r"code2|absmax|offset|bias|\bbe\b", arg), f"{f}: __ldg on something that is not a weight-side table: {arg}"
 
 
 def test_config_and_create_weights_mirror_reference(pkg):

@@ -404,6 +404,38 @@ def test_shape_the_pipeline_cannot_place_is_refused(pkg, cuda_device):
         assert int(b["meta"][4].item()) == 0
 
 
+def test_merged_launch_refuses_a_tile_list_built_for_larger_tiles(pkg, cuda_device):
+    """nf4moe_gemm_w13_w2 serves token tiles of at most 32 rows.  Handed the list nf4moe_bucket builds by default at a prefill-sized
+    batch (160-row tiles; meta[5] records the size), the kernel used to clamp its MMA N and drop the rest of every tile silently.
+    Now the whole launch is refused: NF4MOE_STATUS_DEC_NOFIT in meta[4], h and y untouched.  The same batch bucketed with 32-row
+    tiles runs and raises nothing."""
+    E, H, I, k, T = 4, 256, 128, 2, 320                      # 640 pairs on 4 experts: 160 rows per expert on average
+    g = torch.Generator(device=cuda_device).manual_seed(5)
+    code2 = torch.linspace(-1, 1, 256)
+    w13 = pkg.NF4ExpertWeights.quantize((torch.randn(E, 2 * I, H, generator=g, device=cuda_device) * 0.05).half(), code2)
+    w2 = pkg.NF4ExpertWeights.quantize((torch.randn(E, H, I, generator=g, device=cuda_device) * 0.05).half(), code2)
+    x = torch.randn(T, H, generator=g, device=cuda_device).half()
+    ids = torch.stack([torch.arange(T, device=cuda_device) % E, (torch.arange(T, device=cuda_device) + 1) % E], 1).to(torch.int32)
+    b = pkg.ops.bucket(ids, E)                               # tile_rows = 0: what the prefill grouped GEMM wants here
+    assert int(b["meta"][5].item()) > 32
+    xs = pkg.ops.permute_rows(x, b, k)
+    h = torch.full((T * k, I), 3.0, dtype=torch.float16, device=cuda_device)
+    y = torch.full((T * k, H), 3.0, dtype=torch.float16, device=cuda_device)
+    pkg.ops.expert_w13_w2(xs, w13, w2, b, T, k, nested=True, h=h, y=y)
+    torch.cuda.synchronize(cuda_device)
+    assert int(b["meta"][4].item()) & pkg._lib.STATUS_DEC_NOFIT
+    assert bool((h == 3.0).all()) and bool((y == 3.0).all())
+    b32 = pkg.ops.bucket(ids, E, tile_rows=32)
+    assert int(b32["meta"][5].item()) == 32
+    h2, y2 = pkg.ops.expert_w13_w2(pkg.ops.permute_rows(x, b32, k), w13, w2, b32, T, k, nested=True)
+    torch.cuda.synchronize(cuda_device)
+    assert int(b32["meta"][4].item()) == 0
+    ref = pkg.ops.moe_forward(x, w13, w2, k, topk_ids=ids, topk_weights=torch.ones(T, k, device=cuda_device), nested=True,
+                              regime=pkg.REGIME_GEMM_FAST)
+    got = y2.view(T, k, H).float().sum(1)
+    assert torch.allclose(got, ref.float(), atol=2e-2, rtol=1e-2)
+
+
 # ------------------------------------------------------------------------------------------------- real vLLM layer
 def test_real_vllm_fused_moe_forward(pkg, cuda_device):
     """What P/patch_6_add_bnb_moe.py:75-107 and P/patch_9_fusedmoe_unsloth.py:19-56 were trying to reach: a REAL
