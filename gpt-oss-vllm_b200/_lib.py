@@ -22,7 +22,7 @@ EXPORTED = (
     "nf4moe_version", "nf4moe_auto_regime", "nf4moe_auto_regime_for", "nf4moe_cast_f16_bf16", "nf4moe_last_error", "nf4moe_workspace_bytes", "nf4moe_dequant", "nf4moe_dequant_absmax",
     "nf4moe_quantize", "nf4moe_quantize_static", "nf4moe_route_topk", "nf4moe_bucket", "nf4moe_permute_rows", "nf4moe_combine",
     "nf4moe_gemv_w13_swiglu", "nf4moe_gemv_w2", "nf4moe_gemm_w13_swiglu", "nf4moe_gemm_w2", "nf4moe_gemm_w13_w2", "nf4moe_moe_forward", "nf4moe_moe_forward_bias",
-    "nf4moe_last_launch_count", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
+    "nf4moe_last_launch_count", "nf4moe_set_merged_decode", "nf4moe_ep_pack", "nf4moe_expert_rows", "nf4moe_combine_indexed",
     "nf4moe_workspace_status_offset", "nf4moe_expert_rows_bias", "nf4moe_combine_indexed_bias",
     "nf4moe_ep_dispatch_p2p", "nf4moe_ep_return_p2p", "nf4moe_ep_wait",
 )
@@ -59,6 +59,7 @@ def _declare(lib):
     lib.nf4moe_auto_regime_for.argtypes = [i32] * 4
     lib.nf4moe_last_error.restype = C.c_char_p
     lib.nf4moe_last_launch_count.restype = i32
+    lib.nf4moe_set_merged_decode.argtypes = [i32]
     lib.nf4moe_workspace_bytes.restype = sz
     lib.nf4moe_workspace_bytes.argtypes = [i32] * 5
     lib.nf4moe_workspace_status_offset.restype = sz

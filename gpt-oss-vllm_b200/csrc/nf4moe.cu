@@ -19,6 +19,7 @@ namespace {
 
 thread_local char g_err[512] = "";
 thread_local int g_launches = 0;
+std::atomic<int> g_merged_decode{1};   // nf4moe_set_merged_decode
 
 int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -187,6 +188,7 @@ extern "C" int nf4moe_debug_bucket_stamps(long long* out8) { return (int)cudaMem
 #endif
 const char* nf4moe_last_error(void) { return g_err; }
 int nf4moe_last_launch_count(void) { return g_launches; }
+int nf4moe_set_merged_decode(int enabled) { return g_merged_decode.exchange(enabled ? 1 : 0, std::memory_order_relaxed); }
 
 size_t nf4moe_workspace_bytes(int T, int E, int H, int I, int k) {
   if (T < 0 || E <= 0 || H <= 0 || I <= 0 || k <= 0) return 0;
@@ -496,7 +498,7 @@ static int run_experts(const void* x, const int32_t* ids, const nf4moe_qweight* 
     *launches += g_launches; g_launches = 0;
     // decode regime with the fused activation: w13 and w2 in ONE persistent launch (gemm_dec.cuh, DecSide)
     if (tile_rows <= kDecMaxTile && act == NF4MOE_ACT_SWIGLU_OAI && !bias_split && (w13->absmax_f32 == nullptr) == (w2->absmax_f32 == nullptr) &&
-        experiment_env("NF4MOE_DEC_MERGED", 1) != 0) {
+        g_merged_decode.load(std::memory_order_relaxed) != 0 && experiment_env("NF4MOE_DEC_MERGED", 1) != 0) {
       if (int rc = dec_launch_both(ws.xs, w13, ws.h, w2, y, ws.sorted, ws.meta, ws.tiles, T, k, E, act, mode, stream, g_err, sizeof(g_err),
                                    &g_launches, bias_fused ? w13_bias : nullptr, ws.status, tile_rows)) return rc;
       *launches += g_launches; g_launches = 0;

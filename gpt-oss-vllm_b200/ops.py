@@ -291,6 +291,14 @@ def last_launch_count() -> int:
     return int(_lib.load_library().nf4moe_last_launch_count())
 
 
+def set_merged_decode(enabled: bool) -> bool:
+    """nf4moe_set_merged_decode: False = the decode regime issues w13 and w2 as two launches (safe on a GPU this process shares --
+    MPS percentage, SM partitions, a concurrent kernel that waits for this stream -- where the single merged launch may not get all
+    its CTAs resident and would time out and trap); True (default) = one launch.  Results are bit-identical.  Returns the previous
+    setting; process-wide; set it before capturing CUDA graphs."""
+    return bool(_lib.load_library().nf4moe_set_merged_decode(1 if enabled else 0))
+
+
 # ---- expert parallelism (nf4moe_ep_pack / nf4moe_expert_rows / nf4moe_combine_indexed) ---------------------------------
 def ep_pack(x: torch.Tensor, ids: torch.Tensor, b: dict, E: int, world: int, cap: int, send_rows: torch.Tensor,
             send_ids: torch.Tensor, pair_slot: torch.Tensor, status: torch.Tensor) -> None:

@@ -230,6 +230,17 @@ int nf4moe_gemm_w13_w2(const void* x_sorted, const nf4moe_qweight* w13, const vo
                        const nf4moe_qweight* w2, void* y, const int32_t* sorted_pairs, const int32_t* meta, int32_t* tile_list,
                        int T, int k, int E, int act, int mode, void* stream);
 
+/* Process-wide switch for GPUs this process does not own outright.  The merged launch above assigns its work items to CTAs
+ * statically and lets w2 items spin until the w13 items of their token tile are counted, so it makes progress only if all of its
+ * CTAs (one per SM) get to run at the same time.  On an exclusively owned GPU they do.  Under an MPS active-thread percentage, a
+ * green context / SM partition, or next to a long-running kernel of another stream that itself waits for this one, some CTAs may
+ * never be scheduled while the resident ones spin: the kernel then gives up after 2^26 polls (seconds) and traps
+ * (NF4MOE_STATUS_DEP_TIMEOUT).  enabled = 0 makes nf4moe_moe_forward* / nf4moe_expert_rows* issue w13 and w2 as two launches of the
+ * same kernel (no cross-CTA wait, any residency; bit-identical results; about 9 % slower at 64 tokens on a B200); enabled != 0
+ * (the default) restores the single launch.  Returns the previous setting.  Takes effect for calls made afterwards -- set it
+ * before capturing CUDA graphs.  No counterpart in the reference (its forward is a Python loop, P/unsloth_to_vllm_converter.py:298-323). */
+int nf4moe_set_merged_decode(int enabled);
+
 /* ---- the whole layer ---------------------------------------------------------------------------------------------- */
 
 /* out[T,H] = MoE(x[T,H]).  Routing is computed from `router_logits` when non-NULL (the north-star / legacy
