@@ -441,6 +441,12 @@ def run_ep(args, pkg, dev, rank, world, code2):
                                       "tokens_per_s": Tp * world / (ms_p * 1e-3), "tflops_all_ranks": flops / (ms_p * 1e-3) / 1e12,
                                       "tensor_frac_of_nominal_per_gpu": flops / (ms_p * 1e-3) / 1e12 / world / 2250.0}
     wire = layers[0].wire_bytes()
+    # this library's kernels per layer on this rank, by phase (EPMoELayer.forward): counted, not estimated -- the owner chain is
+    # what nf4moe_expert_rows reported for the last layer it ran; NCCL's own kernels are not ours and are not counted
+    p2p = exchange.kind == "p2p"
+    ep_launches = {"route": 1, "bucket": 1, "dispatch_p2p" if p2p else "pack": 1,
+                   "wait": 2 if (p2p and not getattr(exchange, "fused_wait", False)) else 0,
+                   "expert_rows": pkg.ops.last_launch_count(), "return_p2p": 1 if p2p else 0, "combine_indexed": 1}
     if rank == 0:
         T_all = T * world
         shape_name = "gpt-oss-120b-shape" if big else "gpt-oss-20b"
@@ -465,7 +471,7 @@ def run_ep(args, pkg, dev, rank, world, code2):
                 "ep_matches_single_gpu": ep_matches, "ep_vs_single_gpu_max_abs_diff": ep_maxdiff,
                 "e2e": {"value": T_all / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": hx.numel() * 2 + hlg.numel() * 2,
                         "d2h_bytes_per_step": hout.numel() * 2, "ms_per_step": e2e_ms, "api": e2e_api},
-                "gpu_launches": (pkg.ops.last_launch_count() + 5) * L * K,
+                "gpu_launches": sum(ep_launches.values()) * L * K, "launches_per_layer": ep_launches,
                 "collectives_per_layer": exchange.collectives_per_layer, "wire_bytes_per_rank_per_layer": wire,
                 "roofline": {"bound": "hbm", "kernel": "expert_rows chain (bucket + permute + w13 + w2) on this rank's experts",
                              "achieved": wbytes / d / 1e9, "peak": peak, "unit": "GB/s", "frac": wbytes / d / 1e9 / peak,
@@ -533,8 +539,9 @@ def stack_and_kernel_times(pkg, dev, stack, T, E, regime, nested, seed, reps=6):
     pkg.ops.check_status(ws)
     peak, _ = measured_peaks()
     ms = statistics.mean(ts)
-    b13 = eact * stack[0][0].nbytes(nested) + T * H * 2 + T * TOP_K * I * 2
-    b2 = eact * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2
+    # algorithmic bytes: weights + absmax of the active experts, x in, out out; the h / y intermediates do not count
+    b13 = eact * stack[0][0].nbytes(nested) + T * H * 2
+    b2 = eact * stack[0][1].nbytes(nested) + T * H * 2
     d13, d2 = statistics.mean(t13) * 1e-3, statistics.mean(t2) * 1e-3
     name = {pkg.REGIME_GEMV: "gemv", pkg.REGIME_GEMM: "tcgen05 exact operand", pkg.REGIME_GEMM_FAST: "tcgen05 fast operand"}[eff]
     return {"tokens": T, "regime": name, "absmax": "nested" if nested else "flat", "experts_active_mean": eact,
@@ -574,7 +581,6 @@ def run_ours(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from oracle import nf4_oracle as orc     # cpu_baseline leg only (and the code2 table, which is data)
     pkg = importlib.import_module("gpt-oss-vllm_b200")
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -592,7 +598,7 @@ def run_ours(args):
 
     E, T, L, K, W = args.experts, args.tokens, args.layers, args.steps, max(3, args.warmup)
     nested = args.absmax == "nested"
-    code2 = torch.from_numpy(orc.create_dynamic_map())
+    code2 = pkg.dynamic_code_map()          # the product's own table generator: the GPU arm needs nothing from oracle/
     if world > 1:
         return run_ep(args, pkg, dev, rank, world, code2)
 
@@ -757,10 +763,12 @@ def run_ours(args):
             if rep > 0:
                 t_both.append(a0.elapsed_time(a1) / L)
     ea = sum(eact) / len(eact)
-    b13 = ea * stack[0][0].nbytes(nested) + T * H * 2 + T * TOP_K * I * 2
-    b2 = ea * stack[0][1].nbytes(nested) + T * TOP_K * I * 2 + T * TOP_K * H * 2
+    # algorithmic bytes: E_act * (packed + absmax) + T * (2 * H * 2 + E * 2); the h [T k, I] and y [T k, H] intermediates
+    # are NOT algorithmic bytes -- they count against the kernel, not for it
+    b13 = ea * stack[0][0].nbytes(nested) + T * H * 2
+    b2 = ea * stack[0][1].nbytes(nested) + T * H * 2
     d13, d2 = statistics.mean(t13) * 1e-3, statistics.mean(t2) * 1e-3
-    layer_bytes = b13 + b2
+    layer_bytes = b13 + b2 + T * E * 2
     traffic, traffic_src = None, None
     try:   # dram bytes of this kernel at this configuration from the committed `ncu --set full` capture (never measured under ncu here)
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:

@@ -11,7 +11,7 @@ from ._lib import (ACT_CHUNK_SILU, ACT_SWIGLU_OAI, REGIME_AUTO, REGIME_GEMM, REG
                    load_library)
 from .graphed import GraphedForward  # noqa: F401
 from .moe_method import B200NF4MoEConfig, B200NF4MoEMethod, NF4MoELayer  # noqa: F401
-from .quant import BLOCKSIZE, NESTED_BLOCKSIZE, NF4ExpertWeights  # noqa: F401
+from .quant import BLOCKSIZE, NESTED_BLOCKSIZE, NF4ExpertWeights, dynamic_code_map  # noqa: F401
 
 __all__ = ["NF4ExpertWeights", "B200NF4MoEConfig", "B200NF4MoEMethod", "NF4MoELayer", "GraphedForward", "ops", "load_library",
            "Nf4MoeError"]

@@ -47,6 +47,26 @@ def _shared_code2(t: torch.Tensor | None) -> torch.Tensor | None:
     return _CODE2_TABLES.setdefault(key, t)
 
 
+def dynamic_code_map() -> torch.Tensor:
+    """The 256-entry table (`code2`, fp32, ascending) that double quantisation stores the absmax bytes against: bitsandbytes'
+    signed 8-bit "dynamic" map as used by quantize_4bit(compress_statistics=True) (V/model_executor/model_loader/
+    bitsandbytes_loader.py:433-438 is where vLLM triggers it).  Seven decades 1e-6 .. 1e0; decade d carries 2^d magnitudes --
+    the midpoints of 2^d equal steps across [0.1, 1] -- with both signs, plus exactly 0 and exactly 1: 2 * 127 + 2 = 256 values.
+    It is DATA as far as dequantisation goes (the table travels in the quant state), so this exists only for callers that
+    quantise locally (NF4ExpertWeights.quantize, bench.py, tests)."""
+    import numpy as np
+    vals = [np.float32(0.0), np.float32(1.0)]
+    for d in range(7):
+        edges = np.linspace(0.1, 1, 2 ** d + 1, dtype=np.float32)
+        mags = (10 ** (d - 6)) * ((edges[:-1] + edges[1:]) / 2.0)
+        vals.extend(mags)
+        vals.extend(-mags)
+    table = np.sort(np.asarray(vals, dtype=np.float32))
+    assert table.shape == (256,)
+    return torch.from_numpy(table)
+
+
+
 @dataclass
 class NF4ExpertWeights:
     """One fused expert matrix set: E experts x [rows, cols]."""
