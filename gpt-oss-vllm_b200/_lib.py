@@ -11,6 +11,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libnf4moe.so")
 
+ABI_VERSION = 101          # NF4MOE_VERSION of include/nf4moe.h this binding was written against
 ACT_SWIGLU_OAI = 0
 ACT_CHUNK_SILU = 1
 REGIME_AUTO, REGIME_GEMV, REGIME_GEMM, REGIME_GEMM_FAST = 0, 1, 2, 3

@@ -20,7 +20,7 @@ def test_library_exports_header_symbols(pkg):
     assert declared == set(pkg._lib.EXPORTED)
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.nf4moe_version() == 101
+    assert lib.nf4moe_version() == 101 == pkg._lib.ABI_VERSION
     assert int(re.search(r"#define NF4MOE_VERSION (\d+)", header).group(1)) == 101
 
 
